@@ -1,0 +1,123 @@
+/* pcb.h — C ABI of the B200-native octree/LOD builder (libpcb.so / libpcb.a).
+ *
+ * Drop-in boundary for point-converter's conversion path.  The reference has
+ * no FFI; its seam is the Rust API below (paths relative to /root/reference):
+ *
+ *   load_metadata + Converter::new      point-converter/src/lib.rs:12-13, 86-101;
+ *                                       converter.rs:79-94            -> pcb_open
+ *   per input file (batches never span  point-converter/src/lib.rs:17-32
+ *   files)                                                            -> pcb_begin_file
+ *   Converter::add_points_batch         converter.rs:106-112 (called once per
+ *                                       get_batch(10_000), lib.rs:32-34) -> pcb_add_points
+ *   Drop for Converter (save_cache +    converter.rs:218-246           -> pcb_finish
+ *   save_metadata)
+ *
+ * Plain pointers and sizes only; no exceptions cross the boundary; every
+ * function returns 0 or a negative pcb_status.  One caller thread per handle
+ * (the reference's Converter is not shared either).  There is NO CPU fallback:
+ * without a CUDA device every compute entry point fails with PCB_ERR_CUDA.
+ *
+ * Semantics: results (node point sets, overflow lists in emission order,
+ * headers, metadata.json) are bit-identical to the reference CLI fed the same
+ * files in the same order.  The build is bulk and level-synchronous: points are
+ * staged to the device by pcb_add_points and the octree is built in pcb_finish.
+ */
+#ifndef PCB_H
+#define PCB_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* point-converter/src/point.rs:8-14, 25-37 — 16-byte little-endian record. */
+typedef struct pcb_point {
+    float x, y, z;
+    uint8_t rgba[4];
+} pcb_point;
+
+typedef struct pcb_handle pcb_handle;
+
+typedef enum pcb_status {
+    PCB_OK = 0,
+    PCB_ERR_ARG = -1,      /* bad argument / call order */
+    PCB_ERR_IO = -2,       /* file system error (reference: panic, converter.rs:84,153,171,203,243) */
+    PCB_ERR_FORMAT = -3,   /* unreadable metadata.json / node file (reference: unwrap panic, lib.rs:94) */
+    PCB_ERR_CUDA = -4,     /* CUDA error, or no device: there is no CPU fallback */
+    PCB_ERR_RANGE = -5,    /* non-finite coordinate, level-0 index out of range, or octree deeper than
+                              31 levels (reference overflows 2u32.pow(32), metadata.rs:92) */
+    PCB_ERR_NOMEM = -6
+} pcb_status;
+
+/* flags for pcb_options.flags */
+#define PCB_FLAG_NO_FILES 1u     /* do not touch the file system; node images stay in host memory and are
+                                    read back with pcb_node_* (tests, bench e2e) */
+#define PCB_FLAG_DEVICE_ONLY 2u  /* implies NO_FILES; node images stay in device memory (bench `value`) */
+#define PCB_FLAG_PROFILE 4u      /* time every kernel class with CUDA events (pcb_kernel_stat) */
+
+typedef struct pcb_options {
+    uint32_t struct_size;   /* sizeof(pcb_options), for ABI growth */
+    int32_t device;         /* CUDA device ordinal */
+    uint32_t batch_size;    /* 0 => 10000 (lib.rs:32).  GUI caller uses 50000 (src/plugins/converter.rs:600) */
+    uint32_t flags;
+    /* Config override for a FRESH output only (ignored when metadata.json exists).  All zero => reference
+       defaults 5000 / 96 / 1000.0 (metadata.rs:80-88).  The reference CLI has no such flags; tests use
+       this the way they would pre-seed a metadata.json. */
+    uint32_t cell_point_overflow_limit;
+    uint32_t sub_grid_dimension;
+    float max_cell_size;
+    uint32_t reserved;
+} pcb_options;
+
+typedef struct pcb_stats {
+    uint64_t number_of_points;   /* metadata.number_of_points after this run */
+    uint64_t points_added;       /* points staged through this handle */
+    uint64_t arrivals;           /* sum over levels of points delivered to cells */
+    uint64_t nodes_written;      /* node images produced by this run */
+    uint64_t node_bytes;         /* total bytes of those images */
+    uint32_t hierarchies;        /* metadata.hierarchies after this run */
+    uint32_t levels_built;       /* levels visited by this run */
+    uint64_t gpu_launches;       /* kernels launched by this handle */
+    double h2d_seconds, build_seconds, d2h_seconds, write_seconds, total_seconds;
+    float bbox_min[3], bbox_max[3];
+} pcb_stats;
+
+typedef struct pcb_kernel_stat {
+    char name[32];
+    uint64_t launches;
+    uint64_t units;          /* elements processed, summed over launches */
+    uint64_t bytes;          /* algorithmic bytes, summed over launches */
+    double ms;               /* CUDA-event time, summed over launches (PCB_FLAG_PROFILE only) */
+} pcb_kernel_stat;
+
+typedef struct pcb_node_info {
+    uint32_t hierarchy;
+    int32_t index[3];
+    uint64_t offset;         /* into the level image buffer */
+    uint64_t size;           /* bytes of the node file image */
+} pcb_node_info;
+
+int pcb_open(const char* out_dir, const pcb_options* opt, pcb_handle** out);
+int pcb_begin_file(pcb_handle* h);
+int pcb_add_points(pcb_handle* h, const pcb_point* pts, uint64_t n);
+/* Same, but `d_pts` is a device pointer on the handle's device (resident-input path). */
+int pcb_add_points_device(pcb_handle* h, const pcb_point* d_pts, uint64_t n);
+int pcb_finish(pcb_handle* h, pcb_stats* stats);
+void pcb_close(pcb_handle* h);
+const char* pcb_last_error(const pcb_handle* h);
+
+/* Results in memory (after pcb_finish). */
+uint64_t pcb_node_count(const pcb_handle* h);
+int pcb_node_get(const pcb_handle* h, uint64_t i, pcb_node_info* info, const uint8_t** host_image);
+int pcb_metadata_json(const pcb_handle* h, char* buf, uint64_t cap); /* returns length */
+int pcb_kernel_stat_count(const pcb_handle* h);
+int pcb_kernel_stat_get(const pcb_handle* h, int i, pcb_kernel_stat* out);
+
+const char* pcb_version(void);
+int pcb_device_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCB_H */
