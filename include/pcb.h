@@ -100,7 +100,14 @@ typedef struct pcb_node_info {
 
 int pcb_open(const char* out_dir, const pcb_options* opt, pcb_handle** out);
 int pcb_begin_file(pcb_handle* h);
+/* Appends `n` points of the current input file; the stream is cut into batches of pcb_options.batch_size
+   points exactly as lib.rs:31-35 does with get_batch(10_000).  Host pointer; copied before returning. */
 int pcb_add_points(pcb_handle* h, const pcb_point* pts, uint64_t n);
+/* Exactly ONE batch, the direct mirror of Converter::add_points_batch(Vec<Point>) (converter.rs:106-112;
+   the GUI caller src/plugins/converter.rs:203 uses its own batch sizes).  n may be 0. */
+int pcb_add_points_batch(pcb_handle* h, const pcb_point* pts, uint64_t n);
+/* Optional capacity hint (total points this handle will receive). */
+int pcb_reserve(pcb_handle* h, uint64_t n);
 /* Same, but `d_pts` is a device pointer on the handle's device (resident-input path). */
 int pcb_add_points_device(pcb_handle* h, const pcb_point* d_pts, uint64_t n);
 int pcb_finish(pcb_handle* h, pcb_stats* stats);

@@ -1,0 +1,289 @@
+// api.cpp — the C ABI of include/pcb.h over pcb::Builder.  No exception crosses the boundary.
+// Reference seam being replaced: load_metadata + Converter::new / add_points_batch / Drop
+// (point-converter/src/lib.rs:11-60, 86-101; converter.rs:78-112, 218-246).
+#include <errno.h>
+#include <sys/stat.h>
+#include <sys/types.h>
+
+#include <algorithm>
+#include <atomic>
+#include <memory>
+#include <vector>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <thread>
+
+#include "builder.h"
+
+using namespace pcb;
+
+namespace pcb {
+int device_count();
+}
+
+struct pcb_handle {
+    std::unique_ptr<Builder> builder;
+    Metadata meta;
+    std::string out_dir;
+    pcb_options opt;
+    bool merge = false;     // metadata.json existed at open (lib.rs:92-95)
+    bool finished = false;
+    std::string err;
+    std::string meta_json;
+    std::vector<KernelStat> kstats;
+};
+
+static thread_local std::string g_open_error;
+
+static int fail(pcb_handle* h, int status, const std::string& msg) {
+    if (h) h->err = msg;
+    else g_open_error = msg;
+    return status;
+}
+
+// create_dir_all (converter.rs:80)
+static bool mkdir_p(const std::string& path) {
+    if (path.empty()) return true;
+    std::string cur;
+    for (size_t i = 0; i <= path.size(); i++) {
+        if (i == path.size() || path[i] == '/') {
+            if (!cur.empty() && cur != "/" && ::mkdir(cur.c_str(), 0777) != 0 && errno != EEXIST) return false;
+        }
+        if (i < path.size()) cur += path[i];
+    }
+    return true;
+}
+
+static bool read_file(const std::string& path, std::vector<uint8_t>* out, bool* not_found) {
+    *not_found = false;
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) {
+        *not_found = (errno == ENOENT);
+        return false;
+    }
+    std::fseek(f, 0, SEEK_END);
+    long n = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    out->resize(n > 0 ? (size_t)n : 0);
+    size_t got = n > 0 ? std::fread(out->data(), 1, (size_t)n, f) : 0;
+    std::fclose(f);
+    return got == out->size();
+}
+
+static bool write_file(const std::string& path, const void* data, size_t n) {
+    FILE* f = std::fopen(path.c_str(), "wb");
+    if (!f) return false;
+    size_t put = n ? std::fwrite(data, 1, n, f) : 0;
+    return (std::fclose(f) == 0) && put == n;
+}
+
+// converter.rs:180-207: a missing file means a new cell; any other failure is fatal (reference panics)
+struct DirNodeSource : NodeSource {
+    std::string dir;
+    bool load(uint32_t hierarchy, const int32_t idx[3], ExistingNode* out) override {
+        std::vector<uint8_t> bytes;
+        bool nf = false;
+        std::string p = dir + "/" + node_rel_path(hierarchy, idx);
+        if (!read_file(p, &bytes, &nf)) {
+            if (nf) return false;
+            throw Error{PCB_ERR_IO, "cannot read node file " + p};
+        }
+        if (!parse_node(bytes.data(), bytes.size(), out)) throw Error{PCB_ERR_FORMAT, "corrupt node file " + p};
+        return true;
+    }
+};
+
+extern "C" {
+
+const char* pcb_version(void) { return "point-cloud-b200 0.1 (sm_100a)"; }
+int pcb_device_count(void) { return pcb::device_count(); }
+
+int pcb_open(const char* out_dir, const pcb_options* opt, pcb_handle** out) {
+    if (!out) return PCB_ERR_ARG;
+    *out = nullptr;
+    std::unique_ptr<pcb_handle> h(new pcb_handle());
+    std::memset(&h->opt, 0, sizeof h->opt);
+    if (opt) std::memcpy(&h->opt, opt, std::min<size_t>(sizeof h->opt, opt->struct_size ? opt->struct_size : sizeof h->opt));
+    if (h->opt.flags & PCB_FLAG_DEVICE_ONLY) h->opt.flags |= PCB_FLAG_NO_FILES;
+    h->out_dir = out_dir ? out_dir : "";
+    if (h->out_dir.empty()) h->opt.flags |= PCB_FLAG_NO_FILES;
+    if (!h->out_dir.empty()) {
+        if (!(h->opt.flags & PCB_FLAG_NO_FILES) && !mkdir_p(h->out_dir))
+            return fail(nullptr, PCB_ERR_IO, "cannot create output directory " + h->out_dir);
+        std::vector<uint8_t> bytes;
+        bool nf = false;
+        if (read_file(h->out_dir + "/metadata.json", &bytes, &nf)) {  // lib.rs:87-95
+            if (!metadata_from_json(std::string(bytes.begin(), bytes.end()), &h->meta))
+                return fail(nullptr, PCB_ERR_FORMAT, "unreadable metadata.json");
+            h->merge = true;
+        }
+    }
+    if (!h->merge) {  // Metadata::default() (metadata.rs:30-41), optionally with a test-supplied config
+        if (h->opt.cell_point_overflow_limit || h->opt.sub_grid_dimension || h->opt.max_cell_size != 0.0f) {
+            h->meta.cell_point_overflow_limit = h->opt.cell_point_overflow_limit;
+            h->meta.sub_grid_dimension = h->opt.sub_grid_dimension;
+            h->meta.max_cell_size = h->opt.max_cell_size;
+        }
+    }
+    try {
+        h->builder.reset(new Builder(h->opt.device, h->opt.flags));
+    } catch (const Error& e) {
+        return fail(nullptr, e.status, e.message);
+    } catch (const std::exception& e) {
+        return fail(nullptr, PCB_ERR_NOMEM, e.what());
+    }
+    *out = h.release();
+    return PCB_OK;
+}
+
+const char* pcb_last_error(const pcb_handle* h) { return h ? h->err.c_str() : g_open_error.c_str(); }
+
+#define PCB_GUARD(h, body)                                 \
+    if (!(h)) return PCB_ERR_ARG;                          \
+    try {                                                  \
+        body;                                              \
+    } catch (const Error& e) {                             \
+        return fail((h), e.status, e.message);             \
+    } catch (const std::bad_alloc&) {                      \
+        return fail((h), PCB_ERR_NOMEM, "out of host memory"); \
+    } catch (const std::exception& e) {                    \
+        return fail((h), PCB_ERR_ARG, e.what());           \
+    }                                                      \
+    return PCB_OK;
+
+int pcb_reserve(pcb_handle* h, uint64_t n) { PCB_GUARD(h, h->builder->reserve(n)) }
+
+int pcb_begin_file(pcb_handle* h) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    PCB_GUARD(h, h->builder->begin_file())
+}
+
+int pcb_add_points(pcb_handle* h, const pcb_point* pts, uint64_t n) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    if (h && n && !pts) return fail(h, PCB_ERR_ARG, "null points");
+    PCB_GUARD(h, h->builder->add_points(pts, n, h->opt.batch_size, false))
+}
+
+int pcb_add_points_device(pcb_handle* h, const pcb_point* d_pts, uint64_t n) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    if (h && n && !d_pts) return fail(h, PCB_ERR_ARG, "null points");
+    PCB_GUARD(h, h->builder->add_points(d_pts, n, h->opt.batch_size, true))
+}
+
+int pcb_add_points_batch(pcb_handle* h, const pcb_point* pts, uint64_t n) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    if (h && n && !pts) return fail(h, PCB_ERR_ARG, "null points");
+    PCB_GUARD(h, h->builder->add_points_one_batch(pts, n, false))
+}
+
+static void write_outputs(pcb_handle* h, pcb_stats* stats) {
+    auto t0 = std::chrono::steady_clock::now();
+    const auto& nodes = h->builder->nodes();
+    const auto& levels = h->builder->levels();
+    // converter.rs:141-158: h_<level> directories
+    for (uint32_t l = 0; l < h->meta.hierarchies; l++) {
+        std::string d = h->out_dir + "/h_" + std::to_string(l);
+        if (::mkdir(d.c_str(), 0777) != 0 && errno != EEXIST) throw Error{PCB_ERR_IO, "cannot create " + d};
+    }
+    // converter.rs:209-224 save_cell for every node touched by this run
+    std::atomic<size_t> next{0};
+    std::atomic<bool> bad{false};
+    unsigned nthreads = std::min<unsigned>(16, std::max<unsigned>(1, std::thread::hardware_concurrency()));
+    if (nodes.size() < 64) nthreads = 1;
+    auto worker = [&]() {
+        for (;;) {
+            size_t i = next.fetch_add(1);
+            if (i >= nodes.size()) return;
+            const NodeRec& r = nodes[i];
+            const unsigned char* img = levels[r.level_slot].h_image + r.offset;
+            if (!write_file(h->out_dir + "/" + node_rel_path(r.hierarchy, r.index), img, r.size)) bad = true;
+        }
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < nthreads; t++) th.emplace_back(worker);
+    worker();
+    for (auto& t : th) t.join();
+    if (bad) throw Error{PCB_ERR_IO, "failed to write a node file"};
+    // converter.rs:226-238 save_metadata
+    if (!write_file(h->out_dir + "/metadata.json", h->meta_json.data(), h->meta_json.size()))
+        throw Error{PCB_ERR_IO, "failed to write metadata.json"};
+    if (stats) stats->write_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+int pcb_finish(pcb_handle* h, pcb_stats* stats) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    PCB_GUARD(h, {
+        auto t0 = std::chrono::steady_clock::now();
+        DirNodeSource src;
+        src.dir = h->out_dir;
+        h->builder->build(&h->meta, h->merge ? &src : nullptr);
+        h->finished = true;
+        h->meta_json = metadata_to_json(h->meta);
+        h->kstats = h->builder->kernel_stats();
+        pcb_stats s;
+        std::memset(&s, 0, sizeof s);
+        if (!(h->opt.flags & PCB_FLAG_NO_FILES)) write_outputs(h, &s);
+        s.number_of_points = h->meta.number_of_points;
+        s.points_added = h->builder->points_added();
+        s.arrivals = h->builder->arrivals();
+        s.nodes_written = h->builder->nodes().size();
+        for (auto& n : h->builder->nodes()) s.node_bytes += n.size;
+        s.hierarchies = h->meta.hierarchies;
+        s.levels_built = h->builder->levels_built();
+        s.gpu_launches = h->builder->launches();
+        s.h2d_seconds = h->builder->h2d_seconds();
+        s.build_seconds = h->builder->build_seconds();
+        s.d2h_seconds = h->builder->d2h_seconds();
+        s.total_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        for (int a = 0; a < 3; a++) {
+            s.bbox_min[a] = h->meta.bbox_min[a];
+            s.bbox_max[a] = h->meta.bbox_max[a];
+        }
+        if (stats) *stats = s;
+    })
+}
+
+void pcb_close(pcb_handle* h) { delete h; }
+
+uint64_t pcb_node_count(const pcb_handle* h) { return (h && h->finished) ? h->builder->nodes().size() : 0; }
+
+int pcb_node_get(const pcb_handle* h, uint64_t i, pcb_node_info* info, const uint8_t** host_image) {
+    if (!h || !h->finished || i >= h->builder->nodes().size()) return PCB_ERR_ARG;
+    const NodeRec& r = h->builder->nodes()[i];
+    if (info) {
+        info->hierarchy = r.hierarchy;
+        for (int a = 0; a < 3; a++) info->index[a] = r.index[a];
+        info->offset = r.offset;
+        info->size = r.size;
+    }
+    if (host_image) {
+        const unsigned char* base = h->builder->levels()[r.level_slot].h_image;
+        *host_image = base ? base + r.offset : nullptr;
+    }
+    return PCB_OK;
+}
+
+int pcb_metadata_json(const pcb_handle* h, char* buf, uint64_t cap) {
+    if (!h || !h->finished) return PCB_ERR_ARG;
+    if (buf && cap > h->meta_json.size()) std::memcpy(buf, h->meta_json.c_str(), h->meta_json.size() + 1);
+    return (int)h->meta_json.size();
+}
+
+int pcb_kernel_stat_count(const pcb_handle* h) { return h ? (int)h->kstats.size() : 0; }
+
+int pcb_kernel_stat_get(const pcb_handle* h, int i, pcb_kernel_stat* out) {
+    if (!h || !out || i < 0 || i >= (int)h->kstats.size()) return PCB_ERR_ARG;
+    const KernelStat& k = h->kstats[i];
+    std::memset(out, 0, sizeof *out);
+    std::snprintf(out->name, sizeof out->name, "%s", k.name.c_str());
+    out->launches = k.launches;
+    out->units = k.units;
+    out->bytes = k.bytes;
+    out->ms = k.ms;
+    return PCB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,640 @@
+// builder.cu — host driver of the device build: owns device memory and streams, launches the per-level
+// kernels of level.cuh in the order tests/bulk_model.py specifies.  There is no CPU compute path here:
+// without a CUDA device the constructor throws (PCB_ERR_CUDA).
+#include <limits.h>
+#include <string.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+
+#include "builder.h"
+#include "common.cuh"
+#include "level.cuh"
+#include "radix.cuh"
+#include "scan.cuh"
+
+namespace pcb {
+
+static double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+struct Scratch {  // small device-resident results, mirrored in pinned host memory
+    u64 diffmask;
+    u32 err;
+    u32 ncell;
+    u32 nwin;
+    u32 pad;
+    int bbox[6];
+    LevelTotals totals;
+};
+
+class BuilderImpl {
+   public:
+    int device;
+    uint32_t flags;
+    bool profile;
+    cudaStream_t st = nullptr, copy_st = nullptr;
+    uint32_t limit = 5000, dim = 96;
+    float max_cell_size = 1000.0f;
+
+    // staged input (input order), batch segments
+    PcbPoint* d_in = nullptr;
+    u64 n_in = 0, cap_in = 0;
+    std::vector<BatchSeg> segs;
+    u32 next_batch = 0;
+    u64 batches = 0;
+
+    Scratch* d_scr = nullptr;
+    Scratch* h_scr = nullptr;
+
+    std::vector<NodeRec> nodes;
+    std::vector<LevelImage> levels;
+    std::vector<KernelStat> stats;
+    struct ProfRec {
+        int cls;
+        cudaEvent_t a, b;
+    };
+    std::vector<ProfRec> prof_recs;
+    cudaEvent_t prof_a = nullptr;
+    u64 launches = 0, arrivals = 0;
+    u32 levels_built = 0;
+    double h2d_s = 0, build_s = 0, d2h_s = 0;
+
+    BuilderImpl(int dev, uint32_t fl) : device(dev), flags(fl), profile((fl & PCB_FLAG_PROFILE) != 0) {
+        int count = 0;
+        cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || count == 0)
+            throw Error{PCB_ERR_CUDA, "no CUDA device: this library has no CPU fallback"};
+        if (dev < 0 || dev >= count) throw Error{PCB_ERR_ARG, "bad device ordinal"};
+        CUDA_TRY(cudaSetDevice(dev));
+        CUDA_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&copy_st, cudaStreamNonBlocking));
+        cudaMemPool_t pool;
+        CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, dev));
+        uint64_t thr = UINT64_MAX;
+        CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+        CUDA_TRY(cudaMalloc(&d_scr, sizeof(Scratch)));
+        CUDA_TRY(cudaHostAlloc(&h_scr, sizeof(Scratch), cudaHostAllocDefault));
+    }
+    ~BuilderImpl() {
+        cudaSetDevice(device);
+        cudaDeviceSynchronize();
+        for (auto& l : levels) {
+            if (l.d_image) cudaFree(l.d_image);
+            if (l.h_image) cudaFreeHost(l.h_image);
+        }
+        if (d_in) cudaFree(d_in);
+        if (d_scr) cudaFree(d_scr);
+        if (h_scr) cudaFreeHost(h_scr);
+        if (st) cudaStreamDestroy(st);
+        if (copy_st) cudaStreamDestroy(copy_st);
+    }
+
+    template <class T>
+    T* dalloc(u64 n) {
+        void* p = nullptr;
+        CUDA_TRY(cudaMallocAsync(&p, std::max<u64>(n, 1) * sizeof(T), st));
+        return (T*)p;
+    }
+    void dfree(void* p) {
+        if (p) CUDA_TRY(cudaFreeAsync(p, st));
+    }
+
+    int cls(const char* name) {
+        for (size_t i = 0; i < stats.size(); i++)
+            if (stats[i].name == name) return (int)i;
+        KernelStat s;
+        s.name = name;
+        stats.push_back(s);
+        return (int)stats.size() - 1;
+    }
+    void pb() {
+        if (!profile) return;
+        CUDA_TRY(cudaEventCreate(&prof_a));
+        CUDA_TRY(cudaEventRecord(prof_a, st));
+    }
+    void pe(const char* name, u64 nlaunch, u64 units, u64 bytes) {
+        int c = cls(name);
+        stats[c].launches += nlaunch;
+        stats[c].units += units;
+        stats[c].bytes += bytes;
+        launches += nlaunch;
+        if (!profile) return;
+        ProfRec r;
+        r.cls = c;
+        r.a = prof_a;
+        CUDA_TRY(cudaEventCreate(&r.b));
+        CUDA_TRY(cudaEventRecord(r.b, st));
+        prof_recs.push_back(r);
+    }
+    void prof_collect() {
+        for (auto& r : prof_recs) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, r.a, r.b);
+            stats[r.cls].ms += ms;
+            cudaEventDestroy(r.a);
+            cudaEventDestroy(r.b);
+        }
+        prof_recs.clear();
+    }
+
+    void fetch_scratch() {
+        CUDA_TRY(cudaMemcpyAsync(h_scr, d_scr, sizeof(Scratch), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+    }
+    void check_err() {
+        u32 e = h_scr->err;
+        if (e & PCB_DERR_NONFINITE) throw Error{PCB_ERR_RANGE, "non-finite coordinate in input"};
+        if (e & PCB_DERR_L0RANGE) throw Error{PCB_ERR_RANGE, "level-0 cell index outside +-2^20"};
+        if (e & PCB_DERR_HEXRANGE)
+            throw Error{PCB_ERR_RANGE, "hex key outside its cell window (coordinate precision exhausted)"};
+        if (e & PCB_DERR_NEST) throw Error{PCB_ERR_RANGE, "child cell index does not nest in its parent"};
+    }
+
+    void reserve(u64 n) {
+        if (n <= cap_in) return;
+        if (n >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "more than 2^30-1 points on one device"};
+        PcbPoint* p = nullptr;
+        CUDA_TRY(cudaMalloc(&p, n * sizeof(PcbPoint)));
+        if (n_in) CUDA_TRY(cudaMemcpyAsync(p, d_in, n_in * sizeof(PcbPoint), cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        if (d_in) CUDA_TRY(cudaFree(d_in));
+        d_in = p;
+        cap_in = n;
+    }
+
+    // ---- batch bookkeeping (lib.rs:31-52).  A "run" = one input file: its points are cut into batches
+    // of run_bs points; a file without points still yields one (empty) batch because lib.rs:32-34 calls
+    // add_points_batch before it looks at remaining_points().
+    bool run_open = false;
+    u32 run_bs = 0;
+    u64 run_points = 0;
+    void end_run() {
+        if (!run_open) return;
+        u64 bs = std::max<u32>(run_bs, 1);
+        u64 nb = std::max<u64>(1, (run_points + bs - 1) / bs);
+        next_batch += (u32)nb;
+        batches += nb;
+        run_open = false;
+    }
+    void open_run() {
+        end_run();
+        run_open = true;
+        run_bs = 0;
+        run_points = 0;
+    }
+    void begin_file() { open_run(); }
+
+    void add(const pcb_point* pts, u64 n, u32 batch_size, bool device_ptr, bool one_batch) {
+        CUDA_TRY(cudaSetDevice(device));
+        if (n_in + n >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "more than 2^30-1 points on one device"};
+        if (one_batch) {
+            open_run();
+            batch_size = (u32)std::max<u64>(n, 1);
+        } else if (!run_open || (run_bs != 0 && run_bs != batch_size)) {
+            open_run();
+        }
+        if (run_bs == 0 && n > 0) {
+            run_bs = batch_size;
+            // the run may already hold batches only if it held points; it does not: start a segment here
+            BatchSeg s{(u32)n_in, next_batch, batch_size, 0};
+            segs.push_back(s);
+        }
+        run_points += n;
+        if (n) {
+            if (n_in + n > cap_in) reserve(std::min<u64>(std::max<u64>(n_in + n, cap_in + cap_in / 2), (1ull << 30) - 1));
+            double t0 = now_s();
+            CUDA_TRY(cudaMemcpyAsync(d_in + n_in, pts, n * sizeof(PcbPoint),
+                                     device_ptr ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+            if (!device_ptr) {
+                CUDA_TRY(cudaStreamSynchronize(st));
+                h2d_s += now_s() - t0;
+            }
+            n_in += n;
+        }
+        if (one_batch) end_run();
+    }
+
+    void build(Metadata* meta, NodeSource* existing);
+    void build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start, int*& cell_idx, u32& n, u32& ncell,
+                     Metadata* meta, NodeSource* existing);
+};
+
+static int bits_for(u32 range) {
+    int b = 1;
+    while ((1u << b) < range) b++;
+    return b;
+}
+
+// hex window of one cell: the cell spans 2*dim hex radii per axis; columns are sqrt(3) R apart, rows
+// 1.5 R, layers R (hex.rs:55-65).  The window origin is the key of the min corner minus a margin that
+// absorbs rounding and the odd-row column shift; k_hexkey verifies every key falls inside.
+static LevelGeom make_geom(float max_cell_size, u32 dim, u32 h) {
+    LevelGeom g;
+    g.S = max_cell_size / (float)(1u << h);        // metadata.rs:91-93
+    g.S_child = max_cell_size / (float)(1u << (h + 1 < 32 ? h + 1 : 31));
+    g.sub = g.S / (float)dim;                      // metadata.rs:95-97
+    g.R = g.sub / 2.0f;                            // cell.rs:277
+    u32 rx = (u32)std::ceil(2.0 * dim / 1.7320508) + 3, ry = (u32)std::ceil(2.0 * dim / 1.5) + 3, rz = 2 * dim + 3;
+    g.bx = bits_for(rx + 16);
+    g.by = bits_for(ry + 16);
+    g.bz = bits_for(rz + 16);
+    g.mx = (int)(((1u << g.bx) - rx) / 2);
+    g.my = (int)(((1u << g.by) - ry) / 2);
+    g.mz = (int)(((1u << g.bz) - rz) / 2);
+    g.hexbits = g.bx + g.by + g.bz;
+    return g;
+}
+
+void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
+    CUDA_TRY(cudaSetDevice(device));
+    end_run();
+    const double t_start = now_s();
+    limit = meta->cell_point_overflow_limit;
+    dim = meta->sub_grid_dimension;
+    max_cell_size = meta->max_cell_size;
+    if (dim == 0 || !(max_cell_size > 0.0f) || !std::isfinite(max_cell_size))
+        throw Error{PCB_ERR_ARG, "bad config (sub_grid_dimension / max_cell_size)"};
+    if (batches == 0) return;                                   // nothing was ever added
+    meta->hierarchies = std::max<uint32_t>(meta->hierarchies, 1);  // converter.rs:111,120: level 0 always visited
+    if (n_in == 0) return;
+    const u32 n0 = (u32)n_in;
+    const float S0 = max_cell_size;
+
+    // ---- stage 0a: bounding box + validation
+    Scratch init;
+    memset(&init, 0, sizeof init);
+    for (int a = 0; a < 3; a++) { init.bbox[a] = INT_MAX; init.bbox[3 + a] = INT_MIN; }
+    CUDA_TRY(cudaMemcpyAsync(d_scr, &init, sizeof init, cudaMemcpyHostToDevice, st));
+    const int grid_big = 148 * 8;
+    pb();
+    k_bbox_check<<<grid_big, 256, 0, st>>>(d_in, n0, S0, d_scr->bbox, &d_scr->err);
+    pe("bbox_check", 1, n0, 16ull * n0);
+    fetch_scratch();
+    check_err();
+    float lo[3], hi[3];
+    for (int a = 0; a < 3; a++) { lo[a] = ord2f_host(h_scr->bbox[a]); hi[a] = ord2f_host(h_scr->bbox[3 + a]); }
+    if (meta->number_of_points == 0) {              // converter.rs:98-99: first points REPLACE the box
+        for (int a = 0; a < 3; a++) { meta->bbox_min[a] = lo[a]; meta->bbox_max[a] = hi[a]; }
+    } else {                                        // converter.rs:100-102
+        for (int a = 0; a < 3; a++) {
+            meta->bbox_min[a] = std::fmin(meta->bbox_min[a], lo[a]);
+            meta->bbox_max[a] = std::fmax(meta->bbox_max[a], hi[a]);
+        }
+    }
+    meta->number_of_points += n_in;                 // converter.rs:108
+
+    // ---- stage 0b-d: level-0 arrivals in (cell, input index) order
+    L0Box box;
+    int o3[3];
+    u32 d3[3];
+    for (int a = 0; a < 3; a++) {
+        o3[a] = (int)std::floor(lo[a] / S0);
+        d3[a] = (u32)((int)std::floor(hi[a] / S0) - o3[a] + 1);
+    }
+    box.ox = o3[0]; box.oy = o3[1]; box.oz = o3[2];
+    box.nx = d3[0]; box.ny = d3[1]; box.nz = d3[2];
+    u64 *kA = dalloc<u64>(n0), *vA = dalloc<u64>(n0), *kB = dalloc<u64>(n0), *vB = dalloc<u64>(n0);
+    RadixTemp rt;
+    rt.tile_hist = dalloc<u32>(RadixTemp::hist_words(n0));
+    const u64 scan_bytes = 32ull * (256ull * div_up(n0, RADIX_TILE) / 2048 + n0 / 2048 + 8);
+    unsigned char* scan_tmp = dalloc<unsigned char>(scan_bytes);
+    rt.scan_agg = (u32*)scan_tmp;
+    pb();
+    k_l0_key<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, kA, vA, &d_scr->diffmask);
+    pe("l0_key", 1, n0, 32ull * n0);
+    fetch_scratch();
+    int passes = 0;
+    u64 l0 = launches;
+    pb();
+    int cur = radix_sort_pairs(kA, vA, kB, vB, n0, h_scr->diffmask, rt, st, &launches, &passes);
+    { u64 k = launches - l0; launches = l0; pe("radix_sort", k, (u64)n0 * passes, 40ull * n0 * passes); }
+    u64* ks = cur ? kB : kA;
+    u64* vs = cur ? vB : vA;
+    u64 vol = (u64)box.nx * box.ny * box.nz;
+    u32 ncell_ub = (u32)std::min<u64>(n0, vol);
+    u32* cell_start = dalloc<u32>((u64)ncell_ub + 1);
+    int* cell_idx = dalloc<int>(3ull * ncell_ub);
+    L0HeadOp hop{ks, n0, box, cell_start, cell_idx, &d_scr->ncell};
+    pb();
+    int nl = device_scan(hop, n0, (u32*)scan_tmp, st);
+    pe("l0_heads", nl, n0, 16ull * n0);
+    BatchSeg* d_segs = dalloc<BatchSeg>(segs.size());
+    CUDA_TRY(cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(BatchSeg), cudaMemcpyHostToDevice, st));
+    PcbPoint* pts = dalloc<PcbPoint>(n0);
+    u32* bat = dalloc<u32>(n0);
+    pb();
+    k_l0_gather<<<div_up(n0, 256), 256, 0, st>>>(d_in, vs, n0, d_segs, (u32)segs.size(), pts, bat);
+    pe("l0_gather", 1, n0, 44ull * n0);
+    fetch_scratch();
+    u32 ncell = h_scr->ncell;
+    dfree(kA); dfree(vA); dfree(kB); dfree(vB); dfree(rt.tile_hist); dfree(scan_tmp); dfree(d_segs);
+
+
+    // ---- levels
+    u32 n = n0, h = 0;
+    while (n) {
+        if (h >= 32) throw Error{PCB_ERR_RANGE, "octree deeper than 31 levels (reference overflows 2u32.pow, metadata.rs:92)"};
+        meta->hierarchies = std::max<uint32_t>(meta->hierarchies, h + 1);  // converter.rs:141-144
+        build_level(h, pts, bat, cell_start, cell_idx, n, ncell, meta, existing);
+        h++;
+    }
+    levels_built = h;
+    dfree(pts); dfree(bat); dfree(cell_start); dfree(cell_idx);
+    CUDA_TRY(cudaStreamSynchronize(st));
+    build_s += now_s() - t_start;
+    double t1 = now_s();
+    CUDA_TRY(cudaStreamSynchronize(copy_st));
+    d2h_s += now_s() - t1;
+    for (auto& l : levels)
+        if (l.h_image && l.d_image) {
+            CUDA_TRY(cudaFree(l.d_image));
+            l.d_image = nullptr;
+        }
+    prof_collect();
+}
+
+// One level of the hierarchy for ALL batches (converter.rs:114-139).  In: arrivals sorted by (cell, tau).
+// Out: this level's node images + the next level's arrivals (same invariant).
+void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start, int*& cell_idx, u32& n, u32& ncell,
+                              Metadata* meta, NodeSource* existing) {
+    (void)meta;
+    const LevelGeom g = make_geom(max_cell_size, dim, h);
+    if ((u64)ncell >= (1ull << (62 - g.hexbits))) throw Error{PCB_ERR_RANGE, "too many cells on one level"};
+    const u32 n_new = n;  // arrivals proper (incumbents of merge mode are added below)
+    arrivals += n_new;
+
+    // ---- merge mode: read the node files of the cells that receive arrivals (converter.rs:160-207)
+    unsigned char* ex_state = nullptr;
+    u32 *ex_m0 = nullptr, *ex_bucket = nullptr, *ex_rank = nullptr;
+    PcbPoint* ex_pts = nullptr;
+    u32 nex = 0;
+    if (existing) {
+        std::vector<int> hidx(3ull * ncell);
+        CUDA_TRY(cudaMemcpyAsync(hidx.data(), cell_idx, hidx.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        std::vector<u32> inc_start(ncell + 1, 0);
+        std::vector<pcb_point> inc_pts, exl_pts;
+        std::vector<unsigned char> hstate(8ull * ncell, PCB_EX_ABSENT);
+        std::vector<u32> hm0(8ull * ncell, 0), hbucket, hrank;
+        bool any = false;
+        ExistingNode en;
+        for (u32 c = 0; c < ncell; c++) {
+            inc_start[c] = (u32)inc_pts.size();
+            en.grid.clear();
+            en.entries.clear();
+            if (!existing->load(h, &hidx[3 * c], &en)) continue;
+            any = true;
+            inc_pts.insert(inc_pts.end(), en.grid.begin(), en.grid.end());
+            for (auto& e : en.entries) {
+                int dx = e.child[0] - 2 * hidx[3 * c], dy = e.child[1] - 2 * hidx[3 * c + 1],
+                    dz = e.child[2] - 2 * hidx[3 * c + 2];
+                if ((unsigned)dx > 1u || (unsigned)dy > 1u || (unsigned)dz > 1u)
+                    throw Error{PCB_ERR_FORMAT, "existing node has an overflow entry outside its 8 children"};
+                u32 k = 8 * c + (u32)(dx * 4 + dy * 2 + dz);
+                if (e.none) {
+                    hstate[k] = PCB_EX_NONE;
+                } else {
+                    hstate[k] = PCB_EX_SOME;
+                    hm0[k] = (u32)e.list.size();
+                    for (u32 r = 0; r < e.list.size(); r++) { hbucket.push_back(k); hrank.push_back(r); }
+                    exl_pts.insert(exl_pts.end(), e.list.begin(), e.list.end());
+                }
+            }
+        }
+        inc_start[ncell] = (u32)inc_pts.size();
+        if (any) {
+            const u32 ninc = (u32)inc_pts.size();
+            if ((u64)n + ninc >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "level too large for one device"};
+            ex_state = dalloc<unsigned char>(hstate.size());
+            ex_m0 = dalloc<u32>(hm0.size());
+            CUDA_TRY(cudaMemcpyAsync(ex_state, hstate.data(), hstate.size(), cudaMemcpyHostToDevice, st));
+            CUDA_TRY(cudaMemcpyAsync(ex_m0, hm0.data(), hm0.size() * 4, cudaMemcpyHostToDevice, st));
+            nex = (u32)exl_pts.size();
+            if (nex) {
+                ex_pts = dalloc<PcbPoint>(nex);
+                ex_bucket = dalloc<u32>(nex);
+                ex_rank = dalloc<u32>(nex);
+                CUDA_TRY(cudaMemcpyAsync(ex_pts, exl_pts.data(), 16ull * nex, cudaMemcpyHostToDevice, st));
+                CUDA_TRY(cudaMemcpyAsync(ex_bucket, hbucket.data(), 4ull * nex, cudaMemcpyHostToDevice, st));
+                CUDA_TRY(cudaMemcpyAsync(ex_rank, hrank.data(), 4ull * nex, cudaMemcpyHostToDevice, st));
+            }
+            if (ninc) {
+                u32* d_inc_start = dalloc<u32>(ncell + 1);
+                PcbPoint* d_inc = dalloc<PcbPoint>(ninc);
+                CUDA_TRY(cudaMemcpyAsync(d_inc_start, inc_start.data(), 4ull * (ncell + 1), cudaMemcpyHostToDevice, st));
+                CUDA_TRY(cudaMemcpyAsync(d_inc, inc_pts.data(), 16ull * ninc, cudaMemcpyHostToDevice, st));
+                PcbPoint* mp = dalloc<PcbPoint>((u64)n + ninc);
+                u32* mb = dalloc<u32>((u64)n + ninc);
+                pb();
+                k_merge_arrivals<<<div_up(n, 256), 256, 0, st>>>(pts, bat, n, cell_start, ncell, d_inc_start, mp, mb);
+                k_merge_incumbents<<<div_up(ninc, 256), 256, 0, st>>>(d_inc, ninc, d_inc_start, ncell, cell_start, mp, mb);
+                k_merge_starts<<<div_up(ncell + 1, 256), 256, 0, st>>>(cell_start, d_inc_start, ncell);
+                pe("merge_incumbents", 3, (u64)n + ninc, 40ull * ((u64)n + ninc));
+                CUDA_TRY(cudaStreamSynchronize(st));  // host vectors above must outlive the copies
+                dfree(pts); dfree(bat); dfree(d_inc_start); dfree(d_inc);
+                pts = mp; bat = mb;
+                n += ninc;
+            } else {
+                CUDA_TRY(cudaStreamSynchronize(st));
+            }
+        }
+    }
+
+    // ---- stages 1-2: hex keys
+    int* cellbase = dalloc<int>(3ull * ncell);
+    u64 *kA = dalloc<u64>(n), *vA = dalloc<u64>(n), *kB = dalloc<u64>(n), *vB = dalloc<u64>(n);
+    u32* cell_of = dalloc<u32>(n);
+    CUDA_TRY(cudaMemsetAsync(&d_scr->diffmask, 0, sizeof(u64), st));
+    pb();
+    k_cellbase<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, ncell, g, cellbase);
+    k_hexkey<<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, cellbase, g, kA, vA,
+                                                                     cell_of, &d_scr->diffmask, &d_scr->err);
+    pe("hexkey", 2, n, 36ull * n);
+    fetch_scratch();
+    check_err();
+
+    // ---- stage 3: stable sort by (cell, Z, Y, X)
+    RadixTemp rt;
+    rt.tile_hist = dalloc<u32>(RadixTemp::hist_words(n));
+    const u64 scan_bytes = 32ull * (256ull * div_up(n, RADIX_TILE) / 2048 + n / 2048 + (u64)ncell / 2048 + 8);
+    unsigned char* scan_tmp = dalloc<unsigned char>(scan_bytes);
+    rt.scan_agg = (u32*)scan_tmp;
+    int passes = 0;
+    u64 l0 = launches;
+    pb();
+    int cur = radix_sort_pairs(kA, vA, kB, vB, n, h_scr->diffmask, rt, st, &launches, &passes);
+    { u64 k = launches - l0; launches = l0; pe("radix_sort", k, (u64)n * passes, 40ull * n * passes); }
+    u64* ks = cur ? kB : kA;
+    u64* vs = cur ? vB : vA;
+
+    // ---- stage 4: contest
+    u32* emitted = dalloc<u32>(n);
+    u32* win_src = dalloc<u32>(n);
+    u32* win_end = dalloc<u32>(ncell);
+    ContestOp cop{ks, vs, n, g.hexbits, emitted, win_src, win_end, &d_scr->nwin};
+    pb();
+    int nl = device_scan(cop, n, (ContestState*)scan_tmp, st);
+    pe("contest", nl, n, 2 * 16ull * n + 8ull * n);
+
+    // ---- stages 5-6: octants + segmented 8-way split of the losers
+    unsigned char* oct8 = dalloc<unsigned char>(n);
+    u32* rank = dalloc<u32>(n);
+    u32* cellP = dalloc<u32>(8ull * (ncell + 1));
+    u32* bstart = dalloc<u32>(8ull * ncell + 1);
+    u32 *los_src = dalloc<u32>(n), *los_bat = dalloc<u32>(n), *los_bucket = dalloc<u32>(n);
+    pb();
+    k_octant<<<div_up(n, 256), 256, 0, st>>>(emitted, pts, cell_of, cell_idx, n, g.S_child, oct8, &d_scr->err);
+    pe("octant", 1, n, 25ull * n);
+    OctScanOp oop{oct8, cell_of, ncell, rank, cellP};
+    pb();
+    nl = device_scan<OctScanOp, 256, 16>(oop, n, (Oct8*)scan_tmp, st);
+    pe("oct_scan", nl, n, 14ull * n);
+    pb();
+    k_bucket_start<<<div_up(ncell, 256), 256, 0, st>>>(cellP, ncell, bstart);
+    k_loser_scatter<<<div_up(n, 256), 256, 0, st>>>(oct8, rank, cell_of, cellP, bstart, emitted, bat, n, los_src,
+                                                    los_bat, los_bucket);
+    pe("loser_scatter", 2, n, 29ull * n);
+
+    // ---- stage 7: flush decisions + offsets
+    unsigned char* bflag = dalloc<unsigned char>(8ull * ncell);
+    u32 *bfl = dalloc<u32>(8ull * ncell), *bcount = dalloc<u32>(8ull * ncell), *bdst = dalloc<u32>(8ull * ncell);
+    u64* boff = dalloc<u64>(8ull * ncell);
+    u32 *cell_deliver = dalloc<u32>(ncell), *cell_children = dalloc<u32>(ncell);
+    u32 *cell_dbase = dalloc<u32>(ncell), *cell_cbase = dalloc<u32>(ncell);
+    u64 *cell_bytes = dalloc<u64>(ncell), *node_off = dalloc<u64>(ncell);
+    pb();
+    k_bucket_decide<<<div_up(ncell, 128), 128, 0, st>>>(bstart, los_bat, win_end, ncell, limit, ex_state, ex_m0, bflag,
+                                                        bfl, bcount, cell_deliver, cell_children, cell_bytes);
+    CellScanOp sop{cell_deliver, cell_children, cell_bytes, cell_dbase, cell_cbase, node_off, &d_scr->totals};
+    nl = device_scan(sop, ncell, (CellScanState*)scan_tmp, st);
+    pe("bucket_decide", 1 + nl, ncell, 200ull * ncell);
+    // node table for the host
+    std::vector<int> hidx(3ull * ncell);
+    std::vector<u64> hoff(ncell), hbytes(ncell);
+    CUDA_TRY(cudaMemcpyAsync(hidx.data(), cell_idx, hidx.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(hoff.data(), node_off, 8ull * ncell, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaMemcpyAsync(hbytes.data(), cell_bytes, 8ull * ncell, cudaMemcpyDeviceToHost, st));
+    fetch_scratch();
+    check_err();
+    const LevelTotals tot = h_scr->totals;
+    const u32 nwin = h_scr->nwin, nlos = n - nwin;
+
+    // ---- stage 8: node images + next level's arrivals
+    LevelImage img;
+    img.hierarchy = h;
+    img.bytes = tot.image_bytes;
+    CUDA_TRY(cudaMalloc(&img.d_image, std::max<u64>(img.bytes, 16)));
+    PcbPoint* next_pts = dalloc<PcbPoint>(tot.n_next);
+    u32* next_bat = dalloc<u32>(tot.n_next);
+    u32* next_cell_start = dalloc<u32>((u64)tot.ncell_next + 1);
+    int* next_cell_idx = dalloc<int>(3ull * tot.ncell_next);
+    pb();
+    k_cell_emit<<<div_up(ncell, 128), 128, 0, st>>>(cell_idx, ncell, h, g, win_end, bflag, bcount, cell_dbase, cell_cbase,
+                                                    node_off, cell_bytes, img.d_image, bdst, boff, next_cell_start,
+                                                    next_cell_idx, tot.n_next, tot.ncell_next);
+    pe("cell_emit", 1, ncell, 300ull * ncell);
+    pb();
+    if (nlos)
+        k_loser_emit<<<div_up(nlos, 256), 256, 0, st>>>(los_src, los_bat, los_bucket, nlos, pts, bstart, bflag, bfl, bcount,
+                                                        bdst, boff, next_pts, next_bat, img.d_image);
+    pe("loser_emit", nlos ? 1 : 0, nlos, 48ull * nlos);
+    pb();
+    k_winner_emit<<<div_up(nwin, 256), 256, 0, st>>>(win_src, nwin, win_end, cell_of, pts, node_off, img.d_image);
+    pe("winner_emit", 1, nwin, 40ull * nwin);
+    if (nex) {
+        pb();
+        k_exlist_emit<<<div_up(nex, 256), 256, 0, st>>>(ex_pts, nex, ex_bucket, ex_rank, bflag, bfl, bdst, boff, next_pts,
+                                                        next_bat, img.d_image);
+        pe("exlist_emit", 1, nex, 44ull * nex);
+    }
+
+    // node records (host) and image download
+    const u32 slot = (u32)levels.size();
+    for (u32 c = 0; c < ncell; c++) {
+        NodeRec r;
+        r.hierarchy = h;
+        r.index[0] = hidx[3 * c]; r.index[1] = hidx[3 * c + 1]; r.index[2] = hidx[3 * c + 2];
+        r.offset = hoff[c];
+        r.size = hbytes[c];
+        r.level_slot = slot;
+        nodes.push_back(r);
+    }
+    if (!(flags & PCB_FLAG_DEVICE_ONLY)) {
+        CUDA_TRY(cudaHostAlloc(&img.h_image, std::max<u64>(img.bytes, 16), cudaHostAllocDefault));
+        cudaEvent_t ev;
+        CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventRecord(ev, st));
+        CUDA_TRY(cudaStreamWaitEvent(copy_st, ev, 0));
+        CUDA_TRY(cudaMemcpyAsync(img.h_image, img.d_image, img.bytes, cudaMemcpyDeviceToHost, copy_st));
+        CUDA_TRY(cudaEventDestroy(ev));
+    }
+    levels.push_back(img);
+
+    // ---- hand over to the next level
+    dfree(cellbase); dfree(kA); dfree(vA); dfree(kB); dfree(vB); dfree(cell_of); dfree(rt.tile_hist); dfree(scan_tmp);
+    dfree(emitted); dfree(win_src); dfree(win_end); dfree(oct8); dfree(rank); dfree(cellP); dfree(bstart);
+    dfree(los_src); dfree(los_bat); dfree(los_bucket); dfree(bflag); dfree(bfl); dfree(bcount); dfree(bdst); dfree(boff);
+    dfree(cell_deliver); dfree(cell_children); dfree(cell_dbase); dfree(cell_cbase); dfree(cell_bytes); dfree(node_off);
+    dfree(ex_state); dfree(ex_m0); dfree(ex_pts); dfree(ex_bucket); dfree(ex_rank);
+    dfree(pts); dfree(bat); dfree(cell_start); dfree(cell_idx);
+    pts = next_pts; bat = next_bat; cell_start = next_cell_start; cell_idx = next_cell_idx;
+    n = tot.n_next;
+    ncell = tot.ncell_next;
+}
+
+// ---- public wrappers: every CUDA failure becomes a pcb::Error ------------------------------------------
+template <class F>
+static auto guarded(F&& f) -> decltype(f()) {
+    try {
+        return f();
+    } catch (const PcbCudaError& e) {
+        char buf[512];
+        snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d: %s", (int)e.code, cudaGetErrorString(e.code), e.file,
+                 e.line, e.expr);
+        throw Error{PCB_ERR_CUDA, buf};
+    }
+}
+
+Builder::Builder(int device, uint32_t flags) : impl_(nullptr) {
+    guarded([&] { impl_ = new BuilderImpl(device, flags); return 0; });
+}
+Builder::~Builder() { delete impl_; }
+void Builder::set_config(uint32_t limit, uint32_t dim, float max_cell_size) {
+    impl_->limit = limit;
+    impl_->dim = dim;
+    impl_->max_cell_size = max_cell_size;
+}
+void Builder::reserve(uint64_t n) {
+    guarded([&] { impl_->reserve(n); return 0; });
+}
+void Builder::begin_file() { impl_->begin_file(); }
+void Builder::add_points(const pcb_point* pts, uint64_t n, uint32_t batch_size, bool device_ptr) {
+    guarded([&] { impl_->add(pts, n, batch_size ? batch_size : 10000u, device_ptr, false); return 0; });
+}
+void Builder::add_points_one_batch(const pcb_point* pts, uint64_t n, bool device_ptr) {
+    guarded([&] { impl_->add(pts, n, 0, device_ptr, true); return 0; });
+}
+void Builder::build(Metadata* meta, NodeSource* existing) {
+    guarded([&] { impl_->build(meta, existing); return 0; });
+}
+const std::vector<NodeRec>& Builder::nodes() const { return impl_->nodes; }
+const std::vector<LevelImage>& Builder::levels() const { return impl_->levels; }
+std::vector<KernelStat> Builder::kernel_stats() const { return impl_->stats; }
+uint64_t Builder::points_added() const { return impl_->n_in; }
+uint64_t Builder::arrivals() const { return impl_->arrivals; }
+uint64_t Builder::launches() const { return impl_->launches; }
+uint32_t Builder::levels_built() const { return impl_->levels_built; }
+double Builder::h2d_seconds() const { return impl_->h2d_s; }
+double Builder::build_seconds() const { return impl_->build_s; }
+double Builder::d2h_seconds() const { return impl_->d2h_s; }
+
+int device_count() {
+    int c = 0;
+    if (cudaGetDeviceCount(&c) != cudaSuccess) return 0;
+    return c;
+}
+
+}  // namespace pcb

@@ -1,0 +1,209 @@
+"""ctypes binding of libpcb.so (include/pcb.h) — the host-side mirror of the reference's converter API.
+
+Reference interface mirrored (paths relative to /root/reference):
+  Converter::new / add_points_batch / Drop   point-converter/src/converter.rs:78-112, 218-246
+  convert_from_paths batch loop              point-converter/src/lib.rs:11-60
+
+There is NO CPU fallback: if the CUDA library is missing or no device is present, construction fails.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+from typing import Dict, Optional
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "libpcb.so"
+
+POINT_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("rgba", "u1", (4,))])
+
+FLAG_NO_FILES = 1
+FLAG_DEVICE_ONLY = 2
+FLAG_PROFILE = 4
+
+EXPORTS = [
+    "pcb_open", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
+    "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_last_error", "pcb_node_count", "pcb_node_get",
+    "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
+]
+
+
+class PcbOptions(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("batch_size", C.c_uint32),
+                ("flags", C.c_uint32), ("cell_point_overflow_limit", C.c_uint32),
+                ("sub_grid_dimension", C.c_uint32), ("max_cell_size", C.c_float), ("reserved", C.c_uint32)]
+
+
+class PcbStats(C.Structure):
+    _fields_ = [("number_of_points", C.c_uint64), ("points_added", C.c_uint64), ("arrivals", C.c_uint64),
+                ("nodes_written", C.c_uint64), ("node_bytes", C.c_uint64), ("hierarchies", C.c_uint32),
+                ("levels_built", C.c_uint32), ("gpu_launches", C.c_uint64), ("h2d_seconds", C.c_double),
+                ("build_seconds", C.c_double), ("d2h_seconds", C.c_double), ("write_seconds", C.c_double),
+                ("total_seconds", C.c_double), ("bbox_min", C.c_float * 3), ("bbox_max", C.c_float * 3)]
+
+
+class PcbKernelStat(C.Structure):
+    _fields_ = [("name", C.c_char * 32), ("launches", C.c_uint64), ("units", C.c_uint64), ("bytes", C.c_uint64),
+                ("ms", C.c_double)]
+
+
+class PcbNodeInfo(C.Structure):
+    _fields_ = [("hierarchy", C.c_uint32), ("index", C.c_int32 * 3), ("offset", C.c_uint64), ("size", C.c_uint64)]
+
+
+class PcbError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"pcb error {status}: {message}")
+        self.status = status
+
+
+_lib = None
+
+
+def load_library():
+    """Loads libpcb.so; raises if it has not been built (no fallback of any kind)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise RuntimeError(f"{LIB_PATH} is missing: build it with __graft_entry__.build() "
+                           f"(make -C point-cloud_b200/csrc); there is no CPU fallback")
+    L = C.CDLL(str(LIB_PATH))
+    vp = C.c_void_p
+    L.pcb_open.argtypes = [C.c_char_p, C.POINTER(PcbOptions), C.POINTER(vp)]
+    L.pcb_begin_file.argtypes = [vp]
+    L.pcb_add_points.argtypes = [vp, vp, C.c_uint64]
+    L.pcb_add_points_batch.argtypes = [vp, vp, C.c_uint64]
+    L.pcb_add_points_device.argtypes = [vp, vp, C.c_uint64]
+    L.pcb_reserve.argtypes = [vp, C.c_uint64]
+    L.pcb_finish.argtypes = [vp, C.POINTER(PcbStats)]
+    L.pcb_close.argtypes = [vp]
+    L.pcb_close.restype = None
+    L.pcb_last_error.argtypes = [vp]
+    L.pcb_last_error.restype = C.c_char_p
+    L.pcb_node_count.argtypes = [vp]
+    L.pcb_node_count.restype = C.c_uint64
+    L.pcb_node_get.argtypes = [vp, C.c_uint64, C.POINTER(PcbNodeInfo), C.POINTER(vp)]
+    L.pcb_metadata_json.argtypes = [vp, C.c_char_p, C.c_uint64]
+    L.pcb_kernel_stat_count.argtypes = [vp]
+    L.pcb_kernel_stat_get.argtypes = [vp, C.c_int, C.POINTER(PcbKernelStat)]
+    L.pcb_version.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def _as_records(arr) -> np.ndarray:
+    a = np.ascontiguousarray(arr)
+    if a.dtype != POINT_DTYPE:
+        a = a.view(np.uint8).reshape(-1, 16).view(POINT_DTYPE).reshape(-1)
+    return a
+
+
+class Converter:
+    """Mirror of the reference's `Converter` (converter.rs:72-246) on the GPU library.
+
+    out_dir=None keeps every node image in host memory (`nodes()`), nothing touches the file system.
+    `config=(limit, sub_grid_dimension, max_cell_size)` seeds a FRESH output only, the way a hand-written
+    metadata.json would; an existing metadata.json always wins (lib.rs:86-101)."""
+
+    def __init__(self, out_dir: Optional[str] = None, *, device: int = 0, batch_size: int = 0, flags: int = 0,
+                 config=None):
+        self._L = load_library()
+        opt = PcbOptions()
+        opt.struct_size = C.sizeof(PcbOptions)
+        opt.device = device
+        opt.batch_size = batch_size
+        opt.flags = flags
+        if config is not None:
+            opt.cell_point_overflow_limit, opt.sub_grid_dimension, opt.max_cell_size = (
+                int(config[0]), int(config[1]), float(config[2]))
+        self._h = C.c_void_p()
+        rc = self._L.pcb_open(str(out_dir).encode() if out_dir else None, C.byref(opt), C.byref(self._h))
+        if rc != 0:
+            raise PcbError(rc, (self._L.pcb_last_error(None) or b"").decode())
+        self.stats: Optional[PcbStats] = None
+
+    def _check(self, rc):
+        if rc != 0:
+            raise PcbError(rc, (self._L.pcb_last_error(self._h) or b"").decode())
+
+    def reserve(self, n: int):
+        self._check(self._L.pcb_reserve(self._h, n))
+
+    def begin_file(self):
+        self._check(self._L.pcb_begin_file(self._h))
+
+    def add_points(self, arr):
+        """Points of the current input file; cut into batches of batch_size like lib.rs:31-35."""
+        a = _as_records(arr)
+        self._check(self._L.pcb_add_points(self._h, a.ctypes.data if len(a) else None, len(a)))
+
+    def add_points_batch(self, arr):
+        """Exactly one batch — Converter::add_points_batch (converter.rs:106-112)."""
+        a = _as_records(arr)
+        self._check(self._L.pcb_add_points_batch(self._h, a.ctypes.data if len(a) else None, len(a)))
+
+    def add_points_device(self, device_ptr: int, n: int):
+        self._check(self._L.pcb_add_points_device(self._h, C.c_void_p(device_ptr), n))
+
+    def finish(self) -> PcbStats:
+        """Drop for Converter (converter.rs:241-246): build, write node files + metadata.json."""
+        st = PcbStats()
+        self._check(self._L.pcb_finish(self._h, C.byref(st)))
+        self.stats = st
+        return st
+
+    def metadata_json(self) -> str:
+        n = self._L.pcb_metadata_json(self._h, None, 0)
+        buf = C.create_string_buffer(n + 1)
+        self._L.pcb_metadata_json(self._h, buf, n + 1)
+        return buf.value.decode()
+
+    def nodes(self) -> Dict[str, bytes]:
+        """{relative path: node file bytes} of every node this run produced (host copies)."""
+        out = {}
+        info = PcbNodeInfo()
+        img = C.c_void_p()
+        for i in range(self._L.pcb_node_count(self._h)):
+            self._check(self._L.pcb_node_get(self._h, i, C.byref(info), C.byref(img)))
+            path = "h_%d/c_%d_%d_%d.bin" % (info.hierarchy, info.index[0], info.index[1], info.index[2])
+            out[path] = C.string_at(img.value, info.size) if img.value else b""
+        return out
+
+    def kernel_stats(self):
+        out = []
+        ks = PcbKernelStat()
+        for i in range(self._L.pcb_kernel_stat_count(self._h)):
+            self._L.pcb_kernel_stat_get(self._h, i, C.byref(ks))
+            out.append(dict(name=ks.name.decode(), launches=ks.launches, units=ks.units, bytes=ks.bytes, ms=ks.ms))
+        return out
+
+    def close(self):
+        if self._h:
+            self._L.pcb_close(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def convert(files, out_dir=None, *, config=None, batch_size=0, device=0, flags=0):
+    """convert_from_paths (lib.rs:11-60) over in-memory 'files' (arrays of 16-byte point records).
+    Returns (nodes, metadata_json, stats, kernel_stats)."""
+    with Converter(out_dir, device=device, batch_size=batch_size, flags=flags, config=config) as cv:
+        for f in files:
+            cv.begin_file()
+            cv.add_points(f)
+        st = cv.finish()
+        return cv.nodes(), cv.metadata_json(), st, cv.kernel_stats()

@@ -235,3 +235,16 @@ def sort_records(rec: np.ndarray) -> np.ndarray:
     if len(rec) == 0:
         return rec
     return rec[np.lexsort(rec.T[::-1])]
+
+
+def load_pcb():
+    """Import point-cloud_b200/pcb.py (the directory name is not a Python identifier)."""
+    import importlib.util
+    name = "point_cloud_b200_pcb"
+    if name in sys.modules:
+        return sys.modules[name]
+    spec = importlib.util.spec_from_file_location(name, ROOT / "point-cloud_b200" / "pcb.py")
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
