@@ -23,7 +23,8 @@ std::string format_f32(float v) {
     float a = std::fabs(v);
     if (a == 0.0f) return out + "0.0";
     char sci[48];
-    auto r = std::to_chars(sci, sci + sizeof sci, a, std::chars_format::scientific);
+    auto r = std::to_chars(sci, sci + sizeof sci - 1, a, std::chars_format::scientific);
+    *r.ptr = 0;
     // sci = d[.ddd]e[+-]XX
     std::string digits;
     const char* p = sci;
