@@ -1,0 +1,283 @@
+#!/usr/bin/env python
+"""bench.py — octree/LOD build throughput (BASELINE.json metric) on B200.
+
+A step = ONE full conversion (all levels) of the synthetic cloud of the workload.
+  value  : Mpoints/s with the input resident in HBM and the node images left in HBM (device build)
+  e2e    : Mpoints/s through the C ABI with HOST buffers: pinned host points -> H2D -> build -> node
+           images D2H into host memory (no file system), wall clock
+  roofline: dominant kernel class, algorithmic bytes / CUDA-event time vs MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline: the CPU oracle (sequential port of the reference's algorithm; the reference CLI itself
+           is single-threaded and Rust cannot be built here) on a bounded, same-density sample
+`--impl reference` times that CPU oracle alone (all the threads the algorithm can use: it is parallel
+only across level-0 cells).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT / "tests"))
+sys.path.insert(0, str(ROOT / "point-cloud_b200"))
+
+METRIC = "octree_build_throughput"
+UNIT = "Mpoints/s"
+DENSITY = 6.25  # points per m^2 of the C2 terrain workload (1e8 points over 4 km x 4 km)
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_oracle_run(n_points, extent, threads, seed=2):
+    """Times the CPU oracle on a terrain tile of the workload's density.  Returns (Mpts/s, seconds)."""
+    import synth
+    from pcutil import oracle_convert
+    pts = synth.terrain(n_points, seed, "cpu", extent).numpy()
+    t0 = time.perf_counter()
+    oracle_convert([pts], dump=False, threads=threads)
+    dt = time.perf_counter() - t0
+    return n_points / dt / 1e6, dt
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            out, _ = self.proc.communicate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def run_reference(args, rank, world):
+    """CPU arm: the oracle port on the host cores.  Rank 0 only."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    # 2 x 2 level-0 cells at full density: the only parallelism the algorithm has is across level-0 cells
+    threads = min(4, cores)
+    side = 2000.0
+    n = int(DENSITY * side * side * args.cpu_scale)
+    vals = []
+    for _ in range(max(1, min(args.steps, 2))):
+        v, dt = cpu_oracle_run(n, (-1000.0, -1000.0 + side, -1000.0, -1000.0 + side), threads)
+        vals.append((v, dt))
+    v = statistics.median([x[0] for x in vals])
+    dt = statistics.median([x[1] for x in vals])
+    sample = (f"{n} points of the same terrain generator at the workload's density ({DENSITY}/m^2) over 2x2 "
+              f"level-0 cells, {threads} threads (one per level-0 cell)")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": round(v, 4), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(vals), "warmup": 0, "ms_per_step": round(dt * 1e3, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32+u64", "data": "synthetic",
+        "config": {"workload": "C2 terrain 100M (bounded CPU sample)", "sample_points": n},
+        "cpu_baseline": {"value": round(v, 4), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": round(v, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--points", type=int, default=100_000_000, help="points per GPU (C2 = 1e8)")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--cpu-scale", type=float, default=1.0, help="scales the bounded CPU sample")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import synth
+    from pcutil import load_pcb
+    pcb = load_pcb()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    n = args.points
+    # Each rank owns a disjoint block of level-0 cell columns of the terrain (the state after the
+    # level-0 exchange of SURVEY.md §8e); same density, same extent per rank => weak scaling.
+    side = (n / DENSITY) ** 0.5
+    x0 = -side / 2 + rank * side
+    pts = synth.terrain(n, 2 + rank, dev, (x0, x0 + side, -side / 2, side / 2))
+    torch.cuda.synchronize()
+    stream = torch.cuda.current_stream()
+
+    def step(profile=True):
+        flags = pcb.FLAG_DEVICE_ONLY | (pcb.FLAG_PROFILE if profile else 0)
+        cv = pcb.Converter(None, device=local_rank, flags=flags)
+        try:
+            cv.set_stream(stream.cuda_stream)
+            cv.begin_file()
+            cv.add_points_device(pts.data_ptr(), n)
+            st = cv.finish()
+            return st, cv.kernel_stats()
+        finally:
+            cv.close()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches, kstats, last = 0, {}, None
+    ev0.record(stream)
+    for _ in range(args.steps):
+        last, ks = step()
+        launches += last.gpu_launches
+        for k in ks:
+            d = kstats.setdefault(k["name"], dict(launches=0, units=0, bytes=0, ms=0.0))
+            for f in ("launches", "units", "bytes", "ms"):
+                d[f] += k[f]
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = n * world / (ms_per_step * 1e-3) / 1e6
+
+    # ---- e2e: host buffers through the C ABI (H2D + build + D2H of every node image)
+    e2e = None
+    if args.e2e_steps > 0:
+        host = torch.empty((n, 16), dtype=torch.uint8, pin_memory=True)
+        host.copy_(pts)
+        torch.cuda.synchronize()
+        hnp = host.numpy()
+        times, d2h = [], 0
+
+        def e2e_step():
+            cv = pcb.Converter(None, device=local_rank, flags=pcb.FLAG_NO_FILES)
+            try:
+                cv.reserve(n)
+                cv.begin_file()
+                cv.add_points(hnp)
+                st = cv.finish()
+                return st
+            finally:
+                cv.close()
+
+        e2e_step()  # warm-up (pinned staging cache, memory pool)
+        barrier()
+        for _ in range(args.e2e_steps):
+            t0 = time.perf_counter()
+            st = e2e_step()
+            torch.cuda.synchronize()
+            times.append(time.perf_counter() - t0)
+            d2h = int(st.node_bytes)
+        t = statistics.median(times)
+        if world > 1:
+            tt = torch.tensor([t], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t = float(tt.item())
+        e2e = {"value": round(n * world / t / 1e6, 3), "unit": UNIT, "h2d_bytes_per_step": 16 * n,
+               "d2h_bytes_per_step": d2h, "ms_per_step": round(t * 1e3, 2)}
+        del host
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        top = max(kstats.items(), key=lambda kv: kv[1]["ms"]) if kstats else None
+        roofline = None
+        if top and top[1]["ms"] > 0:
+            name, d = top
+            achieved = d["bytes"] / (d["ms"] * 1e-3) / 1e9
+            traffic = None
+            tp = ROOT / "profiles" / "traffic.json"
+            if tp.exists():
+                traffic = json.loads(tp.read_text()).get(name)
+            roofline = {"bound": "hbm", "kernel": name, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                        "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                        "launches": d["launches"], "avg_ms": round(d["ms"] / max(1, d["launches"]), 4),
+                        "step_share": round(d["ms"] / ms, 4),
+                        "kernels": {k: {"ms_per_step": round(v["ms"] / args.steps, 3),
+                                        "GBps": round(v["bytes"] / max(v["ms"], 1e-9) / 1e6, 1)} for k, v in
+                                    sorted(kstats.items(), key=lambda kv: -kv[1]["ms"])}}
+        cpu = None
+        if not args.no_cpu:
+            ncpu = int(DENSITY * 1000.0 * 1000.0 * args.cpu_scale)
+            v, dt = cpu_oracle_run(ncpu, (0.0, 1000.0, 0.0, 1000.0), 1)
+            cpu = {"value": round(v, 4), "unit": UNIT, "cores": 1, "kind": "port", "seconds": round(dt, 2),
+                   "sample": f"{ncpu} points: one level-0 cell (1 km^2) of the same terrain generator at the "
+                             f"workload's density ({DENSITY}/m^2); sequential oracle = the reference CLI's own "
+                             f"concurrency (single-threaded)"}
+        out = {"metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+               "warmup": args.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True,
+               "scaling": "weak", "vs_baseline": None, "dtype": "f32+u64", "data": "synthetic",
+               "config": {"workload": f"C2 terrain, {n} points per GPU, 2.5-D heightfield + noise, default config "
+                                      f"(5000/96/1000.0), batch 10000", "points_per_gpu": n,
+                          "l2": "inputs (1.6 GB/step) larger than L2, no explicit flush",
+                          "levels": int(last.levels_built), "arrivals_per_point": round(last.arrivals / n, 3),
+                          "nodes": int(last.nodes_written), "sharding": "disjoint level-0 cell blocks per rank"},
+               "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+               "clocks": clocks}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

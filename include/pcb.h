@@ -108,10 +108,16 @@ int pcb_add_points(pcb_handle* h, const pcb_point* pts, uint64_t n);
 int pcb_add_points_batch(pcb_handle* h, const pcb_point* pts, uint64_t n);
 /* Optional capacity hint (total points this handle will receive). */
 int pcb_reserve(pcb_handle* h, uint64_t n);
-/* Same, but `d_pts` is a device pointer on the handle's device (resident-input path). */
+/* Run all device work of this handle on the caller's CUDA stream (a cudaStream_t), e.g. so that the
+   caller's CUDA events bracket it.  Call right after pcb_open. */
+int pcb_set_stream(pcb_handle* h, void* cuda_stream);
+/* Same, but `d_pts` is a device pointer on the handle's device (resident-input path).  When it is the first
+   add on the handle the buffer is aliased, not copied: keep it valid and unchanged until pcb_finish returns. */
 int pcb_add_points_device(pcb_handle* h, const pcb_point* d_pts, uint64_t n);
 int pcb_finish(pcb_handle* h, pcb_stats* stats);
 void pcb_close(pcb_handle* h);
+/* Node images are staged in pinned host buffers that are recycled across handles; this frees the idle ones. */
+void pcb_trim_host_cache(void);
 const char* pcb_last_error(const pcb_handle* h);
 
 /* Results in memory (after pcb_finish). */

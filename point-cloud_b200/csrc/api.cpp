@@ -22,6 +22,7 @@ using namespace pcb;
 
 namespace pcb {
 int device_count();
+void trim_host_cache();
 }
 
 struct pcb_handle {
@@ -156,6 +157,8 @@ const char* pcb_last_error(const pcb_handle* h) { return h ? h->err.c_str() : g_
 
 int pcb_reserve(pcb_handle* h, uint64_t n) { PCB_GUARD(h, h->builder->reserve(n)) }
 
+int pcb_set_stream(pcb_handle* h, void* cuda_stream) { PCB_GUARD(h, h->builder->set_stream(cuda_stream)) }
+
 int pcb_begin_file(pcb_handle* h) {
     if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
     PCB_GUARD(h, h->builder->begin_file())
@@ -247,6 +250,8 @@ int pcb_finish(pcb_handle* h, pcb_stats* stats) {
 }
 
 void pcb_close(pcb_handle* h) { delete h; }
+
+void pcb_trim_host_cache(void) { pcb::trim_host_cache(); }
 
 uint64_t pcb_node_count(const pcb_handle* h) { return (h && h->finished) ? h->builder->nodes().size() : 0; }
 

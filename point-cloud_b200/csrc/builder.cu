@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <mutex>
 
 #include "builder.h"
 #include "common.cuh"
@@ -19,6 +20,42 @@ namespace pcb {
 static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
+
+// Process-wide cache of pinned host buffers: cudaHostAlloc costs ~0.3 ms/MB, far more than the copy it
+// serves, so node-image staging buffers are recycled between levels, handles and runs.
+struct PinnedCache {
+    std::mutex mu;
+    std::vector<std::pair<void*, u64>> free_list;
+    void* get(u64 bytes, u64* got) {
+        {
+            std::lock_guard<std::mutex> g(mu);
+            size_t best = SIZE_MAX;
+            for (size_t i = 0; i < free_list.size(); i++)
+                if (free_list[i].second >= bytes && (best == SIZE_MAX || free_list[i].second < free_list[best].second)) best = i;
+            if (best != SIZE_MAX && free_list[best].second <= 2 * bytes + (1u << 20)) {
+                void* p = free_list[best].first;
+                *got = free_list[best].second;
+                free_list.erase(free_list.begin() + best);
+                return p;
+            }
+        }
+        void* p = nullptr;
+        u64 sz = (bytes + (1u << 20) - 1) & ~((u64)(1u << 20) - 1);
+        CUDA_TRY(cudaHostAlloc(&p, sz, cudaHostAllocDefault));
+        *got = sz;
+        return p;
+    }
+    void put(void* p, u64 bytes) {
+        std::lock_guard<std::mutex> g(mu);
+        free_list.emplace_back(p, bytes);
+    }
+    void trim() {
+        std::lock_guard<std::mutex> g(mu);
+        for (auto& f : free_list) cudaFreeHost(f.first);
+        free_list.clear();
+    }
+};
+static PinnedCache g_pinned;
 
 struct Scratch {  // small device-resident results, mirrored in pinned host memory
     u64 diffmask;
@@ -41,6 +78,8 @@ class BuilderImpl {
 
     // staged input (input order), batch segments
     PcbPoint* d_in = nullptr;
+    bool in_borrowed = false;  // d_in aliases the caller's device buffer (pcb_add_points_device, first add)
+    bool own_stream = true;
     u64 n_in = 0, cap_in = 0;
     std::vector<BatchSeg> segs;
     u32 next_batch = 0;
@@ -83,12 +122,12 @@ class BuilderImpl {
         cudaDeviceSynchronize();
         for (auto& l : levels) {
             if (l.d_image) cudaFree(l.d_image);
-            if (l.h_image) cudaFreeHost(l.h_image);
+            if (l.h_image) g_pinned.put(l.h_image, l.h_cap);
         }
-        if (d_in) cudaFree(d_in);
+        if (d_in && !in_borrowed) cudaFree(d_in);
         if (d_scr) cudaFree(d_scr);
         if (h_scr) cudaFreeHost(h_scr);
-        if (st) cudaStreamDestroy(st);
+        if (st && own_stream) cudaStreamDestroy(st);
         if (copy_st) cudaStreamDestroy(copy_st);
     }
 
@@ -140,6 +179,11 @@ class BuilderImpl {
         prof_recs.clear();
     }
 
+    void set_stream(cudaStream_t s) {
+        if (st && own_stream) cudaStreamDestroy(st);
+        st = s;
+        own_stream = false;
+    }
     void fetch_scratch() {
         CUDA_TRY(cudaMemcpyAsync(h_scr, d_scr, sizeof(Scratch), cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
@@ -160,9 +204,10 @@ class BuilderImpl {
         CUDA_TRY(cudaMalloc(&p, n * sizeof(PcbPoint)));
         if (n_in) CUDA_TRY(cudaMemcpyAsync(p, d_in, n_in * sizeof(PcbPoint), cudaMemcpyDeviceToDevice, st));
         CUDA_TRY(cudaStreamSynchronize(st));
-        if (d_in) CUDA_TRY(cudaFree(d_in));
+        if (d_in && !in_borrowed) CUDA_TRY(cudaFree(d_in));
         d_in = p;
         cap_in = n;
+        in_borrowed = false;
     }
 
     // ---- batch bookkeeping (lib.rs:31-52).  A "run" = one input file: its points are cut into batches
@@ -203,7 +248,14 @@ class BuilderImpl {
             segs.push_back(s);
         }
         run_points += n;
-        if (n) {
+        if (n && device_ptr && n_in == 0 && cap_in == 0) {
+            // resident input: alias the caller's buffer instead of copying it (it must stay valid and
+            // unchanged until the build has run)
+            d_in = (PcbPoint*)pts;
+            in_borrowed = true;
+            cap_in = n;
+            n_in = n;
+        } else if (n) {
             if (n_in + n > cap_in) reserve(std::min<u64>(std::max<u64>(n_in + n, cap_in + cap_in / 2), (1ull << 30) - 1));
             double t0 = now_s();
             CUDA_TRY(cudaMemcpyAsync(d_in + n_in, pts, n * sizeof(PcbPoint),
@@ -306,11 +358,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     k_l0_key<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, kA, vA, &d_scr->diffmask);
     pe("l0_key", 1, n0, 32ull * n0);
     fetch_scratch();
-    int passes = 0;
-    u64 l0 = launches;
-    pb();
-    int cur = radix_sort_pairs(kA, vA, kB, vB, n0, h_scr->diffmask, rt, st, &launches, &passes);
-    { u64 k = launches - l0; launches = l0; pe("radix_sort", k, (u64)n0 * passes, 40ull * n0 * passes); }
+    int cur = radix_sort_pairs(kA, vA, kB, vB, n0, h_scr->diffmask, rt, st, *this);
     u64* ks = cur ? kB : kA;
     u64* vs = cur ? vB : vA;
     u64 vol = (u64)box.nx * box.ny * box.nz;
@@ -462,11 +510,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     const u64 scan_bytes = 32ull * (256ull * div_up(n, RADIX_TILE) / 2048 + n / 2048 + (u64)ncell / 2048 + 8);
     unsigned char* scan_tmp = dalloc<unsigned char>(scan_bytes);
     rt.scan_agg = (u32*)scan_tmp;
-    int passes = 0;
-    u64 l0 = launches;
-    pb();
-    int cur = radix_sort_pairs(kA, vA, kB, vB, n, h_scr->diffmask, rt, st, &launches, &passes);
-    { u64 k = launches - l0; launches = l0; pe("radix_sort", k, (u64)n * passes, 40ull * n * passes); }
+    int cur = radix_sort_pairs(kA, vA, kB, vB, n, h_scr->diffmask, rt, st, *this);
     u64* ks = cur ? kB : kA;
     u64* vs = cur ? vB : vA;
 
@@ -563,7 +607,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         nodes.push_back(r);
     }
     if (!(flags & PCB_FLAG_DEVICE_ONLY)) {
-        CUDA_TRY(cudaHostAlloc(&img.h_image, std::max<u64>(img.bytes, 16), cudaHostAllocDefault));
+        img.h_image = (unsigned char*)g_pinned.get(std::max<u64>(img.bytes, 16), &img.h_cap);
         cudaEvent_t ev;
         CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
         CUDA_TRY(cudaEventRecord(ev, st));
@@ -611,6 +655,7 @@ void Builder::reserve(uint64_t n) {
     guarded([&] { impl_->reserve(n); return 0; });
 }
 void Builder::begin_file() { impl_->begin_file(); }
+void Builder::set_stream(void* stream) { impl_->set_stream((cudaStream_t)stream); }
 void Builder::add_points(const pcb_point* pts, uint64_t n, uint32_t batch_size, bool device_ptr) {
     guarded([&] { impl_->add(pts, n, batch_size ? batch_size : 10000u, device_ptr, false); return 0; });
 }
@@ -630,6 +675,8 @@ uint32_t Builder::levels_built() const { return impl_->levels_built; }
 double Builder::h2d_seconds() const { return impl_->h2d_s; }
 double Builder::build_seconds() const { return impl_->build_s; }
 double Builder::d2h_seconds() const { return impl_->d2h_s; }
+
+void trim_host_cache() { g_pinned.trim(); }
 
 int device_count() {
     int c = 0;

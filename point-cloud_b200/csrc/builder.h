@@ -60,6 +60,7 @@ struct LevelImage {
     uint64_t bytes = 0;
     unsigned char* d_image = nullptr;  // device copy (kept when PCB_FLAG_DEVICE_ONLY)
     unsigned char* h_image = nullptr;  // pinned host copy (otherwise)
+    uint64_t h_cap = 0;
 };
 
 struct KernelStat {
@@ -75,6 +76,7 @@ class Builder {
     ~Builder();
     void set_config(uint32_t limit, uint32_t dim, float max_cell_size);
     void reserve(uint64_t n);
+    void set_stream(void* cuda_stream);  // run on the caller's stream (e.g. torch's current stream)
     void begin_file();                                        // lib.rs:17-32: batches never span files
     void add_points(const pcb_point* pts, uint64_t n, uint32_t batch_size, bool device_ptr);
     void add_points_one_batch(const pcb_point* pts, uint64_t n, bool device_ptr);  // converter.rs:106

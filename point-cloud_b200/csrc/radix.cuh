@@ -137,15 +137,16 @@ struct RadixTemp {
 };
 
 // Sorts by the key bits set in `diffmask`.  Ping-pongs between (k0,v0) and (k1,v1); returns 0 or 1 = which
-// pair holds the sorted data.  `launches` is incremented by the kernels launched.
+// pair holds the sorted data.  `prof` brackets every kernel class: prof.pb(); prof.pe(name, launches, units, bytes).
+template <class Prof>
 static inline int radix_sort_pairs(u64* k0, u64* v0, u64* k1, u64* v1, u32 n, u64 diffmask, RadixTemp& tmp,
-                                   cudaStream_t st, u64* launches, int* passes_out = nullptr) {
+                                   cudaStream_t st, Prof& prof) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(k_radix_downsweep, cudaFuncAttributeMaxDynamicSharedMemorySize, RADIX_SMEM_BYTES);
         attr_set = true;
     }
-    int cur = 0, passes = 0;
+    int cur = 0;
     if (n < 2) diffmask = 0;
     const u32 ntiles = div_up(n, RADIX_TILE);
     int shift = 0;
@@ -154,16 +155,19 @@ static inline int radix_sort_pairs(u64* k0, u64* v0, u64* k1, u64* v1, u32 n, u6
         int bits = 64 - shift < 8 ? 64 - shift : 8;
         u32 mask = (1u << bits) - 1u;
         u64 *ki = cur ? k1 : k0, *vi = cur ? v1 : v0, *ko = cur ? k0 : k1, *vo = cur ? v0 : v1;
+        prof.pb();
         k_radix_upsweep<<<ntiles, RADIX_THREADS, 0, st>>>(ki, n, shift, mask, ntiles, tmp.tile_hist);
+        prof.pe("radix_upsweep", 1, n, 8ull * n);
         SumOp<u32, u32> op{tmp.tile_hist, tmp.tile_hist, nullptr};
-        *launches += 1 + device_scan(op, 256u * ntiles, tmp.scan_agg, st);
+        prof.pb();
+        int nl = device_scan(op, 256u * ntiles, tmp.scan_agg, st);
+        prof.pe("radix_scan", nl, 256ull * ntiles, 8ull * 256 * ntiles);
+        prof.pb();
         k_radix_downsweep<<<ntiles, RADIX_THREADS, RADIX_SMEM_BYTES, st>>>(ki, vi, ko, vo, n, shift, mask, ntiles,
                                                                         tmp.tile_hist);
-        *launches += 1;
+        prof.pe("radix_downsweep", 1, n, 32ull * n);
         cur ^= 1;
-        passes++;
         shift += 8;
     }
-    if (passes_out) *passes_out = passes;
     return cur;
 }

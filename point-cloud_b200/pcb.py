@@ -24,8 +24,8 @@ FLAG_DEVICE_ONLY = 2
 FLAG_PROFILE = 4
 
 EXPORTS = [
-    "pcb_open", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
-    "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_last_error", "pcb_node_count", "pcb_node_get",
+    "pcb_open", "pcb_set_stream", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
+    "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
     "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
 
@@ -78,6 +78,7 @@ def load_library():
     L.pcb_add_points_batch.argtypes = [vp, vp, C.c_uint64]
     L.pcb_add_points_device.argtypes = [vp, vp, C.c_uint64]
     L.pcb_reserve.argtypes = [vp, C.c_uint64]
+    L.pcb_set_stream.argtypes = [vp, vp]
     L.pcb_finish.argtypes = [vp, C.POINTER(PcbStats)]
     L.pcb_close.argtypes = [vp]
     L.pcb_close.restype = None
@@ -128,6 +129,9 @@ class Converter:
     def _check(self, rc):
         if rc != 0:
             raise PcbError(rc, (self._L.pcb_last_error(self._h) or b"").decode())
+
+    def set_stream(self, cuda_stream: int):
+        self._check(self._L.pcb_set_stream(self._h, C.c_void_p(cuda_stream)))
 
     def reserve(self, n: int):
         self._check(self._L.pcb_reserve(self._h, n))

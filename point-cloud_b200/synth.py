@@ -1,0 +1,80 @@
+"""Synthetic clouds of BASELINE.json's configs, generated with torch so the same code
+runs on the GPU (bench inputs resident in HBM) and on the CPU (bounded CPU-baseline samples).
+Every generator returns a uint8 tensor of shape (n, 16): the reference's 16-byte Point records
+(point-converter/src/point.rs:25-37: f32 x, y, z little-endian + r, g, b, a)."""
+from __future__ import annotations
+
+import torch
+
+
+def _hash01(ix: torch.Tensor, iy: torch.Tensor, seed: int) -> torch.Tensor:
+    """Integer lattice hash -> uniform [0, 1) float32 (splitmix-style, int64 arithmetic wraps)."""
+    h = ix * 0x632BE59B + iy * 0x2545F491 + seed * 0x9E3779B1
+    h = (h ^ (h >> 15)) * 0x2C1B3C6D
+    h = (h ^ (h >> 12)) * 0x297A2D39
+    h = h ^ (h >> 15)
+    return (h & 0xFFFFFF).to(torch.float32) / 16777216.0
+
+
+def _value_noise(x: torch.Tensor, y: torch.Tensor, wavelength: float, seed: int) -> torch.Tensor:
+    u, v = x / wavelength, y / wavelength
+    iu, iv = torch.floor(u), torch.floor(v)
+    fu, fv = u - iu, v - iv
+    iu, iv = iu.to(torch.int64), iv.to(torch.int64)
+    su, sv = fu * fu * (3 - 2 * fu), fv * fv * (3 - 2 * fv)
+    a, b = _hash01(iu, iv, seed), _hash01(iu + 1, iv, seed)
+    c, d = _hash01(iu, iv + 1, seed), _hash01(iu + 1, iv + 1, seed)
+    return (a + (b - a) * su) * (1 - sv) + (c + (d - c) * su) * sv
+
+
+def _pack(xyz: torch.Tensor, gen: torch.Generator) -> torch.Tensor:
+    n = xyz.shape[0]
+    out = torch.empty((n, 16), dtype=torch.uint8, device=xyz.device)
+    out[:, :12] = xyz.contiguous().view(torch.uint8).view(n, 12)
+    rgb = torch.randint(0, 256, (n, 3), dtype=torch.uint8, device=xyz.device, generator=gen)
+    out[:, 12:15] = rgb
+    out[:, 15] = 255
+    return out
+
+
+def terrain(n: int, seed: int = 2, device="cpu", extent=(-2000.0, 2000.0, -2000.0, 2000.0), chunk=1 << 24) -> torch.Tensor:
+    """C2: 2.5-D LiDAR-like terrain: x, y uniform in the extent, z = 3-octave value noise (amplitude 120 m,
+    base wavelength 1 km) + Gaussian sensor noise sigma = 0.05 m.  Density for the named config:
+    1e8 points over 4 km x 4 km = 6.25 points/m^2."""
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    out = torch.empty((n, 16), dtype=torch.uint8, device=device)
+    x0, x1, y0, y1 = extent
+    for s in range(0, n, chunk):
+        m = min(chunk, n - s)
+        x = torch.rand(m, device=device, generator=gen) * (x1 - x0) + x0
+        y = torch.rand(m, device=device, generator=gen) * (y1 - y0) + y0
+        z = (_value_noise(x, y, 1000.0, seed) + 0.5 * _value_noise(x, y, 500.0, seed + 1) +
+             0.25 * _value_noise(x, y, 250.0, seed + 2)) * (120.0 / 1.75)
+        z = z + torch.randn(m, device=device, generator=gen) * 0.05
+        out[s:s + m] = _pack(torch.stack([x, y, z], dim=1).to(torch.float32), gen)
+    return out
+
+
+def uniform_cube(n: int, seed: int = 1, device="cpu") -> torch.Tensor:
+    """C1: uniform points in the unit cube."""
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    return _pack(torch.rand((n, 3), device=device, generator=gen), gen)
+
+
+def gaussian_blobs(n: int, seed: int = 4, device="cpu", blobs: int = 64, chunk=1 << 24) -> torch.Tensor:
+    """C4: Zipf-weighted isotropic Gaussian blobs, sigma log-uniform 1..100 m, centres in +-4 km."""
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    centres = torch.rand((blobs, 3), device=device, generator=gen) * torch.tensor([8000.0, 8000.0, 500.0], device=device) \
+        - torch.tensor([4000.0, 4000.0, 0.0], device=device)
+    sigma = 100.0 ** torch.rand(blobs, device=device, generator=gen)
+    w = 1.0 / torch.arange(1, blobs + 1, device=device, dtype=torch.float32)
+    out = torch.empty((n, 16), dtype=torch.uint8, device=device)
+    for s in range(0, n, chunk):
+        m = min(chunk, n - s)
+        k = torch.multinomial(w, m, replacement=True, generator=gen)
+        xyz = centres[k] + torch.randn((m, 3), device=device, generator=gen) * sigma[k, None]
+        out[s:s + m] = _pack(xyz.to(torch.float32), gen)
+    return out
