@@ -2,6 +2,8 @@
 // kernels of level.cuh in the order tests/bulk_model.py specifies.  There is no CPU compute path here:
 // without a CUDA device the constructor throws (PCB_ERR_CUDA).
 #include <limits.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -19,6 +21,19 @@ namespace pcb {
 
 static double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// PCB_TRACE=1: host-side timeline of the build on stderr (synchronises at every mark; debugging only)
+static bool g_trace = getenv("PCB_TRACE") != nullptr;
+static double g_trace_t0 = 0, g_trace_last = 0;
+static void trace_mark(cudaStream_t st, const char* what, unsigned level = 0, unsigned long long n = 0) {
+    if (!g_trace) return;
+    double a = now_s();
+    cudaStreamSynchronize(st);
+    double b = now_s();
+    fprintf(stderr, "[pcb] %8.3f ms (+%7.3f host, +%7.3f drain) L%u n=%llu %s\n", (b - g_trace_t0) * 1e3,
+            (a - g_trace_last) * 1e3, (b - a) * 1e3, level, n, what);
+    g_trace_last = now_s();
 }
 
 // Process-wide cache of pinned host buffers: cudaHostAlloc costs ~0.3 ms/MB, far more than the copy it
@@ -304,6 +319,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     CUDA_TRY(cudaSetDevice(device));
     end_run();
     const double t_start = now_s();
+    g_trace_t0 = g_trace_last = t_start;
     limit = meta->cell_point_overflow_limit;
     dim = meta->sub_grid_dimension;
     max_cell_size = meta->max_cell_size;
@@ -326,6 +342,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     pe("bbox_check", 1, n0, 16ull * n0);
     fetch_scratch();
     check_err();
+    trace_mark(st, "bbox", 0, n0);
     float lo[3], hi[3];
     for (int a = 0; a < 3; a++) { lo[a] = ord2f_host(h_scr->bbox[a]); hi[a] = ord2f_host(h_scr->bbox[3 + a]); }
     if (meta->number_of_points == 0) {              // converter.rs:98-99: first points REPLACE the box
@@ -358,7 +375,9 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     k_l0_key<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, kA, vA, &d_scr->diffmask);
     pe("l0_key", 1, n0, 32ull * n0);
     fetch_scratch();
+    trace_mark(st, "l0_key", 0, n0);
     int cur = radix_sort_pairs(kA, vA, kB, vB, n0, h_scr->diffmask, rt, st, *this);
+    trace_mark(st, "l0_sort", 0, n0);
     u64* ks = cur ? kB : kA;
     u64* vs = cur ? vB : vA;
     u64 vol = (u64)box.nx * box.ny * box.nz;
@@ -378,6 +397,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     pe("l0_gather", 1, n0, 44ull * n0);
     fetch_scratch();
     u32 ncell = h_scr->ncell;
+    trace_mark(st, "l0_gather", 0, n0);
     dfree(kA); dfree(vA); dfree(kB); dfree(vB); dfree(rt.tile_hist); dfree(scan_tmp); dfree(d_segs);
 
 
@@ -390,6 +410,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
         h++;
     }
     levels_built = h;
+    trace_mark(st, "levels done");
     dfree(pts); dfree(bat); dfree(cell_start); dfree(cell_idx);
     CUDA_TRY(cudaStreamSynchronize(st));
     build_s += now_s() - t_start;
@@ -503,6 +524,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     pe("hexkey", 2, n, 36ull * n);
     fetch_scratch();
     check_err();
+    trace_mark(st, "hexkey", h, n);
 
     // ---- stage 3: stable sort by (cell, Z, Y, X)
     RadixTemp rt;
@@ -513,6 +535,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     int cur = radix_sort_pairs(kA, vA, kB, vB, n, h_scr->diffmask, rt, st, *this);
     u64* ks = cur ? kB : kA;
     u64* vs = cur ? vB : vA;
+    trace_mark(st, "sort", h, n);
 
     // ---- stage 4: contest
     u32* emitted = dalloc<u32>(n);
@@ -523,6 +546,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     int nl = device_scan(cop, n, (ContestState*)scan_tmp, st);
     pe("contest", nl, n, 2 * 16ull * n + 8ull * n);
 
+    trace_mark(st, "contest", h, n);
     // ---- stages 5-6: octants + segmented 8-way split of the losers
     unsigned char* oct8 = dalloc<unsigned char>(n);
     u32* rank = dalloc<u32>(n);
@@ -542,6 +566,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                                                     los_bat, los_bucket);
     pe("loser_scatter", 2, n, 29ull * n);
 
+    trace_mark(st, "octsplit", h, n);
     // ---- stage 7: flush decisions + offsets
     unsigned char* bflag = dalloc<unsigned char>(8ull * ncell);
     u32 *bfl = dalloc<u32>(8ull * ncell), *bcount = dalloc<u32>(8ull * ncell), *bdst = dalloc<u32>(8ull * ncell);
@@ -565,12 +590,14 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     check_err();
     const LevelTotals tot = h_scr->totals;
     const u32 nwin = h_scr->nwin, nlos = n - nwin;
+    trace_mark(st, "decide", h, ncell);
 
     // ---- stage 8: node images + next level's arrivals
     LevelImage img;
     img.hierarchy = h;
     img.bytes = tot.image_bytes;
     CUDA_TRY(cudaMalloc(&img.d_image, std::max<u64>(img.bytes, 16)));
+    trace_mark(st, "img_malloc", h, img.bytes);
     PcbPoint* next_pts = dalloc<PcbPoint>(tot.n_next);
     u32* next_bat = dalloc<u32>(tot.n_next);
     u32* next_cell_start = dalloc<u32>((u64)tot.ncell_next + 1);
@@ -595,6 +622,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         pe("exlist_emit", 1, nex, 44ull * nex);
     }
 
+    trace_mark(st, "emit", h, nlos);
     // node records (host) and image download
     const u32 slot = (u32)levels.size();
     for (u32 c = 0; c < ncell; c++) {
@@ -617,6 +645,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     }
     levels.push_back(img);
 
+    trace_mark(st, "records+d2h", h, ncell);
     // ---- hand over to the next level
     dfree(cellbase); dfree(kA); dfree(vA); dfree(kB); dfree(vB); dfree(cell_of); dfree(rt.tile_hist); dfree(scan_tmp);
     dfree(emitted); dfree(win_src); dfree(win_end); dfree(oct8); dfree(rank); dfree(cellP); dfree(bstart);
@@ -627,6 +656,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     pts = next_pts; bat = next_bat; cell_start = next_cell_start; cell_idx = next_cell_idx;
     n = tot.n_next;
     ncell = tot.ncell_next;
+    trace_mark(st, "frees", h, n);
 }
 
 // ---- public wrappers: every CUDA failure becomes a pcb::Error ------------------------------------------
