@@ -102,6 +102,9 @@ class BuilderImpl {
 
     Scratch* d_scr = nullptr;
     Scratch* h_scr = nullptr;
+    u64 h_scr_cap = 0;
+    u32* d_bat_in = nullptr;   // optional per-point batch ordinals (pcb_add_points_device_batched)
+    bool bat_owned = false;
 
     std::vector<NodeRec> nodes;
     std::vector<LevelImage> levels;
@@ -129,19 +132,23 @@ class BuilderImpl {
         CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, dev));
         uint64_t thr = UINT64_MAX;
         CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
-        CUDA_TRY(cudaMalloc(&d_scr, sizeof(Scratch)));
-        CUDA_TRY(cudaHostAlloc(&h_scr, sizeof(Scratch), cudaHostAllocDefault));
+        u64 got = 0;
+        h_scr = (Scratch*)g_pinned.get(sizeof(Scratch), &got);   // recycled: cudaHostAlloc costs ~0.1 ms
+        h_scr_cap = got;
     }
     ~BuilderImpl() {
         cudaSetDevice(device);
-        cudaDeviceSynchronize();
+        cudaStreamSynchronize(st);
+        cudaStreamSynchronize(copy_st);
         for (auto& l : levels) {
-            if (l.d_image) cudaFree(l.d_image);
+            if (l.d_image) cudaFreeAsync(l.d_image, st);
             if (l.h_image) g_pinned.put(l.h_image, l.h_cap);
         }
         if (d_in && !in_borrowed) cudaFree(d_in);
-        if (d_scr) cudaFree(d_scr);
-        if (h_scr) cudaFreeHost(h_scr);
+        if (d_bat_in && bat_owned) cudaFree(d_bat_in);
+        if (d_scr) cudaFreeAsync(d_scr, st);
+        if (h_scr) g_pinned.put(h_scr, h_scr_cap);
+        cudaStreamSynchronize(st);
         if (st && own_stream) cudaStreamDestroy(st);
         if (copy_st) cudaStreamDestroy(copy_st);
     }
@@ -285,13 +292,21 @@ class BuilderImpl {
     }
 
     void build(Metadata* meta, NodeSource* existing);
+    template <bool PAIRS>
     void build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start, int*& cell_idx, u32& n, u32& ncell,
-                     Metadata* meta, NodeSource* existing);
+                     NodeSource* existing);
+    bool pairs_mode_for(u32 n, u32 ncell, const LevelGeom& g);
 };
 
 static int bits_for(u32 range) {
     int b = 1;
     while ((1u << b) < range) b++;
+    return b;
+}
+// bits needed to hold any value in [0, count)
+static int bits_count(u64 count) {
+    int b = 0;
+    while (b < 64 && (1ull << b) < count) b++;
     return b;
 }
 
@@ -305,15 +320,17 @@ static LevelGeom make_geom(float max_cell_size, u32 dim, u32 h) {
     g.sub = g.S / (float)dim;                      // metadata.rs:95-97
     g.R = g.sub / 2.0f;                            // cell.rs:277
     u32 rx = (u32)std::ceil(2.0 * dim / 1.7320508) + 3, ry = (u32)std::ceil(2.0 * dim / 1.5) + 3, rz = 2 * dim + 3;
-    g.bx = bits_for(rx + 16);
-    g.by = bits_for(ry + 16);
-    g.bz = bits_for(rz + 16);
+    g.bx = bits_for(rx + 8);
+    g.by = bits_for(ry + 8);
+    g.bz = bits_for(rz + 8);
     g.mx = (int)(((1u << g.bx) - rx) / 2);
     g.my = (int)(((1u << g.by) - ry) / 2);
     g.mz = (int)(((1u << g.bz) - rz) / 2);
     g.hexbits = g.bx + g.by + g.bz;
     return g;
 }
+
+static const bool g_force_pairs = getenv("PCB_FORCE_PAIRS") != nullptr;  // test hook: exercise the payload sort
 
 void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     CUDA_TRY(cudaSetDevice(device));
@@ -330,12 +347,14 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     if (n_in == 0) return;
     const u32 n0 = (u32)n_in;
     const float S0 = max_cell_size;
+    if (!d_scr) d_scr = dalloc<Scratch>(1);
 
     // ---- stage 0a: bounding box + validation
     Scratch init;
     memset(&init, 0, sizeof init);
     for (int a = 0; a < 3; a++) { init.bbox[a] = INT_MAX; init.bbox[3 + a] = INT_MIN; }
-    CUDA_TRY(cudaMemcpyAsync(d_scr, &init, sizeof init, cudaMemcpyHostToDevice, st));
+    *h_scr = init;
+    CUDA_TRY(cudaMemcpyAsync(d_scr, h_scr, sizeof init, cudaMemcpyHostToDevice, st));
     const int grid_big = 148 * 8;
     pb();
     k_bbox_check<<<grid_big, 256, 0, st>>>(d_in, n0, S0, d_scr->bbox, &d_scr->err);
@@ -365,48 +384,56 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     }
     box.ox = o3[0]; box.oy = o3[1]; box.oz = o3[2];
     box.nx = d3[0]; box.ny = d3[1]; box.nz = d3[2];
-    u64 *kA = dalloc<u64>(n0), *vA = dalloc<u64>(n0), *kB = dalloc<u64>(n0), *vB = dalloc<u64>(n0);
+    const u64 vol = (u64)box.nx * box.ny * box.nz;   // < 2^63: every axis spans < 2^21 cells
+    const int cb0 = bits_count(vol);
+    int pb0 = std::max(1, bits_count(n0));
+    const bool pairs0 = g_force_pairs || cb0 + pb0 > 64;
+    if (pairs0) pb0 = 0;
+    const RadixPlan plan0 = radix_plan(pb0, cb0);
+    u64 *kA = dalloc<u64>(n0), *kB = dalloc<u64>(n0);
+    u32 *vA = pairs0 ? dalloc<u32>(n0) : nullptr, *vB = pairs0 ? dalloc<u32>(n0) : nullptr;
     RadixTemp rt;
-    rt.tile_hist = dalloc<u32>(RadixTemp::hist_words(n0));
-    const u64 scan_bytes = 32ull * (256ull * div_up(n0, RADIX_TILE) / 2048 + n0 / 2048 + 8);
-    unsigned char* scan_tmp = dalloc<unsigned char>(scan_bytes);
-    rt.scan_agg = (u32*)scan_tmp;
+    const u64 rwords = RadixTemp::ghist_words() + RadixTemp::status_words(n0, plan0);
+    rt.ghist = dalloc<u32>(rwords);
+    rt.status = rt.ghist + RadixTemp::ghist_words();
+    CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
     pb();
-    k_l0_key<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, kA, vA, &d_scr->diffmask);
-    pe("l0_key", 1, n0, 32ull * n0);
-    fetch_scratch();
-    trace_mark(st, "l0_key", 0, n0);
-    int cur = radix_sort_pairs(kA, vA, kB, vB, n0, h_scr->diffmask, rt, st, *this);
-    trace_mark(st, "l0_sort", 0, n0);
+    k_l0_key<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, pb0, plan0, kA, vA, rt.ghist);
+    pe("l0_key", 1, n0, 24ull * n0);
+    int cur = pairs0 ? radix_sort<true>(kA, vA, kB, vB, n0, plan0, rt, st, *this)
+                     : radix_sort<false>(kA, vA, kB, vB, n0, plan0, rt, st, *this);
     u64* ks = cur ? kB : kA;
-    u64* vs = cur ? vB : vA;
-    u64 vol = (u64)box.nx * box.ny * box.nz;
+    u32* vs = cur ? vB : vA;
+    trace_mark(st, "l0_sort", 0, n0);
     u32 ncell_ub = (u32)std::min<u64>(n0, vol);
     u32* cell_start = dalloc<u32>((u64)ncell_ub + 1);
     int* cell_idx = dalloc<int>(3ull * ncell_ub);
-    L0HeadOp hop{ks, n0, box, cell_start, cell_idx, &d_scr->ncell};
+    void* scan_tmp = dalloc<unsigned char>(chain_scan_temp_bytes<u32, 256, 8>(n0));
+    L0HeadOp hop{ks, n0, pb0, box, cell_start, cell_idx, &d_scr->ncell};
     pb();
-    int nl = device_scan(hop, n0, (u32*)scan_tmp, st);
-    pe("l0_heads", nl, n0, 16ull * n0);
+    int nl = chain_scan<L0HeadOp, 256, 8>(hop, n0, scan_tmp, st);
+    pe("l0_heads", nl, n0, 8ull * n0);
     BatchSeg* d_segs = dalloc<BatchSeg>(segs.size());
     CUDA_TRY(cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(BatchSeg), cudaMemcpyHostToDevice, st));
     PcbPoint* pts = dalloc<PcbPoint>(n0);
     u32* bat = dalloc<u32>(n0);
     pb();
-    k_l0_gather<<<div_up(n0, 256), 256, 0, st>>>(d_in, vs, n0, d_segs, (u32)segs.size(), pts, bat);
+    k_l0_gather<<<div_up(n0, 256), 256, 0, st>>>(d_in, ks, vs, n0, pb0, d_segs, (u32)segs.size(), d_bat_in, pts, bat);
     pe("l0_gather", 1, n0, 44ull * n0);
     fetch_scratch();
     u32 ncell = h_scr->ncell;
     trace_mark(st, "l0_gather", 0, n0);
-    dfree(kA); dfree(vA); dfree(kB); dfree(vB); dfree(rt.tile_hist); dfree(scan_tmp); dfree(d_segs);
-
+    dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp); dfree(d_segs);
 
     // ---- levels
     u32 n = n0, h = 0;
     while (n) {
         if (h >= 32) throw Error{PCB_ERR_RANGE, "octree deeper than 31 levels (reference overflows 2u32.pow, metadata.rs:92)"};
         meta->hierarchies = std::max<uint32_t>(meta->hierarchies, h + 1);  // converter.rs:141-144
-        build_level(h, pts, bat, cell_start, cell_idx, n, ncell, meta, existing);
+        if (pairs_mode_for(n, ncell, make_geom(max_cell_size, dim, h)))
+            build_level<true>(h, pts, bat, cell_start, cell_idx, n, ncell, existing);
+        else
+            build_level<false>(h, pts, bat, cell_start, cell_idx, n, ncell, existing);
         h++;
     }
     levels_built = h;
@@ -419,19 +446,24 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     d2h_s += now_s() - t1;
     for (auto& l : levels)
         if (l.h_image && l.d_image) {
-            CUDA_TRY(cudaFree(l.d_image));
+            dfree(l.d_image);
             l.d_image = nullptr;
         }
     prof_collect();
 }
 
+bool BuilderImpl::pairs_mode_for(u32 n, u32 ncell, const LevelGeom& g) {
+    const int cb = bits_count(ncell), pbits = std::max(1, bits_count(n));
+    if (cb + g.hexbits > 64) throw Error{PCB_ERR_RANGE, "too many cells on one level"};
+    return g_force_pairs || cb + g.hexbits + pbits > 64;
+}
+
 // One level of the hierarchy for ALL batches (converter.rs:114-139).  In: arrivals sorted by (cell, tau).
 // Out: this level's node images + the next level's arrivals (same invariant).
+template <bool PAIRS>
 void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start, int*& cell_idx, u32& n, u32& ncell,
-                              Metadata* meta, NodeSource* existing) {
-    (void)meta;
+                              NodeSource* existing) {
     const LevelGeom g = make_geom(max_cell_size, dim, h);
-    if ((u64)ncell >= (1ull << (62 - g.hexbits))) throw Error{PCB_ERR_RANGE, "too many cells on one level"};
     const u32 n_new = n;  // arrivals proper (incumbents of merge mode are added below)
     arrivals += n_new;
 
@@ -440,8 +472,8 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     u32 *ex_m0 = nullptr, *ex_bucket = nullptr, *ex_rank = nullptr;
     PcbPoint* ex_pts = nullptr;
     u32 nex = 0;
+    std::vector<int> hidx(3ull * ncell);
     if (existing) {
-        std::vector<int> hidx(3ull * ncell);
         CUDA_TRY(cudaMemcpyAsync(hidx.data(), cell_idx, hidx.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
         std::vector<u32> inc_start(ncell + 1, 0);
@@ -512,117 +544,111 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         }
     }
 
-    // ---- stages 1-2: hex keys
+    // ---- key layout and radix plan of this level
+    KeyLayout lay;
+    lay.cb = bits_count(ncell);
+    lay.hexbits = g.hexbits;
+    lay.pb = PAIRS ? 0 : std::max(1, bits_count(n));
+    if (lay.cb + lay.hexbits + lay.pb > 64) throw Error{PCB_ERR_RANGE, "too many cells on one level"};
+    const RadixPlan plan = radix_plan(lay.pb, lay.cb + lay.hexbits);
+
+    // ---- stages 1-2: hex keys (+ the digit histograms of every pass)
     int* cellbase = dalloc<int>(3ull * ncell);
-    u64 *kA = dalloc<u64>(n), *vA = dalloc<u64>(n), *kB = dalloc<u64>(n), *vB = dalloc<u64>(n);
-    u32* cell_of = dalloc<u32>(n);
-    CUDA_TRY(cudaMemsetAsync(&d_scr->diffmask, 0, sizeof(u64), st));
+    u64 *kA = dalloc<u64>(n), *kB = dalloc<u64>(n);
+    u32 *vA = PAIRS ? dalloc<u32>(n) : nullptr, *vB = PAIRS ? dalloc<u32>(n) : nullptr;
+    RadixTemp rt;
+    const u64 rwords = RadixTemp::ghist_words() + RadixTemp::status_words(n, plan);
+    rt.ghist = dalloc<u32>(rwords);
+    rt.status = rt.ghist + RadixTemp::ghist_words();
+    CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
     pb();
     k_cellbase<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, ncell, g, cellbase);
-    k_hexkey<<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, cellbase, g, kA, vA,
-                                                                     cell_of, &d_scr->diffmask, &d_scr->err);
-    pe("hexkey", 2, n, 36ull * n);
-    fetch_scratch();
-    check_err();
+    k_hexkey<PAIRS><<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, cellbase, g, lay,
+                                                                            plan, kA, vA, rt.ghist, &d_scr->err);
+    pe("hexkey", 2, n, (PAIRS ? 28ull : 24ull) * n);
     trace_mark(st, "hexkey", h, n);
 
     // ---- stage 3: stable sort by (cell, Z, Y, X)
-    RadixTemp rt;
-    rt.tile_hist = dalloc<u32>(RadixTemp::hist_words(n));
-    const u64 scan_bytes = 32ull * (256ull * div_up(n, RADIX_TILE) / 2048 + n / 2048 + (u64)ncell / 2048 + 8);
-    unsigned char* scan_tmp = dalloc<unsigned char>(scan_bytes);
-    rt.scan_agg = (u32*)scan_tmp;
-    int cur = radix_sort_pairs(kA, vA, kB, vB, n, h_scr->diffmask, rt, st, *this);
+    int cur = radix_sort<PAIRS>(kA, vA, kB, vB, n, plan, rt, st, *this);
     u64* ks = cur ? kB : kA;
-    u64* vs = cur ? vB : vA;
+    u32* vs = cur ? vB : vA;
+    u64* em = cur ? kA : kB;   // the other key buffer is free now
     trace_mark(st, "sort", h, n);
 
     // ---- stage 4: contest
-    u32* emitted = dalloc<u32>(n);
     u32* win_src = dalloc<u32>(n);
     u32* win_end = dalloc<u32>(ncell);
-    ContestOp cop{ks, vs, n, g.hexbits, emitted, win_src, win_end, &d_scr->nwin};
+    const u64 tmp_bytes = std::max<u64>(std::max<u64>(chain_scan_temp_bytes<ContestState, 256, 8>(n),
+                                                      chain_scan_temp_bytes<Oct8, 512, 4>(n)),
+                                        chain_scan_temp_bytes<CellScanState, 256, 4>(ncell));
+    void* scan_tmp = dalloc<unsigned char>(tmp_bytes);
+    ContestOp<PAIRS> cop{ks, vs, n, lay, g, pts, cellbase, cell_idx, cell_start, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
     pb();
-    int nl = device_scan(cop, n, (ContestState*)scan_tmp, st);
-    pe("contest", nl, n, 2 * 16ull * n + 8ull * n);
-
+    int nl = chain_scan<ContestOp<PAIRS>, 256, 8>(cop, n, scan_tmp, st);
+    pe("contest", nl, n, (PAIRS ? 36ull : 32ull) * n);
     trace_mark(st, "contest", h, n);
-    // ---- stages 5-6: octants + segmented 8-way split of the losers
-    unsigned char* oct8 = dalloc<unsigned char>(n);
-    u32* rank = dalloc<u32>(n);
-    u32* cellP = dalloc<u32>(8ull * (ncell + 1));
-    u32* bstart = dalloc<u32>(8ull * ncell + 1);
-    u32 *los_src = dalloc<u32>(n), *los_bat = dalloc<u32>(n), *los_bucket = dalloc<u32>(n);
-    pb();
-    k_octant<<<div_up(n, 256), 256, 0, st>>>(emitted, pts, cell_of, cell_idx, n, g.S_child, oct8, &d_scr->err);
-    pe("octant", 1, n, 25ull * n);
-    OctScanOp oop{oct8, cell_of, ncell, rank, cellP};
-    pb();
-    nl = device_scan<OctScanOp, 256, 16>(oop, n, (Oct8*)scan_tmp, st);
-    pe("oct_scan", nl, n, 14ull * n);
-    pb();
-    k_bucket_start<<<div_up(ncell, 256), 256, 0, st>>>(cellP, ncell, bstart);
-    k_loser_scatter<<<div_up(n, 256), 256, 0, st>>>(oct8, rank, cell_of, cellP, bstart, emitted, bat, n, los_src,
-                                                    los_bat, los_bucket);
-    pe("loser_scatter", 2, n, 29ull * n);
 
+    // ---- stages 5-6: segmented 8-way split of the losers (ranks inside their (cell, octant) buckets)
+    u32* rank = dalloc<u32>(n);
+    u32* bcnt = dalloc<u32>(8ull * ncell);
+    u32* special = dalloc<u32>(32ull * ncell);
+    OctScanOp oop{em, bat, cell_start, ncell, n, limit, ex_state, ex_m0, rank, bcnt, special};
+    pb();
+    nl = chain_scan<OctScanOp, 512, 4>(oop, n, scan_tmp, st);
+    pe("oct_scan", nl, n, 12ull * n);
     trace_mark(st, "octsplit", h, n);
+
     // ---- stage 7: flush decisions + offsets
-    unsigned char* bflag = dalloc<unsigned char>(8ull * ncell);
-    u32 *bfl = dalloc<u32>(8ull * ncell), *bcount = dalloc<u32>(8ull * ncell), *bdst = dalloc<u32>(8ull * ncell);
-    u64* boff = dalloc<u64>(8ull * ncell);
+    BucketDst* bdst = dalloc<BucketDst>(8ull * ncell);
     u32 *cell_deliver = dalloc<u32>(ncell), *cell_children = dalloc<u32>(ncell);
     u32 *cell_dbase = dalloc<u32>(ncell), *cell_cbase = dalloc<u32>(ncell);
     u64 *cell_bytes = dalloc<u64>(ncell), *node_off = dalloc<u64>(ncell);
     pb();
-    k_bucket_decide<<<div_up(ncell, 128), 128, 0, st>>>(bstart, los_bat, win_end, ncell, limit, ex_state, ex_m0, bflag,
-                                                        bfl, bcount, cell_deliver, cell_children, cell_bytes);
+    k_bucket_decide<<<div_up(ncell, 128), 128, 0, st>>>(bcnt, special, win_end, ncell, limit, ex_state, ex_m0, bdst,
+                                                        cell_deliver, cell_children, cell_bytes);
     CellScanOp sop{cell_deliver, cell_children, cell_bytes, cell_dbase, cell_cbase, node_off, &d_scr->totals};
-    nl = device_scan(sop, ncell, (CellScanState*)scan_tmp, st);
+    nl = chain_scan<CellScanOp, 256, 4>(sop, ncell, scan_tmp, st);
     pe("bucket_decide", 1 + nl, ncell, 200ull * ncell);
     // node table for the host
-    std::vector<int> hidx(3ull * ncell);
     std::vector<u64> hoff(ncell), hbytes(ncell);
-    CUDA_TRY(cudaMemcpyAsync(hidx.data(), cell_idx, hidx.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (!existing) CUDA_TRY(cudaMemcpyAsync(hidx.data(), cell_idx, hidx.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaMemcpyAsync(hoff.data(), node_off, 8ull * ncell, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaMemcpyAsync(hbytes.data(), cell_bytes, 8ull * ncell, cudaMemcpyDeviceToHost, st));
     fetch_scratch();
     check_err();
     const LevelTotals tot = h_scr->totals;
-    const u32 nwin = h_scr->nwin, nlos = n - nwin;
+    const u32 nwin = h_scr->nwin;
     trace_mark(st, "decide", h, ncell);
 
     // ---- stage 8: node images + next level's arrivals
     LevelImage img;
     img.hierarchy = h;
     img.bytes = tot.image_bytes;
-    CUDA_TRY(cudaMalloc(&img.d_image, std::max<u64>(img.bytes, 16)));
-    trace_mark(st, "img_malloc", h, img.bytes);
+    img.d_image = dalloc<unsigned char>(std::max<u64>(img.bytes, 16));
     PcbPoint* next_pts = dalloc<PcbPoint>(tot.n_next);
     u32* next_bat = dalloc<u32>(tot.n_next);
     u32* next_cell_start = dalloc<u32>((u64)tot.ncell_next + 1);
     int* next_cell_idx = dalloc<int>(3ull * tot.ncell_next);
     pb();
-    k_cell_emit<<<div_up(ncell, 128), 128, 0, st>>>(cell_idx, ncell, h, g, win_end, bflag, bcount, cell_dbase, cell_cbase,
-                                                    node_off, cell_bytes, img.d_image, bdst, boff, next_cell_start,
-                                                    next_cell_idx, tot.n_next, tot.ncell_next);
+    k_cell_emit<<<div_up(ncell, 128), 128, 0, st>>>(cell_idx, ncell, h, g, win_end, bdst, cell_dbase, cell_cbase, node_off,
+                                                    cell_bytes, img.d_image, next_cell_start, next_cell_idx, tot.n_next,
+                                                    tot.ncell_next);
     pe("cell_emit", 1, ncell, 300ull * ncell);
     pb();
-    if (nlos)
-        k_loser_emit<<<div_up(nlos, 256), 256, 0, st>>>(los_src, los_bat, los_bucket, nlos, pts, bstart, bflag, bfl, bcount,
-                                                        bdst, boff, next_pts, next_bat, img.d_image);
-    pe("loser_emit", nlos ? 1 : 0, nlos, 48ull * nlos);
+    k_loser_emit<<<div_up(n, 256), 256, 0, st>>>(em, rank, bat, n, cell_start, ncell, pts, bdst, next_pts, next_bat,
+                                                 img.d_image);
+    pe("loser_emit", 1, n, 12ull * n + 40ull * (n - nwin));
     pb();
-    k_winner_emit<<<div_up(nwin, 256), 256, 0, st>>>(win_src, nwin, win_end, cell_of, pts, node_off, img.d_image);
-    pe("winner_emit", 1, nwin, 40ull * nwin);
+    k_winner_emit<<<div_up(nwin, 256), 256, 0, st>>>(win_src, nwin, win_end, ncell, pts, node_off, img.d_image);
+    pe("winner_emit", 1, nwin, 36ull * nwin);
     if (nex) {
         pb();
-        k_exlist_emit<<<div_up(nex, 256), 256, 0, st>>>(ex_pts, nex, ex_bucket, ex_rank, bflag, bfl, bdst, boff, next_pts,
-                                                        next_bat, img.d_image);
+        k_exlist_emit<<<div_up(nex, 256), 256, 0, st>>>(ex_pts, nex, ex_bucket, ex_rank, bdst, next_pts, next_bat,
+                                                        img.d_image);
         pe("exlist_emit", 1, nex, 44ull * nex);
     }
+    trace_mark(st, "emit", h, n - nwin);
 
-    trace_mark(st, "emit", h, nlos);
     // node records (host) and image download
     const u32 slot = (u32)levels.size();
     for (u32 c = 0; c < ncell; c++) {
@@ -645,18 +671,15 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     }
     levels.push_back(img);
 
-    trace_mark(st, "records+d2h", h, ncell);
     // ---- hand over to the next level
-    dfree(cellbase); dfree(kA); dfree(vA); dfree(kB); dfree(vB); dfree(cell_of); dfree(rt.tile_hist); dfree(scan_tmp);
-    dfree(emitted); dfree(win_src); dfree(win_end); dfree(oct8); dfree(rank); dfree(cellP); dfree(bstart);
-    dfree(los_src); dfree(los_bat); dfree(los_bucket); dfree(bflag); dfree(bfl); dfree(bcount); dfree(bdst); dfree(boff);
+    dfree(cellbase); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
+    dfree(win_src); dfree(win_end); dfree(rank); dfree(bcnt); dfree(special); dfree(bdst);
     dfree(cell_deliver); dfree(cell_children); dfree(cell_dbase); dfree(cell_cbase); dfree(cell_bytes); dfree(node_off);
     dfree(ex_state); dfree(ex_m0); dfree(ex_pts); dfree(ex_bucket); dfree(ex_rank);
     dfree(pts); dfree(bat); dfree(cell_start); dfree(cell_idx);
     pts = next_pts; bat = next_bat; cell_start = next_cell_start; cell_idx = next_cell_idx;
     n = tot.n_next;
     ncell = tot.ncell_next;
-    trace_mark(st, "frees", h, n);
 }
 
 // ---- public wrappers: every CUDA failure becomes a pcb::Error ------------------------------------------

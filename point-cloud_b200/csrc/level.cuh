@@ -8,6 +8,7 @@
 // tests/bulk_model.py is the executable specification of this file (validated against the oracle).
 #pragma once
 #include "common.cuh"
+#include "radix.cuh"
 
 struct LevelGeom {
     float S;        // cell edge of this level            metadata.rs:91-93
@@ -69,30 +70,43 @@ __global__ void k_bbox_check(const PcbPoint* __restrict__ pts, u32 n, float S0, 
     }
 }
 
+// Sort-key layout of a level (host decides, kernels follow):
+//   embedded (PAIRS = false): key = [cell ordinal : cb][Z : bz][Y : by][X : bx][arrival position : pb]
+//   pairs    (PAIRS = true) : key = [cell ordinal : cb][Z][Y][X], value = arrival position
+// The radix passes cover the cell + hex bits only; the arrival position in the low bits rides along, and
+// because the input is in arrival order and every pass is stable, groups come out in arrival order.
+struct KeyLayout {
+    int pb;        // bits of the arrival position (0 in pairs mode)
+    int hexbits;   // bx + by + bz
+    int cb;        // bits of the cell ordinal
+};
+
 // Stage 0b: level-0 cell of every input point (converter.rs:110 group_points(points, 0)) as a dense
-// linear id inside the index box [o, o + dim) known from the bounding box; value = input index.
+// linear id inside the index box [o, o + dim) known from the bounding box.  key = cell id << pb | input index.
 struct L0Box {
     int ox, oy, oz;
     u32 nx, ny, nz;
 };
-__device__ __forceinline__ u64 l0_key(const PcbPoint& p, float S0, const L0Box& b) {
+__device__ __forceinline__ u64 l0_cell_id(const PcbPoint& p, float S0, const L0Box& b) {
     u64 ix = (u64)(u32)(cell_index_axis(p.x, S0) - b.ox);
     u64 iy = (u64)(u32)(cell_index_axis(p.y, S0) - b.oy);
     u64 iz = (u64)(u32)(cell_index_axis(p.z, S0) - b.oz);
     return (iz * b.ny + iy) * b.nx + ix;
 }
-__global__ void k_l0_key(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, u64* __restrict__ keys,
-                         u64* __restrict__ vals, u64* __restrict__ diffmask) {
-    const u64 key0 = l0_key(pts[0], S0, box);
-    u64 diff = 0;
+__global__ void __launch_bounds__(256)
+k_l0_key(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, int pb, RadixPlan plan,
+         u64* __restrict__ keys, u32* __restrict__ vals /* pairs mode (pb == 0), else null */, u32* __restrict__ ghist) {
+    __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
+    for (int i = threadIdx.x; i < plan.npass * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
-        u64 k = l0_key(pts[i], S0, box);
+        u64 k = l0_cell_id(pts[i], S0, box);
+        if (vals) vals[i] = (u32)i; else k = (k << pb) | i;
         keys[i] = k;
-        vals[i] = i;
-        diff |= k ^ key0;
+        radix_hist_add(hist, plan, k);
     }
-    for (int o = 16; o; o >>= 1) diff |= __shfl_xor_sync(0xFFFFFFFFu, diff, o);
-    if ((threadIdx.x & 31) == 0 && diff) atomicOr((unsigned long long*)diffmask, (unsigned long long)diff);
+    __syncthreads();
+    radix_hist_flush(hist, plan, ghist);
 }
 
 // Stage 0c: distinct level-0 cells of the sorted keys -> cell list + segment starts.
@@ -100,17 +114,18 @@ struct L0HeadOp {
     typedef u32 State;
     const u64* keys;
     u32 n;
+    int pb;
     L0Box box;
     u32* cell_start;  // [ncell + 1]
     int* cell_idx;    // [ncell * 3]
     u32* ncell_out;
     __device__ State identity() const { return 0; }
-    __device__ State load(u32 i) const { return (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u; }
+    __device__ State load(u32 i) const { return (i == 0 || (keys[i] >> pb) != (keys[i - 1] >> pb)) ? 1u : 0u; }
     __device__ State combine(const State& a, const State& b) const { return a + b; }
-    __device__ void consume(u32 i, const State& excl, const State& incl) const {
+    __device__ void consume(u32 i, const State& excl, const State& incl, const State&) const {
         if (incl != excl) {
             cell_start[excl] = i;
-            u64 k = keys[i];
+            u64 k = keys[i] >> pb;
             u32 ix = (u32)(k % box.nx);
             u64 r = k / box.nx;
             u32 iy = (u32)(r % box.ny);
@@ -127,20 +142,25 @@ struct L0HeadOp {
 };
 
 // Stage 0d: arrivals of level 0 in (cell, input index) order; batch ordinal from the segment table
-// (lib.rs:31-52: batches of `batch_size` points, never spanning files).
+// (lib.rs:31-52: batches of `batch_size` points, never spanning files) or, when the caller supplied them
+// (multi-GPU: the exchange keeps global batch ordinals), from in_bat.
 struct BatchSeg {
     u32 start;       // first input index of the segment
     u32 first_batch; // global ordinal of its first batch
     u32 batch_size;  // points per batch inside the segment
     u32 pad;
 };
-__global__ void k_l0_gather(const PcbPoint* __restrict__ in_pts, const u64* __restrict__ vals, u32 n,
-                            const BatchSeg* __restrict__ segs, u32 nseg, PcbPoint* __restrict__ pts,
-                            u32* __restrict__ bat) {
+__global__ void k_l0_gather(const PcbPoint* __restrict__ in_pts, const u64* __restrict__ keys,
+                            const u32* __restrict__ vals, u32 n, int pb, const BatchSeg* __restrict__ segs, u32 nseg, const u32* __restrict__ in_bat,
+                            PcbPoint* __restrict__ pts, u32* __restrict__ bat) {
     u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
-    u32 i = (u32)vals[j];
+    u32 i = vals ? vals[j] : (u32)(keys[j] & ((1ull << pb) - 1ull));
     pts[j] = in_pts[i];
+    if (in_bat) {
+        bat[j] = in_bat[i] + 1u;
+        return;
+    }
     u32 lo = 0, hi = nseg;
     while (hi - lo > 1) {
         u32 mid = (lo + hi) >> 1;
@@ -164,249 +184,269 @@ __global__ void k_cellbase(const int* __restrict__ cell_idx, u32 ncell, LevelGeo
     cellbase[3 * c + 2] = k.z - g.mz;
 }
 
-// Stage 2: hex-prism key (cell.rs:276-278 -> hex.rs:32-34) and contest metric d2 (cell.rs:75-78)
-// of every arrival.  key = cell ordinal << hexbits | Z << (bx+by) | Y << bx | X   (window-relative)
-//                    val = d2 bits << 32 | arrival position
-__device__ __forceinline__ u64 hexkey_of(const PcbPoint& p, u32 c, const int* __restrict__ cellbase,
-                                         const LevelGeom& g, float* d2, u32* bad) {
-    HexKey k = hex_from_world(p.x, p.y, p.z, g.R);
-    *d2 = hex_d2(k, p.x, p.y, p.z, g.R);
-    u32 rx = (u32)(k.x - cellbase[3 * c + 0]);
-    u32 ry = (u32)(k.y - cellbase[3 * c + 1]);
-    u32 rz = (u32)(k.z - cellbase[3 * c + 2]);
-    if ((rx >> g.bx) | (ry >> g.by) | (rz >> g.bz)) *bad |= PCB_DERR_HEXRANGE;
-    return ((u64)c << g.hexbits) | ((u64)rz << (g.bx + g.by)) | ((u64)ry << g.bx) | (u64)rx;
+// cell of arrival i: one binary search per warp (on the warp's first element), then a short walk
+__device__ __forceinline__ u32 cell_of_arrival(const u32* __restrict__ cell_start, u32 ncell, u32 i, u32 warp_first) {
+    u32 c = find_segment(cell_start, ncell, warp_first);
+    while (__ldg(cell_start + c + 1) <= i) c++;
+    return c;
 }
-__global__ void k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_start, u32 ncell,
-                         const int* __restrict__ cellbase, LevelGeom g, u64* __restrict__ keys,
-                         u64* __restrict__ vals, u32* __restrict__ cell_of, u64* __restrict__ diffmask,
-                         u32* __restrict__ err) {
+
+// Stage 2: hex-prism key (cell.rs:276-278 -> hex.rs:32-34) of every arrival, window-relative, plus the digit
+// histograms of all radix passes.
+template <bool PAIRS>
+__global__ void __launch_bounds__(256)
+k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_start, u32 ncell,
+         const int* __restrict__ cellbase, LevelGeom g, KeyLayout lay, RadixPlan plan, u64* __restrict__ keys,
+         u32* __restrict__ vals, u32* __restrict__ ghist, u32* __restrict__ err) {
+    __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
+    for (int i = threadIdx.x; i < plan.npass * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
     u32 bad = 0;
-    float d2;
-    const u64 key0 = hexkey_of(pts[0], 0, cellbase, g, &d2, &bad);
-    bad = 0;
-    u64 diff = 0;
-    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
-        PcbPoint p = pts[i];
-        u32 c = find_segment(cell_start, ncell, (u32)i);
-        u64 k = hexkey_of(p, c, cellbase, g, &d2, &bad);
-        keys[i] = k;
-        vals[i] = ((u64)__float_as_uint(d2) << 32) | (u64)i;
-        cell_of[i] = c;
-        diff |= k ^ key0;
+    for (u64 i0 = (u64)blockIdx.x * blockDim.x; i0 < n; i0 += (u64)gridDim.x * blockDim.x) {
+        u64 i = i0 + threadIdx.x;
+        if (i < n) {
+            PcbPoint p = pts[i];
+            u32 c = cell_of_arrival(cell_start, ncell, (u32)i, (u32)(i0 + (threadIdx.x & ~31u)));
+            HexKey k = hex_from_world(p.x, p.y, p.z, g.R);
+            u32 rx = (u32)(k.x - __ldg(cellbase + 3 * c + 0));
+            u32 ry = (u32)(k.y - __ldg(cellbase + 3 * c + 1));
+            u32 rz = (u32)(k.z - __ldg(cellbase + 3 * c + 2));
+            if ((rx >> g.bx) | (ry >> g.by) | (rz >> g.bz)) {
+                bad |= PCB_DERR_HEXRANGE;
+                rx &= (1u << g.bx) - 1u; ry &= (1u << g.by) - 1u; rz &= (1u << g.bz) - 1u;
+            }
+            u64 key = ((u64)c << g.hexbits) | ((u64)rz << (g.bx + g.by)) | ((u64)ry << g.bx) | (u64)rx;
+            if (PAIRS) {
+                vals[i] = (u32)i;
+            } else {
+                key = (key << lay.pb) | i;
+            }
+            keys[i] = key;
+            radix_hist_add(hist, plan, key);
+        }
     }
-    for (int o = 16; o; o >>= 1) {
-        diff |= __shfl_xor_sync(0xFFFFFFFFu, diff, o);
-        bad |= __shfl_xor_sync(0xFFFFFFFFu, bad, o);
-    }
-    if ((threadIdx.x & 31) == 0) {
-        if (diff) atomicOr((unsigned long long*)diffmask, (unsigned long long)diff);
-        if (bad) atomicOr(err, bad);
-    }
+    for (int o = 16; o; o >>= 1) bad |= __shfl_xor_sync(0xFFFFFFFFu, bad, o);
+    if ((threadIdx.x & 31) == 0 && bad) atomicOr(err, bad);
+    __syncthreads();
+    radix_hist_flush(hist, plan, ghist);
 }
 
 // Stage 4: the hex-grid contest of Cell::add_point (cell.rs:70-94) for every (cell, prism) group at
 // once.  In sorted order a group is contiguous and in arrival order; the incumbent seen by an arrival
 // is the running minimum of (d2, position) over the earlier members (strict `<`: equal d2 keeps the
 // earlier one).  Every non-first member emits exactly one loser — itself, or the incumbent it displaces
-// — and the emission is recorded under the position of the arrival that triggered it.
+// — and the emission is recorded under the position of the arrival that triggered it, together with the
+// loser's child octant (converter.rs:68 group_points(losers, h + 1); octant = dx*4 + dy*2 + dz, so octant
+// order == lexicographic (x, y, z) order of the child index).
+#define PCB_EM_NONE_OCT 8u
+#define PCB_EM_CELL_LAST (1ull << 40)    // this arrival position is the last one of its cell
+#define PCB_EM_CELL_FIRST (1ull << 41)   // ... the first one
 struct ContestState {
-    u64 mn;       // min (d2 bits << 32 | pos) since the last group head
-    u32 has_head; // a group head lies inside the scanned range
-    u32 ntail;    // groups completed (== winners emitted)
+    u64 mn;     // min (d2 bits << 32 | pos) since the last group head
+    u32 meta;   // bits 0-3: child octant of mn's point; bit 8: a group head lies inside the scanned range;
+                // (single elements only) bit 9: group tail, bit 10: last element of its cell in sorted order
+    u32 ntail;  // groups completed (== winners emitted)
 };
+template <bool PAIRS>
 struct ContestOp {
     typedef ContestState State;
     const u64* keys;
-    const u64* vals;
+    const u32* vals;
     u32 n;
-    int hexbits;
-    u32* emitted;  // [n] by arrival position: loser's arrival position, PCB_NONE for group heads
+    KeyLayout lay;
+    LevelGeom g;
+    const PcbPoint* pts;
+    const int* cellbase;
+    const int* cell_idx;
+    const u32* cell_start;
+    u64* em;       // [n] by arrival position: loser's arrival position | octant << 32 | flags
     u32* win_src;  // [#groups] arrival position of each winner, sorted (cell, Z, Y, X)
     u32* win_end;  // [ncell] end of the cell's winners in win_src
     u32* nwin_out;
+    u32* err;
+    __device__ u64 gid(u64 key) const { return PAIRS ? key : (key >> lay.pb); }
     __device__ State identity() const { return State{~0ull, 0u, 0u}; }
-    __device__ State load(u32 i) const {
-        u64 k = keys[i];
-        u32 head = (i == 0 || keys[i - 1] != k) ? 1u : 0u;
-        u32 tail = (i + 1 == n || keys[i + 1] != k) ? 1u : 0u;
-        return State{vals[i], head, tail};
-    }
-    __device__ State combine(const State& a, const State& b) const {
-        State r;
-        r.mn = b.has_head ? b.mn : (a.mn < b.mn ? a.mn : b.mn);
-        r.has_head = a.has_head | b.has_head;
-        r.ntail = a.ntail + b.ntail;
-        return r;
-    }
-    __device__ void consume(u32 i, const State& excl, const State& incl) const {
-        u64 k = keys[i], v = vals[i];
-        u32 pos = (u32)v;
-        bool head = (i == 0 || keys[i - 1] != k);
-        if (head) {
-            emitted[pos] = PCB_NONE;
-        } else {
-            u64 inc = excl.mn;  // incumbent
-            emitted[pos] = ((u32)(v >> 32) < (u32)(inc >> 32)) ? (u32)inc : pos;  // cell.rs:80 strict <
-        }
-        bool tail = (i + 1 == n || keys[i + 1] != k);
-        if (tail) {
-            win_src[excl.ntail] = (u32)incl.mn;
-            if (i + 1 == n || (keys[i + 1] >> hexbits) != (k >> hexbits)) win_end[(u32)(k >> hexbits)] = excl.ntail + 1;
-        }
-    }
-    __device__ void finish(const State& total) const { *nwin_out = total.ntail; }
-};
-
-// Stage 5: child octant of every emitted loser (converter.rs:68 group_points(losers, h + 1)), stored
-// under the trigger's arrival position; 8 = this arrival emitted nothing.  octant = dx*4 + dy*2 + dz
-// so that octant order == lexicographic (x, y, z) order of the child index.
-__global__ void k_octant(const u32* __restrict__ emitted, const PcbPoint* __restrict__ pts,
-                         const u32* __restrict__ cell_of, const int* __restrict__ cell_idx, u32 n, float S_child,
-                         unsigned char* __restrict__ oct8, u32* __restrict__ err) {
-    u64 t = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n) return;
-    u32 e = emitted[t];
-    unsigned char o = 8;
-    if (e != PCB_NONE) {
-        PcbPoint p = pts[e];
-        u32 c = cell_of[t];
-        int dx = cell_index_axis(p.x, S_child) - 2 * cell_idx[3 * c + 0];
-        int dy = cell_index_axis(p.y, S_child) - 2 * cell_idx[3 * c + 1];
-        int dz = cell_index_axis(p.z, S_child) - 2 * cell_idx[3 * c + 2];
+    __device__ State load(u32 j) const {
+        const u64 key = keys[j];
+        const u64 G = gid(key);
+        const u32 pos = PAIRS ? vals[j] : (u32)(key & ((1ull << lay.pb) - 1ull));
+        const u32 c = (u32)(G >> g.hexbits);
+        const PcbPoint p = pts[pos];
+        HexKey k;
+        k.x = (i32)((u32)G & ((1u << g.bx) - 1u)) + cellbase[3 * c + 0];
+        k.y = (i32)((u32)(G >> g.bx) & ((1u << g.by) - 1u)) + cellbase[3 * c + 1];
+        k.z = (i32)((u32)(G >> (g.bx + g.by)) & ((1u << g.bz) - 1u)) + cellbase[3 * c + 2];
+        const float d2 = hex_d2(k, p.x, p.y, p.z, g.R);
+        int dx = cell_index_axis(p.x, g.S_child) - 2 * cell_idx[3 * c + 0];
+        int dy = cell_index_axis(p.y, g.S_child) - 2 * cell_idx[3 * c + 1];
+        int dz = cell_index_axis(p.z, g.S_child) - 2 * cell_idx[3 * c + 2];
         if (((u32)dx | (u32)dy | (u32)dz) > 1u) {
             atomicOr(err, PCB_DERR_NEST);
             dx &= 1; dy &= 1; dz &= 1;
         }
-        o = (unsigned char)(dx * 4 + dy * 2 + dz);
+        u32 meta = (u32)(dx * 4 + dy * 2 + dz);
+        const bool head = (j == 0) || gid(keys[j - 1]) != G;
+        bool tail = true, cell_end = true;
+        if (j + 1 < n) {
+            const u64 Gn = gid(keys[j + 1]);
+            tail = Gn != G;
+            cell_end = (Gn >> g.hexbits) != (G >> g.hexbits);
+        }
+        meta |= (head ? 0x100u : 0u) | (tail ? 0x200u : 0u) | (cell_end ? 0x400u : 0u);
+        return State{((u64)__float_as_uint(d2) << 32) | pos, meta, tail ? 1u : 0u};
     }
-    oct8[t] = o;
-}
+    __device__ State combine(const State& a, const State& b) const {
+        State r;
+        const bool take_b = (b.meta & 0x100u) || b.mn < a.mn;   // equal only for identity: positions are distinct
+        r.mn = take_b ? b.mn : a.mn;
+        r.meta = ((take_b ? b.meta : a.meta) & 0xFu) | ((a.meta | b.meta) & 0x100u);
+        r.ntail = a.ntail + b.ntail;
+        return r;
+    }
+    __device__ void consume(u32 j, const State& excl, const State& incl, const State& self) const {
+        const u32 pos = (u32)self.mn;
+        u64 e;
+        if (self.meta & 0x100u) {
+            e = (u64)PCB_EM_NONE_OCT << 32 | pos;
+        } else if ((u32)(self.mn >> 32) < (u32)(excl.mn >> 32)) {          // cell.rs:80 strict <: displaces the incumbent
+            e = ((u64)(excl.meta & 0xFu) << 32) | (u32)excl.mn;
+        } else {
+            e = ((u64)(self.meta & 0xFu) << 32) | pos;
+        }
+        const u32 c = (u32)(gid(keys[j]) >> g.hexbits);
+        if (self.meta & 0x200u) win_src[excl.ntail] = (u32)incl.mn;
+        if (self.meta & 0x400u) win_end[c] = excl.ntail + 1;
+        if (__ldg(cell_start + c) == pos) e |= PCB_EM_CELL_FIRST;
+        if (__ldg(cell_start + c + 1) == pos + 1u) e |= PCB_EM_CELL_LAST;
+        em[pos] = e;
+    }
+    __device__ void finish(const State& total) const { *nwin_out = total.ntail; }
+};
 
-// Stage 6: segmented stable 8-way split of the losers by child octant.  One scan over arrival positions
-// with eight running counters gives every loser its rank among the losers of its octant; the counter
-// vector at each cell's first arrival (cellP) turns global ranks into per-(cell, octant) ranks.
+// Stage 6: segmented stable 8-way split of the losers by child octant.  One scan over arrival positions,
+// restarting at every cell, with eight running counters gives every loser its rank inside its
+// (cell, octant) bucket.  The trigger batches at the ranks the flush rule looks at are captured on the fly.
+#define PCB_EX_ABSENT 0
+#define PCB_EX_SOME 1
+#define PCB_EX_NONE 2
 struct Oct8 {
     u32 c[8];
+    u32 head;
 };
 struct OctScanOp {
     typedef Oct8 State;
-    const unsigned char* oct8;
-    const u32* cell_of;
+    const u64* em;
+    const u32* bat;
+    const u32* cell_start;
     u32 ncell;
-    u32* rank;   // [n] exclusive count of the same octant before this position (global)
-    u32* cellP;  // [(ncell + 1) * 8] counters at the first arrival of each cell; [ncell] = totals
+    u32 n;
+    u32 L;
+    const unsigned char* ex_state;  // merge mode only (else null)
+    const u32* ex_m0;
+    u32* rank;     // [n] rank of the loser emitted at this position inside its bucket (new losers only)
+    u32* bcnt;     // [ncell * 8] new losers per bucket
+    u32* special;  // [ncell * 8][4] trigger batch (+1) at ranks 0, L-1, L, and (merge) max(L-1-m0, 0)
     __device__ State identity() const {
         State s;
 #pragma unroll
         for (int k = 0; k < 8; k++) s.c[k] = 0;
+        s.head = 0;
         return s;
     }
+    // head word: bit 0 = a cell's first arrival lies in the range; bit 1 (single elements) = cell's last arrival
     __device__ State load(u32 i) const {
-        State s = identity();
-        u32 o = oct8[i];
+        State s;
+        const u64 e = em[i];
+        u32 o = (u32)(e >> 32) & 0xFu;
 #pragma unroll
         for (int k = 0; k < 8; k++) s.c[k] = (o == (u32)k) ? 1u : 0u;
+        s.head = ((e & PCB_EM_CELL_FIRST) ? 1u : 0u) | ((e & PCB_EM_CELL_LAST) ? 2u : 0u);
         return s;
     }
     __device__ State combine(const State& a, const State& b) const {
         State s;
 #pragma unroll
-        for (int k = 0; k < 8; k++) s.c[k] = a.c[k] + b.c[k];
+        for (int k = 0; k < 8; k++) s.c[k] = (b.head & 1u) ? b.c[k] : a.c[k] + b.c[k];
+        s.head = (a.head | b.head) & 1u;
         return s;
     }
-    __device__ void consume(u32 i, const State& excl, const State&) const {
-        u32 o = oct8[i];
+    __device__ void consume(u32 i, const State& excl, const State& incl, const State& self) const {
+        u32 o = 8;
+#pragma unroll
+        for (int k = 0; k < 8; k++) o = self.c[k] ? (u32)k : o;
+        u32 c = PCB_NONE;
         if (o < 8) {
             u32 r = 0;
 #pragma unroll
             for (int k = 0; k < 8; k++) r = (o == (u32)k) ? excl.c[k] : r;
+            if (self.head & 1u) r = 0;
             rank[i] = r;
+            if (ex_state || r == 0 || r + 1 == L || r == L) {
+                c = find_segment(cell_start, ncell, i);
+                const u32 kk = 8 * c + o;
+                const u32 b = bat[i];
+                if (r == 0) special[4 * kk + 0] = b;
+                if (r + 1 == L) special[4 * kk + 1] = b;
+                if (r == L) special[4 * kk + 2] = b;
+                if (ex_state && ex_state[kk] == PCB_EX_SOME) {
+                    u32 m0 = ex_m0[kk];
+                    u32 want = (L >= 1 + m0) ? L - 1 - m0 : 0;
+                    if (r == want) special[4 * kk + 3] = b;
+                }
+            }
         }
-        u32 c = cell_of[i];
-        if (i == 0 || cell_of[i - 1] != c) {
+        if (self.head & 2u) {   // last arrival of its cell: bucket totals
+            if (c == PCB_NONE) c = find_segment(cell_start, ncell, i);
 #pragma unroll
-            for (int k = 0; k < 8; k++) cellP[8 * c + k] = excl.c[k];
+            for (int k = 0; k < 8; k++) bcnt[8 * c + k] = incl.c[k];
         }
     }
-    __device__ void finish(const State& total) const {
-#pragma unroll
-        for (int k = 0; k < 8; k++) cellP[8 * ncell + k] = total.c[k];
-    }
+    __device__ void finish(const State&) const {}
 };
-
-// bucket (cell, octant) -> first loser slot; losers end up grouped by cell, then octant, each bucket in
-// emission order.
-__global__ void k_bucket_start(const u32* __restrict__ cellP, u32 ncell, u32* __restrict__ bstart) {
-    u32 c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncell) return;
-    u32 base = 0;
-#pragma unroll
-    for (int k = 0; k < 8; k++) base += cellP[8 * c + k];
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-        bstart[8 * c + k] = base;
-        base += cellP[8 * (c + 1) + k] - cellP[8 * c + k];
-    }
-    if (c == ncell - 1) bstart[8 * ncell] = base;
-}
-
-__global__ void k_loser_scatter(const unsigned char* __restrict__ oct8, const u32* __restrict__ rank,
-                                const u32* __restrict__ cell_of, const u32* __restrict__ cellP,
-                                const u32* __restrict__ bstart, const u32* __restrict__ emitted,
-                                const u32* __restrict__ bat, u32 n, u32* __restrict__ los_src,
-                                u32* __restrict__ los_bat, u32* __restrict__ los_bucket) {
-    u64 t = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n) return;
-    u32 o = oct8[t];
-    if (o >= 8) return;
-    u32 c = cell_of[t];
-    u32 k = 8 * c + o;
-    u32 dst = bstart[k] + rank[t] - cellP[k];
-    los_src[dst] = emitted[t];
-    los_bat[dst] = bat[t];  // batch of the TRIGGER: the call in which the loser left the grid
-    los_bucket[dst] = k;
-}
 
 // ---------------------------------------------------------------------------------------------
 // Stage 7: Cell::add_points_in_overflow (cell.rs:108-153) for every (cell, child) bucket, closed form.
-// `lb` = trigger batches (+1) of the bucket's NEW losers in emission order, `m0`/`state` = what the node
-// file held before this run (state 0 absent, 1 Some(list of m0), 2 None).  Returns true when the list is
-// delivered to the child; *bf = batch (+1) of the call that delivers the buffered list (0: every call
-// delivers its own losers, state None).          tests/bulk_model.py::flush_rule
-#define PCB_EX_ABSENT 0
-#define PCB_EX_SOME 1
-#define PCB_EX_NONE 2
-__device__ __forceinline__ bool flush_rule(const u32* __restrict__ lb, u32 n, u32 m0, int state, u32 L, u32* bf) {
+// lb0 / lbLm1 / lbL / lbK = trigger batches (+1) of the bucket's NEW losers at emission ranks 0, L-1, L and
+// max(L-1-m0, 0); `m0`/`state` = what the node file held before this run (state 0 absent, 1 Some(list of
+// m0), 2 None).  Returns true when the list is delivered to the child; *bf = batch (+1) of the call that
+// delivers the buffered list (0: every call delivers its own losers, state None).
+//                                                                        tests/bulk_model.py::flush_rule
+__device__ __forceinline__ bool flush_rule(u32 n, u32 m0, int state, u32 L, u32 lb0, u32 lbLm1, u32 lbL, u32 lbK,
+                                           u32* bf) {
     *bf = 0;
     if (state == PCB_EX_NONE) return true;                     // cell.rs:128-130
     if (state == PCB_EX_SOME) {                                // cell.rs:131-147: flush when len >= L
         if ((u64)m0 + n < L) return false;
-        u32 k = (L >= 1 + m0) ? L - 1 - m0 : 0;
-        *bf = lb[k];
+        *bf = lbK;
         return true;
     }
-    if (L == 0) { *bf = lb[0]; return true; }                  // cell.rs:118: len <= 0 never holds
+    if (L == 0) { *bf = lb0; return true; }                    // cell.rs:118: len <= 0 never holds
     if (n < L) return false;                                   // first call keeps when len <= L
-    u32 bstar = lb[L - 1];
-    if (bstar == lb[0] && (n == L || lb[L] != bstar)) {        // first call brought exactly L: kept (:118),
+    u32 bstar = lbLm1;
+    if (bstar == lb0 && (n == L || lbL != bstar)) {            // first call brought exactly L: kept (:118),
         if (n == L) return false;                              // flushed by the next call (:137)
-        *bf = lb[L];
+        *bf = lbL;
         return true;
     }
     *bf = bstar;
     return true;
 }
 
-#define PCB_BF_ENTRY 1
-#define PCB_BF_FLUSH 2
+#define PCB_BF_ENTRY 1u
+#define PCB_BF_FLUSH 2u
 
-__global__ void k_bucket_decide(const u32* __restrict__ bstart, const u32* __restrict__ los_bat,
+// where a bucket's losers go
+struct __align__(16) BucketDst {
+    u64 base;    // FLUSH: first slot in the next level's arrivals; else byte offset of the list in the image
+    u32 bfl;     // batch (+1) of the flushing call
+    u32 m0fl;    // m0 << 2 | flags
+};
+
+__global__ void k_bucket_decide(const u32* __restrict__ bcnt, const u32* __restrict__ special,
                                 const u32* __restrict__ win_end, u32 ncell, u32 L,
                                 const unsigned char* __restrict__ ex_state, const u32* __restrict__ ex_m0,
-                                unsigned char* __restrict__ bflag, u32* __restrict__ bfl, u32* __restrict__ bcount,
-                                u32* __restrict__ cell_deliver, u32* __restrict__ cell_children,
-                                u64* __restrict__ cell_bytes) {
+                                BucketDst* __restrict__ bdst, u32* __restrict__ cell_deliver,
+                                u32* __restrict__ cell_children, u64* __restrict__ cell_bytes) {
     u32 c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= ncell) return;
     u32 ng = win_end[c] - (c ? win_end[c - 1] : 0u);
@@ -414,16 +454,15 @@ __global__ void k_bucket_decide(const u32* __restrict__ bstart, const u32* __res
     u32 deliver = 0, children = 0;
     for (int o = 0; o < 8; o++) {
         u32 k = 8 * c + o;
-        u32 b0 = bstart[k], n = bstart[k + 1] - b0;
+        u32 n = bcnt[k];
         int st = ex_state ? ex_state[k] : PCB_EX_ABSENT;
         u32 m0 = (st == PCB_EX_SOME) ? ex_m0[k] : 0u;
-        unsigned char fl = 0;
-        u32 bf = 0, cnt = m0 + n;
+        u32 fl = 0, bf = 0, cnt = m0 + n;
         if (n == 0) {
             if (st != PCB_EX_ABSENT) { fl = PCB_BF_ENTRY; bytes += 16ull + 16ull * m0; }
         } else {
             fl = PCB_BF_ENTRY;
-            if (flush_rule(los_bat + b0, n, m0, st, L, &bf)) {
+            if (flush_rule(n, m0, st, L, special[4 * k], special[4 * k + 1], special[4 * k + 2], special[4 * k + 3], &bf)) {
                 fl |= PCB_BF_FLUSH;
                 deliver += cnt;
                 children += 1;
@@ -432,9 +471,11 @@ __global__ void k_bucket_decide(const u32* __restrict__ bstart, const u32* __res
                 bytes += 16ull + 16ull * cnt;
             }
         }
-        bflag[k] = fl;
-        bfl[k] = bf;
-        bcount[k] = cnt;
+        BucketDst d;
+        d.base = cnt;   // provisional: k_cell_emit turns the count into the destination
+        d.bfl = bf;
+        d.m0fl = (m0 << 2) | fl;
+        bdst[k] = d;
     }
     cell_deliver[c] = deliver;
     cell_children[c] = children;
@@ -465,7 +506,7 @@ struct CellScanOp {
     __device__ State combine(const State& a, const State& b) const {
         return State{a.bytes + b.bytes, a.deliver + b.deliver, a.children + b.children};
     }
-    __device__ void consume(u32 i, const State& excl, const State&) const {
+    __device__ void consume(u32 i, const State& excl, const State&, const State&) const {
         node_off[i] = excl.bytes;
         cell_dbase[i] = excl.deliver;
         cell_cbase[i] = excl.children;
@@ -493,13 +534,12 @@ __device__ __forceinline__ void store16_at1(unsigned char* dst, uint4 v) {
 }
 
 // Stage 8a: per node: 48-byte Header (cell.rs:280-298), overflow entry count and entry headers
-// (cell.rs:162-177), plus the bucket -> destination tables used by the point movers below.
+// (cell.rs:162-177), plus the bucket -> destination table used by the point movers below.
 __global__ void k_cell_emit(const int* __restrict__ cell_idx, u32 ncell, u32 hierarchy, LevelGeom g,
-                            const u32* __restrict__ win_end, const unsigned char* __restrict__ bflag,
-                            const u32* __restrict__ bcount, const u32* __restrict__ cell_dbase,
-                            const u32* __restrict__ cell_cbase, const u64* __restrict__ node_off,
-                            const u64* __restrict__ cell_bytes, unsigned char* __restrict__ image,
-                            u32* __restrict__ bdst, u64* __restrict__ boff, u32* __restrict__ next_cell_start,
+                            const u32* __restrict__ win_end, BucketDst* __restrict__ bdst,
+                            const u32* __restrict__ cell_dbase, const u32* __restrict__ cell_cbase,
+                            const u64* __restrict__ node_off, const u64* __restrict__ cell_bytes,
+                            unsigned char* __restrict__ image, u32* __restrict__ next_cell_start,
                             int* __restrict__ next_cell_idx, u32 n_next, u32 ncell_next) {
     u32 c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= ncell) return;
@@ -507,10 +547,10 @@ __global__ void k_cell_emit(const int* __restrict__ cell_idx, u32 ncell, u32 hie
     u32 ng = win_end[c] - (c ? win_end[c - 1] : 0u);
     u32 nov = 0, nent = 0;
     for (int o = 0; o < 8; o++) {
-        unsigned char fl = bflag[8 * c + o];
-        if (fl & PCB_BF_ENTRY) {
+        BucketDst d = bdst[8 * c + o];
+        if (d.m0fl & PCB_BF_ENTRY) {
             nent++;
-            if (!(fl & PCB_BF_FLUSH)) nov += bcount[8 * c + o];
+            if (!(d.m0fl & PCB_BF_FLUSH)) nov += (u32)d.base;
         }
     }
     unsigned char* node = image + node_off[c];
@@ -528,81 +568,91 @@ __global__ void k_cell_emit(const int* __restrict__ cell_idx, u32 ncell, u32 hie
     u32 dbase = cell_dbase[c], cb = cell_cbase[c];
     for (int o = 0; o < 8; o++) {
         u32 k = 8 * c + o;
-        unsigned char fl = bflag[k];
-        if (!(fl & PCB_BF_ENTRY)) continue;
+        BucketDst d = bdst[k];
+        if (!(d.m0fl & PCB_BF_ENTRY)) continue;
+        const u32 cnt = (u32)d.base;
         int child[3] = {2 * ix + ((o >> 2) & 1), 2 * iy + ((o >> 1) & 1), 2 * iz + (o & 1)};
-        u32 kept = (fl & PCB_BF_FLUSH) ? 0u : bcount[k];
+        u32 kept = (d.m0fl & PCB_BF_FLUSH) ? 0u : cnt;
         store_bytes(node + eoff, child, 12);
         store_bytes(node + eoff + 12, &kept, 4);
-        boff[k] = node_off[c] + eoff + 16;
-        eoff += 16ull + 16ull * kept;
-        if (fl & PCB_BF_FLUSH) {
-            bdst[k] = dbase;
+        if (d.m0fl & PCB_BF_FLUSH) {
+            d.base = dbase;
             next_cell_start[cb] = dbase;
             next_cell_idx[3 * cb + 0] = child[0];
             next_cell_idx[3 * cb + 1] = child[1];
             next_cell_idx[3 * cb + 2] = child[2];
-            dbase += bcount[k];
+            dbase += cnt;
             cb++;
+        } else {
+            d.base = node_off[c] + eoff + 16;
         }
+        bdst[k] = d;
+        eoff += 16ull + 16ull * kept;
     }
     // zero the alignment padding after the node
     for (u64 b = eoff; b < ((cell_bytes[c] + 15ull) & ~15ull); b++) node[b] = 0;
     if (c == ncell - 1) next_cell_start[ncell_next] = n_next;
 }
 
-// Stage 8b: move every loser: delivered to its child cell (next level's arrivals, in (child, tau')
-// order, with batch max(b_e, b_flush) — SURVEY N3) or kept in the parent's overflow list (image).
-__global__ void k_loser_emit(const u32* __restrict__ los_src, const u32* __restrict__ los_bat,
-                             const u32* __restrict__ los_bucket, u32 nlos, const PcbPoint* __restrict__ pts,
-                             const u32* __restrict__ bstart, const unsigned char* __restrict__ bflag,
-                             const u32* __restrict__ bfl, const u32* __restrict__ bcount,
-                             const u32* __restrict__ bdst, const u64* __restrict__ boff,
-                             PcbPoint* __restrict__ next_pts, u32* __restrict__ next_bat,
-                             unsigned char* __restrict__ image) {
-    u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= nlos) return;
-    u32 k = los_bucket[j];
-    u32 n = bstart[k + 1] - bstart[k];
-    u32 m0 = bcount[k] - n;
-    u32 r = m0 + ((u32)j - bstart[k]);
-    uint4 p = *(const uint4*)(pts + los_src[j]);
-    if (bflag[k] & PCB_BF_FLUSH) {
-        u32 dst = bdst[k] + r;
+// Stage 8b: move every loser, in arrival (= emission) order: delivered to its child cell (next level's
+// arrivals, in (child, tau') order, with batch max(b_e, b_flush) — SURVEY N3) or kept in the parent's
+// overflow list (image).
+__global__ void __launch_bounds__(256)
+k_loser_emit(const u64* __restrict__ em, const u32* __restrict__ rank, const u32* __restrict__ bat, u32 n,
+             const u32* __restrict__ cell_start, u32 ncell, const PcbPoint* __restrict__ pts,
+             const BucketDst* __restrict__ bdst, PcbPoint* __restrict__ next_pts, u32* __restrict__ next_bat,
+             unsigned char* __restrict__ image) {
+    const u64 t0 = (u64)blockIdx.x * blockDim.x;
+    const u64 t = t0 + threadIdx.x;
+    if (t >= n) return;
+    const u64 e = em[t];
+    const u32 o = (u32)(e >> 32) & 0xFu;
+    if (o >= 8) return;
+    const u32 c = cell_of_arrival(cell_start, ncell, (u32)t, (u32)(t0 + (threadIdx.x & ~31u)));
+    const BucketDst d = bdst[8 * c + o];
+    const u32 r = (d.m0fl >> 2) + rank[t];
+    const uint4 p = *(const uint4*)(pts + (u32)e);
+    if (d.m0fl & PCB_BF_FLUSH) {
+        const u64 dst = d.base + r;
         *(uint4*)(next_pts + dst) = p;
-        next_bat[dst] = max(los_bat[j], bfl[k]);
+        next_bat[dst] = max(bat[t], d.bfl);
     } else {
-        store16_at1(image + boff[k] + 16ull * r, p);
+        store16_at1(image + d.base + 16ull * r, p);
     }
 }
 
 // Stage 8c: grid section of every node: the winners, already in (cell, Z, Y, X) order.
-__global__ void k_winner_emit(const u32* __restrict__ win_src, u32 nwin, const u32* __restrict__ win_end,
-                              const u32* __restrict__ cell_of, const PcbPoint* __restrict__ pts,
-                              const u64* __restrict__ node_off, unsigned char* __restrict__ image) {
+__global__ void k_winner_emit(const u32* __restrict__ win_src, u32 nwin, const u32* __restrict__ win_end, u32 ncell,
+                              const PcbPoint* __restrict__ pts, const u64* __restrict__ node_off,
+                              unsigned char* __restrict__ image) {
     u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (w >= nwin) return;
-    u32 src = win_src[w];
-    u32 c = cell_of[src];
-    u32 wbeg = c ? win_end[c - 1] : 0u;
-    *(uint4*)(image + node_off[c] + 48ull + 16ull * ((u32)w - wbeg)) = *(const uint4*)(pts + src);
+    // cell = first c with win_end[c] > w
+    u32 lo = 0, hi = ncell;
+    while (lo < hi) {
+        u32 mid = (lo + hi) >> 1;
+        if (__ldg(win_end + mid) > (u32)w) hi = mid; else lo = mid + 1;
+    }
+    const u32 c = lo;
+    const u32 wbeg = c ? __ldg(win_end + c - 1) : 0u;
+    *(uint4*)(image + node_off[c] + 48ull + 16ull * ((u32)w - wbeg)) = *(const uint4*)(pts + win_src[w]);
 }
 
 // merge mode: the overflow lists that were already in the node files (front of each bucket)
 __global__ void k_exlist_emit(const PcbPoint* __restrict__ ex_pts, u32 nex, const u32* __restrict__ ex_bucket,
-                              const u32* __restrict__ ex_rank, const unsigned char* __restrict__ bflag,
-                              const u32* __restrict__ bfl, const u32* __restrict__ bdst,
-                              const u64* __restrict__ boff, PcbPoint* __restrict__ next_pts,
-                              u32* __restrict__ next_bat, unsigned char* __restrict__ image) {
+                              const u32* __restrict__ ex_rank, const BucketDst* __restrict__ bdst,
+                              PcbPoint* __restrict__ next_pts, u32* __restrict__ next_bat,
+                              unsigned char* __restrict__ image) {
     u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= nex) return;
-    u32 k = ex_bucket[j], r = ex_rank[j];
+    const BucketDst d = bdst[ex_bucket[j]];
+    const u32 r = ex_rank[j];
     uint4 p = *(const uint4*)(ex_pts + j);
-    if (bflag[k] & PCB_BF_FLUSH) {
-        *(uint4*)(next_pts + bdst[k] + r) = p;
-        next_bat[bdst[k] + r] = bfl[k];  // max(0, b_flush)
+    if (d.m0fl & PCB_BF_FLUSH) {
+        *(uint4*)(next_pts + d.base + r) = p;
+        next_bat[d.base + r] = d.bfl;  // max(0, b_flush)
     } else {
-        store16_at1(image + boff[k] + 16ull * r, p);
+        store16_at1(image + d.base + 16ull * r, p);
     }
 }
 

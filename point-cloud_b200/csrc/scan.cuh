@@ -130,3 +130,193 @@ struct SumOp {
         if (total_out) *total_out = total;
     }
 };
+
+// ---------------------------------------------------------------------------------------------
+// Single-pass chained scan (decoupled look-back): every element is read ONCE.  Tiles take their
+// ordinal from an atomic counter, so every predecessor of a running tile is itself running or done
+// (forward progress); a tile publishes its aggregate, then folds its predecessors' published
+// aggregates / inclusive prefixes (one warp, 32 predecessors per step, in order: the operator need
+// not commute) and publishes its own inclusive prefix.  Publication is data-then-flag with
+// st.release.gpu / ld.acquire.gpu.
+//
+// Op interface as above, except
+//   __device__ void consume(u32 i, const State& excl, const State& incl, const State& self) const;
+// (`self` = load(i), kept in registers: load may be expensive, e.g. a gather).
+template <class State>
+struct ChainTemp {
+    State* agg;    // [ntiles]
+    State* incl;   // [ntiles]
+    u32* flag;     // [ntiles + 1]: 0 nothing, 1 aggregate, 2 inclusive prefix; [ntiles] = tile counter
+    static u64 bytes(u64 ntiles) { return (2 * sizeof(State) + 4) * (ntiles + 1) + 64; }
+    static ChainTemp carve(void* p, u64 ntiles) {
+        ChainTemp t;
+        t.flag = (u32*)p;                                       // flags first: one memset clears them
+        u64 off = ((ntiles + 1) * 4 + 15) & ~15ull;
+        t.agg = (State*)((unsigned char*)p + off);
+        t.incl = t.agg + ntiles;
+        return t;
+    }
+    static u64 flag_bytes(u64 ntiles) { return (ntiles + 1) * 4; }
+};
+
+__device__ __forceinline__ u32 ld_acquire_u32(const u32* p) {
+    u32 v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(u32* p, u32 v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <class State>
+__device__ __forceinline__ State shfl_down_state(const State& s, int d) {
+    static_assert(sizeof(State) % 4 == 0, "State must be a multiple of 4 bytes");
+    State r;
+    const u32* a = (const u32*)&s;
+    u32* b = (u32*)&r;
+#pragma unroll
+    for (int w = 0; w < (int)(sizeof(State) / 4); w++) b[w] = __shfl_down_sync(0xFFFFFFFFu, a[w], d);
+    return r;
+}
+template <class State>
+__device__ __forceinline__ State shfl_up_state(const State& s, int d) {
+    State r;
+    const u32* a = (const u32*)&s;
+    u32* b = (u32*)&r;
+#pragma unroll
+    for (int w = 0; w < (int)(sizeof(State) / 4); w++) b[w] = __shfl_up_sync(0xFFFFFFFFu, a[w], d);
+    return r;
+}
+template <class State>
+__device__ __forceinline__ State shfl_state(const State& s, int lane) {
+    State r;
+    const u32* a = (const u32*)&s;
+    u32* b = (u32*)&r;
+#pragma unroll
+    for (int w = 0; w < (int)(sizeof(State) / 4); w++) b[w] = __shfl_sync(0xFFFFFFFFu, a[w], lane);
+    return r;
+}
+template <class State>
+__device__ __forceinline__ State ldcg_state(const State* p) {
+    State r;
+    const u32* a = (const u32*)p;
+    u32* b = (u32*)&r;
+#pragma unroll
+    for (int w = 0; w < (int)(sizeof(State) / 4); w++) b[w] = __ldcg(a + w);
+    return r;
+}
+
+template <class Op, int THREADS, int ITEMS>
+__global__ void __launch_bounds__(THREADS) k_chain_scan(Op op, u32 n, u32 ntiles, ChainTemp<typename Op::State> tmp) {
+    typedef typename Op::State State;
+    constexpr int WARPS = THREADS / 32;
+    __shared__ State s_warp[WARPS];
+    __shared__ State s_prefix;
+    __shared__ u32 s_tile;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(tmp.flag + ntiles, 1u);
+    __syncthreads();
+    const u32 tile = s_tile;
+    const u64 base = (u64)tile * (THREADS * ITEMS) + (u64)tid * ITEMS;
+
+    State v[ITEMS];
+    State acc = op.identity();
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) {
+        u64 i = base + k;
+        v[k] = (i < n) ? op.load((u32)i) : op.identity();
+    }
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) acc = op.combine(acc, v[k]);
+
+    // inclusive scan of the thread aggregates inside the warp, then across warps
+    State winc = acc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        State up = shfl_up_state(winc, d);
+        if (lane >= d) winc = op.combine(up, winc);
+    }
+    if (lane == 31) s_warp[warp] = winc;
+    __syncthreads();
+    State wpre = op.identity();   // warps before mine
+    State total = op.identity();  // whole tile
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) {
+        State sw = s_warp[w];
+        if (w < warp) wpre = op.combine(wpre, sw);
+        total = op.combine(total, sw);
+    }
+    State texcl = shfl_up_state(winc, 1);
+    if (lane == 0) texcl = op.identity();
+    texcl = op.combine(wpre, texcl);   // exclusive prefix of this thread inside the tile
+
+    if (warp == 0) {
+        if (lane == 0) {
+            if (tile == 0) {
+                tmp.incl[0] = total;
+                st_release_u32(tmp.flag, 2u);
+            } else {
+                tmp.agg[tile] = total;
+                st_release_u32(tmp.flag + tile, 1u);
+            }
+        }
+        State prefix = op.identity();
+        if (tile > 0) {
+            int look = (int)tile - 1;
+            for (;;) {
+                int t = look - lane;
+                u32 f = 2u;
+                State s = op.identity();
+                if (t >= 0) {
+                    do { f = ld_acquire_u32(tmp.flag + t); } while (f == 0u);
+                    s = ldcg_state((f == 2u) ? tmp.incl + t : tmp.agg + t);
+                }
+                const u32 m = __ballot_sync(0xFFFFFFFFu, f == 2u);
+                const int last = m ? (__ffs(m) - 1) : 31;
+                if (lane > last) s = op.identity();
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {   // ordered fold: farther tiles (higher lanes) on the left
+                    State o = shfl_down_state(s, d);
+                    if (lane + d < 32) s = op.combine(o, s);
+                }
+                s = shfl_state(s, 0);
+                prefix = op.combine(s, prefix);
+                if (m) break;
+                look -= 32;
+            }
+            if (lane == 0) {
+                tmp.incl[tile] = op.combine(prefix, total);
+                st_release_u32(tmp.flag + tile, 2u);
+            }
+        }
+        if (lane == 0) s_prefix = prefix;
+    }
+    __syncthreads();
+    State run = op.combine(s_prefix, texcl);
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) {
+        u64 i = base + k;
+        if (i < n) {
+            State incl = op.combine(run, v[k]);
+            op.consume((u32)i, run, incl, v[k]);
+            run = incl;
+        }
+    }
+    if (tile == ntiles - 1 && tid == THREADS - 1) op.finish(op.combine(s_prefix, total));
+}
+
+// Host launcher: `temp` must hold ChainTemp<State>::bytes(ntiles) bytes.  Returns launches (memset excluded).
+template <class Op, int THREADS, int ITEMS>
+static inline int chain_scan(const Op& op, u32 n, void* temp, cudaStream_t st) {
+    typedef typename Op::State State;
+    const u32 ntiles = div_up(n, THREADS * ITEMS);
+    if (!ntiles) return 0;
+    ChainTemp<State> t = ChainTemp<State>::carve(temp, ntiles);
+    cudaMemsetAsync(t.flag, 0, ChainTemp<State>::flag_bytes(ntiles), st);
+    k_chain_scan<Op, THREADS, ITEMS><<<ntiles, THREADS, 0, st>>>(op, n, ntiles, t);
+    return 1;
+}
+template <class State, int THREADS, int ITEMS>
+static inline u64 chain_scan_temp_bytes(u64 n) {
+    return ChainTemp<State>::bytes((n + (u64)THREADS * ITEMS - 1) / ((u64)THREADS * ITEMS));
+}
