@@ -579,12 +579,12 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     u32* win_src = dalloc<u32>(n);
     u32* win_end = dalloc<u32>(ncell);
     const u64 tmp_bytes = std::max<u64>(std::max<u64>(chain_scan_temp_bytes<ContestState, 256, 8>(n),
-                                                      chain_scan_temp_bytes<Oct8, 512, 4>(n)),
+                                                      chain_scan_temp_bytes<Oct8, OCT_THREADS, OCT_ITEMS>(n)),
                                         chain_scan_temp_bytes<CellScanState, 256, 4>(ncell));
     void* scan_tmp = dalloc<unsigned char>(tmp_bytes);
     ContestOp<PAIRS> cop{ks, vs, n, lay, g, pts, cellbase, cell_idx, cell_start, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
     pb();
-    int nl = chain_scan<ContestOp<PAIRS>, 256, 8>(cop, n, scan_tmp, st);
+    int nl = chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, n, scan_tmp, st);
     pe("contest", nl, n, (PAIRS ? 36ull : 32ull) * n);
     trace_mark(st, "contest", h, n);
 
@@ -594,7 +594,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     u32* special = dalloc<u32>(32ull * ncell);
     OctScanOp oop{em, bat, cell_start, ncell, n, limit, ex_state, ex_m0, rank, bcnt, special};
     pb();
-    nl = chain_scan<OctScanOp, 512, 4>(oop, n, scan_tmp, st);
+    nl = octscan(oop, n, scan_tmp, st);
     pe("oct_scan", nl, n, 12ull * n);
     trace_mark(st, "octsplit", h, n);
 

@@ -9,6 +9,7 @@
 #pragma once
 #include "common.cuh"
 #include "radix.cuh"
+#include "scan.cuh"
 
 struct LevelGeom {
     float S;        // cell edge of this level            metadata.rs:91-93
@@ -202,11 +203,16 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
     for (int i = threadIdx.x; i < plan.npass * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
     __syncthreads();
     u32 bad = 0;
-    for (u64 i0 = (u64)blockIdx.x * blockDim.x; i0 < n; i0 += (u64)gridDim.x * blockDim.x) {
+    // every block owns one contiguous chunk of arrivals: the cell ordinal is searched once, then walked
+    const u64 chunk = (((u64)n + gridDim.x - 1) / gridDim.x + 255ull) & ~255ull;
+    const u64 lo = (u64)blockIdx.x * chunk, hi = min((u64)n, lo + chunk);
+    u32 c = 0;
+    if (lo + threadIdx.x < hi) c = find_segment(cell_start, ncell, (u32)(lo + threadIdx.x));
+    for (u64 i0 = lo; i0 < hi; i0 += 256) {
         u64 i = i0 + threadIdx.x;
-        if (i < n) {
+        if (i < hi) {
             PcbPoint p = pts[i];
-            u32 c = cell_of_arrival(cell_start, ncell, (u32)i, (u32)(i0 + (threadIdx.x & ~31u)));
+            while (__ldg(cell_start + c + 1) <= (u32)i) c++;
             HexKey k = hex_from_world(p.x, p.y, p.z, g.R);
             u32 rx = (u32)(k.x - __ldg(cellbase + 3 * c + 0));
             u32 ry = (u32)(k.y - __ldg(cellbase + 3 * c + 1));
@@ -403,6 +409,164 @@ struct OctScanOp {
     }
     __device__ void finish(const State&) const {}
 };
+
+// Specialised single-pass kernel for the scan above: inside a tile the eight counters are packed 4 x 16 bit
+// into two 64-bit words (a tile has 2048 arrivals), only the cross-tile prefix uses the 9-word state.
+#define OCT_THREADS 256
+#define OCT_ITEMS 8
+#define OCT_TILE (OCT_THREADS * OCT_ITEMS)
+struct OctPacked {
+    u64 lo, hi;   // counters of octants 0-3 / 4-7, 16 bits each
+    u32 head;
+};
+__device__ __forceinline__ OctPacked oct_combine(const OctPacked& a, const OctPacked& b) {
+    OctPacked r;
+    r.lo = b.head ? b.lo : a.lo + b.lo;
+    r.hi = b.head ? b.hi : a.hi + b.hi;
+    r.head = a.head | b.head;
+    return r;
+}
+__global__ void __launch_bounds__(OCT_THREADS)
+k_octscan(OctScanOp op, u32 n, u32 ntiles, ChainTemp<Oct8> tmp) {
+    constexpr int WARPS = OCT_THREADS / 32;
+    __shared__ OctPacked s_warp[WARPS];
+    __shared__ Oct8 s_prefix;
+    __shared__ u32 s_tile;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(tmp.flag + ntiles, 1u);
+    __syncthreads();
+    const u32 tile = s_tile;
+    const u64 base = (u64)tile * OCT_TILE + (u64)tid * OCT_ITEMS;
+
+    // per element: octant (8 = none) | first << 4 | last << 5
+    u32 code[OCT_ITEMS];
+    if (base + OCT_ITEMS <= n) {
+        const ulonglong2* src = (const ulonglong2*)(op.em + base);
+#pragma unroll
+        for (int k = 0; k < OCT_ITEMS / 2; k++) {
+            ulonglong2 e = src[k];
+            code[2 * k] = ((u32)(e.x >> 32) & 0xFu) | ((e.x & PCB_EM_CELL_FIRST) ? 16u : 0u) | ((e.x & PCB_EM_CELL_LAST) ? 32u : 0u);
+            code[2 * k + 1] = ((u32)(e.y >> 32) & 0xFu) | ((e.y & PCB_EM_CELL_FIRST) ? 16u : 0u) | ((e.y & PCB_EM_CELL_LAST) ? 32u : 0u);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < OCT_ITEMS; k++) {
+            code[k] = 8u;
+            if (base + k < n) {
+                u64 e = op.em[base + k];
+                code[k] = ((u32)(e >> 32) & 0xFu) | ((e & PCB_EM_CELL_FIRST) ? 16u : 0u) | ((e & PCB_EM_CELL_LAST) ? 32u : 0u);
+            }
+        }
+    }
+    OctPacked acc{0ull, 0ull, 0u};
+#pragma unroll
+    for (int k = 0; k < OCT_ITEMS; k++) {
+        const u32 o = code[k] & 0xFu;
+        if (code[k] & 16u) { acc.lo = 0; acc.hi = 0; acc.head = 1u; }
+        const u64 one = 1ull << (16 * (o & 3u));
+        acc.lo += (o < 4u) ? one : 0ull;
+        acc.hi += (o >= 4u && o < 8u) ? one : 0ull;
+    }
+    OctPacked winc = acc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        OctPacked up;
+        up.lo = __shfl_up_sync(0xFFFFFFFFu, winc.lo, d);
+        up.hi = __shfl_up_sync(0xFFFFFFFFu, winc.hi, d);
+        up.head = __shfl_up_sync(0xFFFFFFFFu, winc.head, d);
+        if (lane >= d) winc = oct_combine(up, winc);
+    }
+    if (lane == 31) s_warp[warp] = winc;
+    __syncthreads();
+    OctPacked wpre{0ull, 0ull, 0u}, total{0ull, 0ull, 0u};
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) {
+        OctPacked sw = s_warp[w];
+        if (w < warp) wpre = oct_combine(wpre, sw);
+        total = oct_combine(total, sw);
+    }
+    OctPacked texcl;
+    texcl.lo = __shfl_up_sync(0xFFFFFFFFu, winc.lo, 1);
+    texcl.hi = __shfl_up_sync(0xFFFFFFFFu, winc.hi, 1);
+    texcl.head = __shfl_up_sync(0xFFFFFFFFu, winc.head, 1);
+    if (lane == 0) texcl = OctPacked{0ull, 0ull, 0u};
+    texcl = oct_combine(wpre, texcl);
+
+    if (warp == 0) {
+        Oct8 tot8;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            tot8.c[k] = (u32)(total.lo >> (16 * k)) & 0xFFFFu;
+            tot8.c[4 + k] = (u32)(total.hi >> (16 * k)) & 0xFFFFu;
+        }
+        tot8.head = total.head;
+        Oct8 prefix = chain_lookback(op, tmp, tile, tot8);
+        if (lane == 0) s_prefix = prefix;
+    }
+    __syncthreads();
+    // running 32-bit counters of this thread: prefix (+) texcl
+    u32 run[8];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        u32 a = (u32)(texcl.lo >> (16 * k)) & 0xFFFFu, b = (u32)(texcl.hi >> (16 * k)) & 0xFFFFu;
+        run[k] = texcl.head ? a : s_prefix.c[k] + a;
+        run[4 + k] = texcl.head ? b : s_prefix.c[4 + k] + b;
+    }
+    u32 rk[OCT_ITEMS];
+#pragma unroll
+    for (int k = 0; k < OCT_ITEMS; k++) {
+        const u64 i = base + k;
+        const u32 o = code[k] & 0xFu;
+        if (code[k] & 16u) {
+#pragma unroll
+            for (int q = 0; q < 8; q++) run[q] = 0;
+        }
+        u32 r = 0;
+#pragma unroll
+        for (int q = 0; q < 8; q++) r = (o == (u32)q) ? run[q] : r;
+        rk[k] = r;
+#pragma unroll
+        for (int q = 0; q < 8; q++) run[q] += (o == (u32)q) ? 1u : 0u;
+        if (i < n) {
+            u32 c = PCB_NONE;
+            if (o < 8u && (op.ex_state || r == 0 || r + 1 == op.L || r == op.L)) {
+                c = find_segment(op.cell_start, op.ncell, (u32)i);
+                const u32 kk = 8 * c + o;
+                const u32 b = op.bat[i];
+                if (r == 0) op.special[4 * kk + 0] = b;
+                if (r + 1 == op.L) op.special[4 * kk + 1] = b;
+                if (r == op.L) op.special[4 * kk + 2] = b;
+                if (op.ex_state && op.ex_state[kk] == PCB_EX_SOME) {
+                    u32 m0 = op.ex_m0[kk];
+                    u32 want = (op.L >= 1 + m0) ? op.L - 1 - m0 : 0;
+                    if (r == want) op.special[4 * kk + 3] = b;
+                }
+            }
+            if (code[k] & 32u) {   // last arrival of its cell: bucket totals
+                if (c == PCB_NONE) c = find_segment(op.cell_start, op.ncell, (u32)i);
+#pragma unroll
+                for (int q = 0; q < 8; q++) op.bcnt[8 * c + q] = run[q];
+            }
+        }
+    }
+    if (base + OCT_ITEMS <= n) {
+        uint4* dst = (uint4*)(op.rank + base);
+        dst[0] = make_uint4(rk[0], rk[1], rk[2], rk[3]);
+        dst[1] = make_uint4(rk[4], rk[5], rk[6], rk[7]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < OCT_ITEMS; k++)
+            if (base + k < n) op.rank[base + k] = rk[k];
+    }
+}
+static inline int octscan(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
+    const u32 ntiles = div_up(n, OCT_TILE);
+    if (!ntiles) return 0;
+    ChainTemp<Oct8> t = ChainTemp<Oct8>::carve(temp, ntiles);
+    cudaMemsetAsync(t.flag, 0, ChainTemp<Oct8>::flag_bytes(ntiles), st);
+    k_octscan<<<ntiles, OCT_THREADS, 0, st>>>(op, n, ntiles, t);
+    return 1;
+}
 
 // ---------------------------------------------------------------------------------------------
 // Stage 7: Cell::add_points_in_overflow (cell.rs:108-153) for every (cell, child) bucket, closed form.

@@ -52,8 +52,17 @@ static inline RadixPlan radix_plan(int lo, int nbits) {
 // shared: u32 hist[npass * RADIX_MAX_BINS], zeroed by the caller
 __device__ __forceinline__ void radix_hist_add(u32* __restrict__ hist, const RadixPlan& plan, u64 key) {
 #pragma unroll
-    for (int p = 0; p < RADIX_MAX_PASSES; p++)
-        if (p < plan.npass) atomicAdd(&hist[p * RADIX_MAX_BINS + ((u32)(key >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u))], 1u);
+    for (int p = 0; p < RADIX_MAX_PASSES; p++) {
+        if (p + 1 < plan.npass) {
+            atomicAdd(&hist[p * RADIX_MAX_BINS + ((u32)(key >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u))], 1u);
+        } else if (p + 1 == plan.npass) {
+            // the most significant digit is nearly uniform inside a warp (arrivals come cell by cell):
+            // aggregate in the warp instead of serialising 32 atomics on one address
+            const u32 d = (u32)(key >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u);
+            const u32 peers = __match_any_sync(__activemask(), d);
+            if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u) atomicAdd(&hist[p * RADIX_MAX_BINS + d], (u32)__popc(peers));
+        }
+    }
 }
 __device__ __forceinline__ void radix_hist_flush(const u32* __restrict__ hist, const RadixPlan& plan, u32* __restrict__ ghist) {
     for (int i = threadIdx.x; i < plan.npass * RADIX_MAX_BINS; i += blockDim.x) {
@@ -96,27 +105,19 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
 
     // warp-striped ownership: item k of lane l in warp w is element w*32*ITEMS + k*32 + l (order: k, then lane)
     u64 key[RADIX_ITEMS];
-    u32 rank[RADIX_ITEMS];
     const u32 wbase = warp * 32 * RADIX_ITEMS + lane;
 #pragma unroll
     for (int k = 0; k < RADIX_ITEMS; k++) {
         u32 j = wbase + k * 32;
         key[k] = (j < tile_n) ? keys_in[tbase + j] : ~0ull;
     }
+    // early counts: per-warp digit histogram with shared-memory atomics, so that the tile's counts can be
+    // published (and the tiles behind us unblocked) before the expensive stable ranking
     u32* wcnt = cnt + warp * RADIX_MAX_BINS;
-    const u32 lt = (1u << lane) - 1u;
 #pragma unroll
     for (int k = 0; k < RADIX_ITEMS; k++) {
         u32 j = wbase + k * 32;
-        bool valid = j < tile_n;
-        u32 d = valid ? ((u32)(key[k] >> shift) & mask) : bins;  // invalid lanes form their own match group
-        u32 peers = __match_any_sync(0xFFFFFFFFu, d);
-        u32 lower = __popc(peers & lt);
-        u32 before = valid ? wcnt[d] : 0u;
-        __syncwarp();
-        if (valid && lower == 0) wcnt[d] = before + __popc(peers);
-        __syncwarp();
-        rank[k] = before + lower;
+        if (j < tile_n) atomicAdd(&wcnt[(u32)(key[k] >> shift) & mask], 1u);
     }
     __syncthreads();
 
@@ -130,14 +131,9 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
         if (q < dpt && d < bins) {
             u32 running = 0;
 #pragma unroll
-            for (int w = 0; w < RADIX_WARPS; w++) {
-                u32 c = cnt[w * RADIX_MAX_BINS + d];
-                cnt[w * RADIX_MAX_BINS + d] = running;  // exclusive over warps
-                running += c;
-            }
+            for (int w = 0; w < RADIX_WARPS; w++) running += cnt[w * RADIX_MAX_BINS + d];
             count[q] = running;
             gcount[q] = ghist[d];
-            // publish this tile's count as early as possible
             u32 word = running | (tile == 0 ? RADIX_FLAG_INCL : RADIX_FLAG_AGG);
             *(volatile u32*)&status[(u64)tile * bins + d] = word;
         }
@@ -157,8 +153,48 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
     for (int w = 0; w < RADIX_WARPS; w++)
         if (w < warp) { toff += s_warp_sums[0][w]; goff += s_warp_sums[1][w]; }
     u32 texcl = toff + tinc - tsum, gexcl = goff + ginc - gsum;
+    // cnt[w][d] := staged position of warp w's first key of digit d; dig_excl[d] := first staged position of d
+    u32 gex[2] = {0, 0};
+#pragma unroll
+    for (u32 q = 0; q < 2; q++) {
+        u32 d = d0 + q;
+        if (q < dpt && d < bins) {
+            u32 running = texcl;
+#pragma unroll
+            for (int w = 0; w < RADIX_WARPS; w++) {
+                u32 c = cnt[w * RADIX_MAX_BINS + d];
+                cnt[w * RADIX_MAX_BINS + d] = running;
+                running += c;
+            }
+            dig_excl[d] = texcl;
+            gex[q] = gexcl;
+            texcl += count[q];
+            gexcl += gcount[q];
+        }
+    }
+    __syncthreads();
 
-    // decoupled look-back, one digit at a time per thread
+    // stable ranking inside the warp (match on the digit), keys go straight to their staged position
+    const u32 lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int k = 0; k < RADIX_ITEMS; k++) {
+        u32 j = wbase + k * 32;
+        bool valid = j < tile_n;
+        u32 d = valid ? ((u32)(key[k] >> shift) & mask) : bins;  // invalid lanes form their own match group
+        u32 peers = __match_any_sync(0xFFFFFFFFu, d);
+        u32 lower = __popc(peers & lt);
+        u32 before = valid ? wcnt[d] : 0u;
+        __syncwarp();
+        if (valid && lower == 0) wcnt[d] = before + __popc(peers);
+        __syncwarp();
+        if (valid) {
+            skeys[before + lower] = key[k];
+            if (PAIRS) svals[before + lower] = vals_in[tbase + j];
+        }
+    }
+
+    // decoupled look-back, one digit at a time per thread (the tiles before us had the whole ranking phase
+    // to publish)
 #pragma unroll
     for (u32 q = 0; q < 2; q++) {
         u32 d = d0 + q;
@@ -175,22 +211,7 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
                 }
                 *(volatile u32*)&status[(u64)tile * bins + d] = ((prev + count[q]) & RADIX_COUNT_MASK) | RADIX_FLAG_INCL;
             }
-            dig_excl[d] = texcl;
-            gbase[d] = gexcl + prev - texcl;   // global slot of staged position j of this digit: gbase[d] + j
-            texcl += count[q];
-            gexcl += gcount[q];
-        }
-    }
-    __syncthreads();
-
-#pragma unroll
-    for (int k = 0; k < RADIX_ITEMS; k++) {
-        u32 j = wbase + k * 32;
-        if (j < tile_n) {
-            u32 d = (u32)(key[k] >> shift) & mask;
-            u32 p = dig_excl[d] + wcnt[d] + rank[k];
-            skeys[p] = key[k];
-            if (PAIRS) svals[p] = vals_in[tbase + j];
+            gbase[d] = gex[q] + prev - dig_excl[d];   // global slot of staged position j of this digit: gbase[d] + j
         }
     }
     __syncthreads();
@@ -218,11 +239,7 @@ struct RadixTemp {
 template <bool PAIRS, class Prof>
 static inline int radix_sort(u64* k0, u32* v0, u64* k1, u32* v1, u32 n, const RadixPlan& plan, RadixTemp& tmp,
                              cudaStream_t st, Prof& prof) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_onesweep<PAIRS>, cudaFuncAttributeMaxDynamicSharedMemorySize, RadixSmem<PAIRS>::bytes);
-        attr_set = true;
-    }
+    cudaFuncSetAttribute(k_onesweep<PAIRS>, cudaFuncAttributeMaxDynamicSharedMemorySize, RadixSmem<PAIRS>::bytes);
     int cur = 0;
     if (n < 2) return 0;
     const u32 ntiles = div_up(n, RADIX_TILE);

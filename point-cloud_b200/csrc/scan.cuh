@@ -206,8 +206,56 @@ __device__ __forceinline__ State ldcg_state(const State* p) {
     return r;
 }
 
-template <class Op, int THREADS, int ITEMS>
-__global__ void __launch_bounds__(THREADS) k_chain_scan(Op op, u32 n, u32 ntiles, ChainTemp<typename Op::State> tmp) {
+// Warp-wide look-back of tile `tile` (call with all 32 lanes of ONE warp): publishes `total` as the tile's
+// aggregate, folds the predecessors, publishes the inclusive prefix and returns the exclusive one (all lanes).
+template <class Op>
+__device__ __forceinline__ typename Op::State chain_lookback(const Op& op, const ChainTemp<typename Op::State>& tmp,
+                                                             u32 tile, const typename Op::State& total) {
+    typedef typename Op::State State;
+    const int lane = threadIdx.x & 31;
+    if (lane == 0) {
+        if (tile == 0) {
+            tmp.incl[0] = total;
+            st_release_u32(tmp.flag, 2u);
+        } else {
+            tmp.agg[tile] = total;
+            st_release_u32(tmp.flag + tile, 1u);
+        }
+    }
+    State prefix = op.identity();
+    if (tile > 0) {
+        int look = (int)tile - 1;
+        for (;;) {
+            int t = look - lane;
+            u32 f = 2u;
+            State s = op.identity();
+            if (t >= 0) {
+                do { f = ld_acquire_u32(tmp.flag + t); } while (f == 0u);
+                s = ldcg_state((f == 2u) ? tmp.incl + t : tmp.agg + t);
+            }
+            const u32 m = __ballot_sync(0xFFFFFFFFu, f == 2u);
+            const int last = m ? (__ffs(m) - 1) : 31;
+            if (lane > last) s = op.identity();
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {   // ordered fold: farther tiles (higher lanes) on the left
+                State o = shfl_down_state(s, d);
+                if (lane + d < 32) s = op.combine(o, s);
+            }
+            s = shfl_state(s, 0);
+            prefix = op.combine(s, prefix);
+            if (m) break;
+            look -= 32;
+        }
+        if (lane == 0) {
+            tmp.incl[tile] = op.combine(prefix, total);
+            st_release_u32(tmp.flag + tile, 2u);
+        }
+    }
+    return prefix;
+}
+
+template <class Op, int THREADS, int ITEMS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 ntiles, ChainTemp<typename Op::State> tmp) {
     typedef typename Op::State State;
     constexpr int WARPS = THREADS / 32;
     __shared__ State s_warp[WARPS];
@@ -251,44 +299,7 @@ __global__ void __launch_bounds__(THREADS) k_chain_scan(Op op, u32 n, u32 ntiles
     texcl = op.combine(wpre, texcl);   // exclusive prefix of this thread inside the tile
 
     if (warp == 0) {
-        if (lane == 0) {
-            if (tile == 0) {
-                tmp.incl[0] = total;
-                st_release_u32(tmp.flag, 2u);
-            } else {
-                tmp.agg[tile] = total;
-                st_release_u32(tmp.flag + tile, 1u);
-            }
-        }
-        State prefix = op.identity();
-        if (tile > 0) {
-            int look = (int)tile - 1;
-            for (;;) {
-                int t = look - lane;
-                u32 f = 2u;
-                State s = op.identity();
-                if (t >= 0) {
-                    do { f = ld_acquire_u32(tmp.flag + t); } while (f == 0u);
-                    s = ldcg_state((f == 2u) ? tmp.incl + t : tmp.agg + t);
-                }
-                const u32 m = __ballot_sync(0xFFFFFFFFu, f == 2u);
-                const int last = m ? (__ffs(m) - 1) : 31;
-                if (lane > last) s = op.identity();
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {   // ordered fold: farther tiles (higher lanes) on the left
-                    State o = shfl_down_state(s, d);
-                    if (lane + d < 32) s = op.combine(o, s);
-                }
-                s = shfl_state(s, 0);
-                prefix = op.combine(s, prefix);
-                if (m) break;
-                look -= 32;
-            }
-            if (lane == 0) {
-                tmp.incl[tile] = op.combine(prefix, total);
-                st_release_u32(tmp.flag + tile, 2u);
-            }
-        }
+        State prefix = chain_lookback(op, tmp, tile, total);
         if (lane == 0) s_prefix = prefix;
     }
     __syncthreads();
@@ -306,14 +317,14 @@ __global__ void __launch_bounds__(THREADS) k_chain_scan(Op op, u32 n, u32 ntiles
 }
 
 // Host launcher: `temp` must hold ChainTemp<State>::bytes(ntiles) bytes.  Returns launches (memset excluded).
-template <class Op, int THREADS, int ITEMS>
+template <class Op, int THREADS, int ITEMS, int MINB = 1>
 static inline int chain_scan(const Op& op, u32 n, void* temp, cudaStream_t st) {
     typedef typename Op::State State;
     const u32 ntiles = div_up(n, THREADS * ITEMS);
     if (!ntiles) return 0;
     ChainTemp<State> t = ChainTemp<State>::carve(temp, ntiles);
     cudaMemsetAsync(t.flag, 0, ChainTemp<State>::flag_bytes(ntiles), st);
-    k_chain_scan<Op, THREADS, ITEMS><<<ntiles, THREADS, 0, st>>>(op, n, ntiles, t);
+    k_chain_scan<Op, THREADS, ITEMS, MINB><<<ntiles, THREADS, 0, st>>>(op, n, ntiles, t);
     return 1;
 }
 template <class State, int THREADS, int ITEMS>
