@@ -48,6 +48,8 @@ def cpu_oracle_run(n_points, extent, threads, seed=2):
 
 
 class ClockSampler:
+    """nvidia-smi clock / throttle-reason samples.  The process is started BEFORE the warm-up (NVML start-up
+    stalls CUDA calls for a while) and only lines that arrive inside [mark_start, mark_end] are used."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -55,27 +57,44 @@ class ClockSampler:
     def __init__(self, index):
         self.proc = None
         self.index = index
+        self.lines = []
+        self.t0 = self.t1 = None
 
     def start(self):
+        import threading
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
+            return
+
+        def reader():
+            for line in self.proc.stdout:
+                self.lines.append((time.time(), line))
+        self.thread = threading.Thread(target=reader, daemon=True)
+        self.thread.start()
+
+    def mark_start(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
 
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
         try:
-            out, _ = self.proc.communicate(timeout=5)
+            self.proc.wait(timeout=5)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-            out, _ = self.proc.communicate()
+        self.thread.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.splitlines():
+        inside = [l for (t, l) in self.lines if self.t0 is None or (self.t0 <= t <= (self.t1 or t) + 0.25)]
+        for line in (inside or [l for _, l in self.lines[-3:]]):
             f = [x.strip() for x in line.split(",")]
             if len(f) < 7:
                 continue
@@ -175,16 +194,21 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for _ in range(args.warmup):
         step()
-    sampler = ClockSampler(local_rank)
     barrier()
-    sampler.start()
+    sampler.mark_start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches, kstats, last = 0, {}, None
+    step_evs = []
     ev0.record(stream)
     for _ in range(args.steps):
         last, ks = step()
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(stream)
+        step_evs.append(e)
         launches += last.gpu_launches
         for k in ks:
             d = kstats.setdefault(k["name"], dict(launches=0, units=0, bytes=0, ms=0.0))
@@ -192,8 +216,10 @@ def main():
                 d[f] += k[f]
     ev1.record(stream)
     barrier()
+    sampler.mark_end()
     clocks = sampler.stop()
     ms = ev0.elapsed_time(ev1)
+    step_ms = [round(a.elapsed_time(b), 2) for a, b in zip([ev0] + step_evs[:-1], step_evs)]
     if world > 1:
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -271,7 +297,7 @@ def main():
                                       f"(5000/96/1000.0), batch 10000", "points_per_gpu": n,
                           "l2": "inputs (1.6 GB/step) larger than L2, no explicit flush",
                           "levels": int(last.levels_built), "arrivals_per_point": round(last.arrivals / n, 3),
-                          "nodes": int(last.nodes_written), "sharding": "disjoint level-0 cell blocks per rank"},
+                          "nodes": int(last.nodes_written), "sharding": "disjoint level-0 cell blocks per rank", "step_ms": step_ms},
                "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
                "clocks": clocks}
         print(json.dumps(out))

@@ -408,7 +408,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     u32 ncell_ub = (u32)std::min<u64>(n0, vol);
     u32* cell_start = dalloc<u32>((u64)ncell_ub + 1);
     int* cell_idx = dalloc<int>(3ull * ncell_ub);
-    void* scan_tmp = dalloc<unsigned char>(chain_scan_temp_bytes<u32, 256, 8>(n0));
+    void* scan_tmp = dalloc<unsigned char>(chain_scan_temp_bytes<256, 8>(n0));
     L0HeadOp hop{ks, n0, pb0, box, cell_start, cell_idx, &d_scr->ncell};
     pb();
     int nl = chain_scan<L0HeadOp, 256, 8>(hop, n0, scan_tmp, st);
@@ -578,9 +578,9 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     // ---- stage 4: contest
     u32* win_src = dalloc<u32>(n);
     u32* win_end = dalloc<u32>(ncell);
-    const u64 tmp_bytes = std::max<u64>(std::max<u64>(chain_scan_temp_bytes<ContestState, 256, 8>(n),
-                                                      chain_scan_temp_bytes<Oct8, OCT_THREADS, OCT_ITEMS>(n)),
-                                        chain_scan_temp_bytes<CellScanState, 256, 4>(ncell));
+    const u64 tmp_bytes = std::max<u64>(std::max<u64>(chain_scan_temp_bytes<256, 8>(n),
+                                                      chain_scan_temp_bytes<OCT_THREADS, OCT_ITEMS>(n)),
+                                        chain_scan_temp_bytes<256, 4>(ncell));
     void* scan_tmp = dalloc<unsigned char>(tmp_bytes);
     ContestOp<PAIRS> cop{ks, vs, n, lay, g, pts, cellbase, cell_idx, cell_start, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
     pb();

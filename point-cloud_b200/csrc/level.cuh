@@ -120,6 +120,11 @@ struct L0HeadOp {
     u32* cell_start;  // [ncell + 1]
     int* cell_idx;    // [ncell * 3]
     u32* ncell_out;
+    __device__ static void pack(const State& s, u32 status, uint4& a, uint4& b) {
+        a = make_uint4(s, 0u, 0u, status);
+        b = make_uint4(0u, 0u, 0u, status);
+    }
+    __device__ static State unpack(const uint4& a, const uint4&) { return a.x; }
     __device__ State identity() const { return 0; }
     __device__ State load(u32 i) const { return (i == 0 || (keys[i] >> pb) != (keys[i - 1] >> pb)) ? 1u : 0u; }
     __device__ State combine(const State& a, const State& b) const { return a + b; }
@@ -270,6 +275,13 @@ struct ContestOp {
     u32* win_end;  // [ncell] end of the cell's winners in win_src
     u32* nwin_out;
     u32* err;
+    __device__ static void pack(const State& s, u32 status, uint4& a, uint4& b) {
+        a = make_uint4((u32)s.mn, (u32)(s.mn >> 32), s.meta, s.ntail | status);   // ntail < 2^30
+        b = make_uint4(0u, 0u, 0u, status);
+    }
+    __device__ static State unpack(const uint4& a, const uint4&) {
+        return State{((u64)a.y << 32) | a.x, a.z, a.w & ~PCB_DESC_MASK};
+    }
     __device__ u64 gid(u64 key) const { return PAIRS ? key : (key >> lay.pb); }
     __device__ State identity() const { return State{~0ull, 0u, 0u}; }
     __device__ State load(u32 j) const {
@@ -352,6 +364,17 @@ struct OctScanOp {
     u32* rank;     // [n] rank of the loser emitted at this position inside its bucket (new losers only)
     u32* bcnt;     // [ncell * 8] new losers per bucket
     u32* special;  // [ncell * 8][4] trigger batch (+1) at ranks 0, L-1, L, and (merge) max(L-1-m0, 0)
+    __device__ static void pack(const State& s, u32 status, uint4& a, uint4& b) {   // counters < 2^30
+        a = make_uint4(s.c[0], s.c[1], s.c[2], s.c[3] | status);
+        b = make_uint4(s.c[4], s.c[5], s.c[6] | ((s.head & 1u) << 31), s.c[7] | status);
+    }
+    __device__ static State unpack(const uint4& a, const uint4& b) {
+        State s;
+        s.c[0] = a.x; s.c[1] = a.y; s.c[2] = a.z; s.c[3] = a.w & ~PCB_DESC_MASK;
+        s.c[4] = b.x; s.c[5] = b.y; s.c[6] = b.z & 0x7FFFFFFFu; s.c[7] = b.w & ~PCB_DESC_MASK;
+        s.head = b.z >> 31;
+        return s;
+    }
     __device__ State identity() const {
         State s;
 #pragma unroll
@@ -427,13 +450,13 @@ __device__ __forceinline__ OctPacked oct_combine(const OctPacked& a, const OctPa
     return r;
 }
 __global__ void __launch_bounds__(OCT_THREADS)
-k_octscan(OctScanOp op, u32 n, u32 ntiles, ChainTemp<Oct8> tmp) {
+k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     constexpr int WARPS = OCT_THREADS / 32;
     __shared__ OctPacked s_warp[WARPS];
     __shared__ Oct8 s_prefix;
     __shared__ u32 s_tile;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(tmp.flag + ntiles, 1u);
+    if (tid == 0) s_tile = atomicAdd((u32*)(desc + 2 * (u64)ntiles), 1u);
     __syncthreads();
     const u32 tile = s_tile;
     const u64 base = (u64)tile * OCT_TILE + (u64)tid * OCT_ITEMS;
@@ -500,7 +523,7 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, ChainTemp<Oct8> tmp) {
             tot8.c[4 + k] = (u32)(total.hi >> (16 * k)) & 0xFFFFu;
         }
         tot8.head = total.head;
-        Oct8 prefix = chain_lookback(op, tmp, tile, tot8);
+        Oct8 prefix = chain_lookback(op, desc, tile, tot8);
         if (lane == 0) s_prefix = prefix;
     }
     __syncthreads();
@@ -562,9 +585,8 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, ChainTemp<Oct8> tmp) {
 static inline int octscan(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
     const u32 ntiles = div_up(n, OCT_TILE);
     if (!ntiles) return 0;
-    ChainTemp<Oct8> t = ChainTemp<Oct8>::carve(temp, ntiles);
-    cudaMemsetAsync(t.flag, 0, ChainTemp<Oct8>::flag_bytes(ntiles), st);
-    k_octscan<<<ntiles, OCT_THREADS, 0, st>>>(op, n, ntiles, t);
+    cudaMemsetAsync(temp, 0, chain_temp_bytes(ntiles), st);
+    k_octscan<<<ntiles, OCT_THREADS, 0, st>>>(op, n, ntiles, (uint4*)temp);
     return 1;
 }
 
@@ -663,6 +685,13 @@ struct CellScanOp {
     u32* cell_cbase;
     u64* node_off;
     LevelTotals* totals;
+    __device__ static void pack(const State& s, u32 status, uint4& a, uint4& b) {
+        a = make_uint4((u32)s.bytes, (u32)(s.bytes >> 32), s.deliver, status);
+        b = make_uint4(s.children, 0u, 0u, status);
+    }
+    __device__ static State unpack(const uint4& a, const uint4& b) {
+        return State{((u64)a.y << 32) | a.x, a.z, b.x};
+    }
     __device__ State identity() const { return State{0ull, 0u, 0u}; }
     __device__ State load(u32 i) const {
         return State{(cell_bytes[i] + 15ull) & ~15ull, cell_deliver[i], cell_children[i]};

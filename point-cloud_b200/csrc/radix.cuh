@@ -202,12 +202,22 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
             u32 prev = 0;
             if (tile > 0) {
                 int t = (int)tile - 1;
-                for (;;) {
-                    u32 s;
-                    do { s = *(volatile const u32*)&status[(u64)t * bins + d]; } while ((s & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u);
-                    prev += s & RADIX_COUNT_MASK;
-                    if (s & RADIX_FLAG_INCL) break;
-                    t--;
+                bool done = false;
+                while (!done) {   // 8 predecessors per step: their status words are independent loads
+                    u32 w[8];
+#pragma unroll
+                    for (int x = 0; x < 8; x++)
+                        w[x] = (t - x >= 0) ? *(volatile const u32*)&status[(u64)(t - x) * bins + d] : RADIX_FLAG_INCL;
+#pragma unroll
+                    for (int x = 0; x < 8; x++) {
+                        if (!done) {
+                            u32 s = w[x];
+                            while ((s & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u) s = *(volatile const u32*)&status[(u64)(t - x) * bins + d];
+                            prev += s & RADIX_COUNT_MASK;
+                            done = (s & RADIX_FLAG_INCL) != 0u;
+                        }
+                    }
+                    t -= 8;
                 }
                 *(volatile u32*)&status[(u64)tile * bins + d] = ((prev + count[q]) & RADIX_COUNT_MASK) | RADIX_FLAG_INCL;
             }

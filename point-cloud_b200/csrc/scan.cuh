@@ -142,22 +142,8 @@ struct SumOp {
 // Op interface as above, except
 //   __device__ void consume(u32 i, const State& excl, const State& incl, const State& self) const;
 // (`self` = load(i), kept in registers: load may be expensive, e.g. a gather).
-template <class State>
-struct ChainTemp {
-    State* agg;    // [ntiles]
-    State* incl;   // [ntiles]
-    u32* flag;     // [ntiles + 1]: 0 nothing, 1 aggregate, 2 inclusive prefix; [ntiles] = tile counter
-    static u64 bytes(u64 ntiles) { return (2 * sizeof(State) + 4) * (ntiles + 1) + 64; }
-    static ChainTemp carve(void* p, u64 ntiles) {
-        ChainTemp t;
-        t.flag = (u32*)p;                                       // flags first: one memset clears them
-        u64 off = ((ntiles + 1) * 4 + 15) & ~15ull;
-        t.agg = (State*)((unsigned char*)p + off);
-        t.incl = t.agg + ntiles;
-        return t;
-    }
-    static u64 flag_bytes(u64 ntiles) { return (ntiles + 1) * 4; }
-};
+// temp layout of a chained scan: uint4 desc[2 * ntiles], then the u32 tile counter; all zero at launch
+static inline u64 chain_temp_bytes(u64 ntiles) { return 32 * ntiles + 16; }
 
 __device__ __forceinline__ u32 ld_acquire_u32(const u32* p) {
     u32 v;
@@ -206,34 +192,53 @@ __device__ __forceinline__ State ldcg_state(const State* p) {
     return r;
 }
 
+// Tile descriptor of the chained scans: 32 bytes = two 16-byte words, each carrying the status (0 nothing,
+// 1 aggregate, 2 inclusive prefix) in bits 30-31 of its .w, so that data and status travel in the same
+// memory transaction: no fence, no L1 invalidation, one volatile 16-byte load per word and poll.
+// Every Op supplies   static void pack(const State&, u32 status, uint4& a, uint4& b)   (status already
+// shifted: PCB_DESC_AGG / PCB_DESC_INCL OR-ed into a.w and b.w by pack) and   static State unpack(a, b).
+#define PCB_DESC_AGG 0x40000000u
+#define PCB_DESC_INCL 0x80000000u
+#define PCB_DESC_MASK 0xC0000000u
+__device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_v4(uint4* p, const uint4& v) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 // Warp-wide look-back of tile `tile` (call with all 32 lanes of ONE warp): publishes `total` as the tile's
 // aggregate, folds the predecessors, publishes the inclusive prefix and returns the exclusive one (all lanes).
 template <class Op>
-__device__ __forceinline__ typename Op::State chain_lookback(const Op& op, const ChainTemp<typename Op::State>& tmp,
-                                                             u32 tile, const typename Op::State& total) {
+__device__ __forceinline__ typename Op::State chain_lookback(const Op& op, uint4* __restrict__ desc, u32 tile,
+                                                             const typename Op::State& total) {
     typedef typename Op::State State;
     const int lane = threadIdx.x & 31;
     if (lane == 0) {
-        if (tile == 0) {
-            tmp.incl[0] = total;
-            st_release_u32(tmp.flag, 2u);
-        } else {
-            tmp.agg[tile] = total;
-            st_release_u32(tmp.flag + tile, 1u);
-        }
+        uint4 a, b;
+        Op::pack(total, tile == 0 ? PCB_DESC_INCL : PCB_DESC_AGG, a, b);
+        st_volatile_v4(desc + 2 * (u64)tile, a);
+        st_volatile_v4(desc + 2 * (u64)tile + 1, b);
     }
     State prefix = op.identity();
     if (tile > 0) {
         int look = (int)tile - 1;
         for (;;) {
             int t = look - lane;
-            u32 f = 2u;
+            u32 f = PCB_DESC_INCL;
             State s = op.identity();
             if (t >= 0) {
-                do { f = ld_acquire_u32(tmp.flag + t); } while (f == 0u);
-                s = ldcg_state((f == 2u) ? tmp.incl + t : tmp.agg + t);
+                uint4 a, b;
+                do {   // both words of one publication (a reader may catch the writer between its two stores)
+                    a = ld_volatile_v4(desc + 2 * (u64)t);
+                    b = ld_volatile_v4(desc + 2 * (u64)t + 1);
+                    f = a.w & PCB_DESC_MASK;
+                } while (f == 0u || f != (b.w & PCB_DESC_MASK));
+                s = Op::unpack(a, b);
             }
-            const u32 m = __ballot_sync(0xFFFFFFFFu, f == 2u);
+            const u32 m = __ballot_sync(0xFFFFFFFFu, f == PCB_DESC_INCL);
             const int last = m ? (__ffs(m) - 1) : 31;
             if (lane > last) s = op.identity();
 #pragma unroll
@@ -247,22 +252,24 @@ __device__ __forceinline__ typename Op::State chain_lookback(const Op& op, const
             look -= 32;
         }
         if (lane == 0) {
-            tmp.incl[tile] = op.combine(prefix, total);
-            st_release_u32(tmp.flag + tile, 2u);
+            uint4 a, b;
+            Op::pack(op.combine(prefix, total), PCB_DESC_INCL, a, b);
+            st_volatile_v4(desc + 2 * (u64)tile, a);
+            st_volatile_v4(desc + 2 * (u64)tile + 1, b);
         }
     }
     return prefix;
 }
 
 template <class Op, int THREADS, int ITEMS, int MINB>
-__global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 ntiles, ChainTemp<typename Op::State> tmp) {
+__global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     typedef typename Op::State State;
     constexpr int WARPS = THREADS / 32;
     __shared__ State s_warp[WARPS];
     __shared__ State s_prefix;
     __shared__ u32 s_tile;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(tmp.flag + ntiles, 1u);
+    if (tid == 0) s_tile = atomicAdd((u32*)(desc + 2 * (u64)ntiles), 1u);
     __syncthreads();
     const u32 tile = s_tile;
     const u64 base = (u64)tile * (THREADS * ITEMS) + (u64)tid * ITEMS;
@@ -299,7 +306,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 
     texcl = op.combine(wpre, texcl);   // exclusive prefix of this thread inside the tile
 
     if (warp == 0) {
-        State prefix = chain_lookback(op, tmp, tile, total);
+        State prefix = chain_lookback(op, desc, tile, total);
         if (lane == 0) s_prefix = prefix;
     }
     __syncthreads();
@@ -316,18 +323,16 @@ __global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 
     if (tile == ntiles - 1 && tid == THREADS - 1) op.finish(op.combine(s_prefix, total));
 }
 
-// Host launcher: `temp` must hold ChainTemp<State>::bytes(ntiles) bytes.  Returns launches (memset excluded).
+// Host launcher: `temp` must hold chain_temp_bytes(ntiles) bytes.  Returns launches (memset excluded).
 template <class Op, int THREADS, int ITEMS, int MINB = 1>
 static inline int chain_scan(const Op& op, u32 n, void* temp, cudaStream_t st) {
-    typedef typename Op::State State;
     const u32 ntiles = div_up(n, THREADS * ITEMS);
     if (!ntiles) return 0;
-    ChainTemp<State> t = ChainTemp<State>::carve(temp, ntiles);
-    cudaMemsetAsync(t.flag, 0, ChainTemp<State>::flag_bytes(ntiles), st);
-    k_chain_scan<Op, THREADS, ITEMS, MINB><<<ntiles, THREADS, 0, st>>>(op, n, ntiles, t);
+    cudaMemsetAsync(temp, 0, chain_temp_bytes(ntiles), st);
+    k_chain_scan<Op, THREADS, ITEMS, MINB><<<ntiles, THREADS, 0, st>>>(op, n, ntiles, (uint4*)temp);
     return 1;
 }
-template <class State, int THREADS, int ITEMS>
+template <int THREADS, int ITEMS>
 static inline u64 chain_scan_temp_bytes(u64 n) {
-    return ChainTemp<State>::bytes((n + (u64)THREADS * ITEMS - 1) / ((u64)THREADS * ITEMS));
+    return chain_temp_bytes((n + (u64)THREADS * ITEMS - 1) / ((u64)THREADS * ITEMS));
 }
