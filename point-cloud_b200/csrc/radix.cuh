@@ -81,7 +81,7 @@ struct RadixSmem {
 };
 
 template <bool PAIRS>
-__global__ void __launch_bounds__(RADIX_THREADS)
+__global__ void __launch_bounds__(RADIX_THREADS, PAIRS ? 3 : 4)
 k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u32* __restrict__ vals_in,
            u32* __restrict__ vals_out, u32 n, int shift, int bits, const u32* __restrict__ ghist /* [bins] */,
            u32* __restrict__ status /* [ntiles][bins] */, u32* __restrict__ counter) {
@@ -250,6 +250,7 @@ template <bool PAIRS, class Prof>
 static inline int radix_sort(u64* k0, u32* v0, u64* k1, u32* v1, u32 n, const RadixPlan& plan, RadixTemp& tmp,
                              cudaStream_t st, Prof& prof) {
     cudaFuncSetAttribute(k_onesweep<PAIRS>, cudaFuncAttributeMaxDynamicSharedMemorySize, RadixSmem<PAIRS>::bytes);
+    cudaFuncSetAttribute(k_onesweep<PAIRS>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
     int cur = 0;
     if (n < 2) return 0;
     const u32 ntiles = div_up(n, RADIX_TILE);
