@@ -48,33 +48,64 @@ def cpu_oracle_run(n_points, extent, threads, seed=2):
 
 
 class ClockSampler:
-    """nvidia-smi clock / throttle-reason samples.  The process is started BEFORE the warm-up (NVML start-up
-    stalls CUDA calls for a while) and only lines that arrive inside [mark_start, mark_end] are used."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock / throttle-reason samples DURING the timed region, read through NVML in a thread of this
+    process (an `nvidia-smi -lms` child was measured to stall the CUDA calls of the timed steps for up to
+    500 ms at a time; in-process NVML queries do not).  Falls back to a slow nvidia-smi loop."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index):
-        self.proc = None
         self.index = index
-        self.lines = []
+        self.samples = []   # (time, sm_mhz, max_mhz, reason bits)
         self.t0 = self.t1 = None
+        self.stop_flag = False
+        self.thread = None
+        self.mode = None
+
+    def _nvml_loop(self):
+        import pynvml as nv
+        h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((time.time(), float(sm), float(mx), int(rs)))
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def _smi_loop(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        bits = [0x8, 0x40, 0x20, 0x4]
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=10).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                rs = sum(b for b, v in zip(bits, f[2:6]) if v.lower().startswith("active"))
+                self.samples.append((time.time(), float(f[0]), float(f[1]), rs))
+            except Exception:
+                pass
+            time.sleep(1.0)
 
     def start(self):
         import threading
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except OSError:
-            self.proc = None
-            return
-
-        def reader():
-            for line in self.proc.stdout:
-                self.lines.append((time.time(), line))
-        self.thread = threading.Thread(target=reader, daemon=True)
+            import pynvml as nv
+            nv.nvmlInit()
+            target, self.mode = self._nvml_loop, "nvml"
+        except Exception:
+            target, self.mode = self._smi_loop, "nvidia-smi"
+        self.thread = threading.Thread(target=target, daemon=True)
         self.thread.start()
+        for _ in range(100):   # NVML start-up is over once the first sample is in
+            if self.samples:
+                break
+            time.sleep(0.05)
 
     def mark_start(self):
         self.t0 = time.time()
@@ -83,31 +114,20 @@ class ClockSampler:
         self.t1 = time.time()
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        self.thread.join(timeout=2)
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        inside = [l for (t, l) in self.lines if self.t0 is None or (self.t0 <= t <= (self.t1 or t) + 0.25)]
-        for line in (inside or [l for _, l in self.lines[-3:]]):
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 7:
-                continue
-            try:
-                sm.append(float(f[0]))
-                mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
+        if not self.thread:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["sampler not started"]}
+        self.stop_flag = True
+        self.thread.join(timeout=12)
+        inside = [x for x in self.samples if self.t0 is None or self.t0 <= x[0] <= (self.t1 or x[0])]
+        use = inside or self.samples[-3:]
+        reasons = set()
+        for x in use:
+            for bit, nm in self.REASONS.items():
+                if x[3] & bit:
                     reasons.add(nm)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        sm = [x[1] for x in use]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max((x[2] for x in use), default=None),
+                "samples": len(inside), "source": self.mode, "reasons": sorted(reasons)}
 
 
 def run_reference(args, rank, world):
@@ -147,6 +167,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-scale", type=float, default=1.0, help="scales the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-clocks", action="store_true", help="debug: do not run the nvidia-smi sampler")
+    ap.add_argument("--host-log", action="store_true", help="debug: per-step host times (open, finish, close) on stderr")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -177,17 +199,24 @@ def main():
     torch.cuda.synchronize()
     stream = torch.cuda.current_stream()
 
+    host_log = []
+
     def step(profile=True):
         flags = pcb.FLAG_DEVICE_ONLY | (pcb.FLAG_PROFILE if profile else 0)
+        t0 = time.perf_counter()
         cv = pcb.Converter(None, device=local_rank, flags=flags)
         try:
             cv.set_stream(stream.cuda_stream)
             cv.begin_file()
             cv.add_points_device(pts.data_ptr(), n)
+            t1 = time.perf_counter()
             st = cv.finish()
+            t2 = time.perf_counter()
             return st, cv.kernel_stats()
         finally:
             cv.close()
+            host_log.append((round((t1 - t0) * 1e3, 2), round((t2 - t1) * 1e3, 2),
+                             round((time.perf_counter() - t2) * 1e3, 2)))
 
     def barrier():
         if world > 1:
@@ -195,7 +224,8 @@ def main():
         torch.cuda.synchronize()
 
     sampler = ClockSampler(local_rank)
-    sampler.start()
+    if not args.no_clocks:
+        sampler.start()
     for _ in range(args.warmup):
         step()
     barrier()
@@ -225,6 +255,8 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     ms_per_step = ms / args.steps
+    if args.host_log:
+        print("host_log (open, finish, close) ms:", host_log[-args.steps:], file=sys.stderr)
     value = n * world / (ms_per_step * 1e-3) / 1e6
 
     # ---- e2e: host buffers through the C ABI (H2D + build + D2H of every node image)

@@ -327,6 +327,8 @@ static LevelGeom make_geom(float max_cell_size, u32 dim, u32 h) {
     g.my = (int)(((1u << g.by) - ry) / 2);
     g.mz = (int)(((1u << g.bz) - rz) / 2);
     g.hexbits = g.bx + g.by + g.bz;
+    g.half_sqrt3 = 1.73205080757f / 2.0f;          // hex.rs:60  SQRT_3 / 2.0
+    g.row_pitch = (g.R * 3.0f) / 2.0f;             // hex.rs:61  cell_radius * 3.0 / 2.0
     return g;
 }
 
@@ -553,7 +555,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     const RadixPlan plan = radix_plan(lay.pb, lay.cb + lay.hexbits);
 
     // ---- stages 1-2: hex keys (+ the digit histograms of every pass)
-    int* cellbase = dalloc<int>(3ull * ncell);
+    CellGeo* geo = dalloc<CellGeo>(ncell);
     u64 *kA = dalloc<u64>(n), *kB = dalloc<u64>(n);
     u32 *vA = PAIRS ? dalloc<u32>(n) : nullptr, *vB = PAIRS ? dalloc<u32>(n) : nullptr;
     RadixTemp rt;
@@ -562,8 +564,8 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     rt.status = rt.ghist + RadixTemp::ghist_words();
     CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
     pb();
-    k_cellbase<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, ncell, g, cellbase);
-    k_hexkey<PAIRS><<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, cellbase, g, lay,
+    k_cellgeo<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, cell_start, ncell, g, geo);
+    k_hexkey<PAIRS><<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay,
                                                                             plan, kA, vA, rt.ghist, &d_scr->err);
     pe("hexkey", 2, n, (PAIRS ? 28ull : 24ull) * n);
     trace_mark(st, "hexkey", h, n);
@@ -582,9 +584,11 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                                                       chain_scan_temp_bytes<OCT_THREADS, OCT_ITEMS>(n)),
                                         chain_scan_temp_bytes<256, 4>(ncell));
     void* scan_tmp = dalloc<unsigned char>(tmp_bytes);
-    ContestOp<PAIRS> cop{ks, vs, n, lay, g, pts, cellbase, cell_idx, cell_start, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
+    ContestOp<PAIRS> cop{ks, vs, n, lay, g, pts, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
     pb();
-    int nl = chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, n, scan_tmp, st);
+    static const int contest_minb = getenv("PCB_CONTEST_MINB") ? atoi(getenv("PCB_CONTEST_MINB")) : 3;  // tuning hook
+    int nl = contest_minb == 4 ? chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, n, scan_tmp, st)
+                               : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, n, scan_tmp, st);
     pe("contest", nl, n, (PAIRS ? 36ull : 32ull) * n);
     trace_mark(st, "contest", h, n);
 
@@ -672,7 +676,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     levels.push_back(img);
 
     // ---- hand over to the next level
-    dfree(cellbase); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
+    dfree(geo); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
     dfree(win_src); dfree(win_end); dfree(rank); dfree(bcnt); dfree(special); dfree(bdst);
     dfree(cell_deliver); dfree(cell_children); dfree(cell_dbase); dfree(cell_cbase); dfree(cell_bytes); dfree(node_off);
     dfree(ex_state); dfree(ex_m0); dfree(ex_pts); dfree(ex_bucket); dfree(ex_rank);

@@ -67,13 +67,16 @@ __device__ __forceinline__ HexKey hex_from_world(float px, float py, float pz, f
     return k;
 }
 
-// hex.rs:18-24 then :55-65, then cell.rs:77-78 distance_squared(centre, p)
-__device__ __forceinline__ float hex_d2(HexKey k, float px, float py, float pz, float R) {
+// hex.rs:18-24 then :55-65, then cell.rs:77-78 distance_squared(centre, p).
+// half_sqrt3 = SQRT_3 / 2.0 and row_pitch = (R * 3.0) / 2.0 are the reference's own sub-expressions, evaluated
+// once per level with the same single IEEE operations.
+__device__ __forceinline__ float hex_d2(HexKey k, float px, float py, float pz, float R, float half_sqrt3,
+                                        float row_pitch) {
     i32 e = (i32)((u32)k.y - (u32)(k.y & 1));
     i32 q = (i32)((u32)k.x - (u32)(e / 2));
     float qf = (float)q, rf = (float)k.y, hf = (float)k.z;
-    float cx = __fmul_rn(R, __fadd_rn(__fmul_rn(PCB_SQRT_3, qf), __fmul_rn(__fdiv_rn(PCB_SQRT_3, 2.0f), rf)));
-    float cy = __fmul_rn(__fdiv_rn(__fmul_rn(R, 3.0f), 2.0f), rf);
+    float cx = __fmul_rn(R, __fadd_rn(__fmul_rn(PCB_SQRT_3, qf), __fmul_rn(half_sqrt3, rf)));
+    float cy = __fmul_rn(row_pitch, rf);
     float cz = __fmul_rn(hf, R);
     float dx = __fsub_rn(cx, px), dy = __fsub_rn(cy, py), dz = __fsub_rn(cz, pz);
     return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));

@@ -19,6 +19,16 @@ struct LevelGeom {
     int bx, by, bz; // bits of the per-cell hex window per axis
     int mx, my, mz; // margins subtracted from the hex key of the cell's min corner
     int hexbits;    // bx + by + bz
+    float half_sqrt3;  // SQRT_3 / 2.0          hex.rs:60 (loop-invariant sub-expressions, same single IEEE ops)
+    float row_pitch;   // (R * 3.0) / 2.0       hex.rs:61
+};
+
+// per-cell constants of a level, one 32-byte record
+struct __align__(16) CellGeo {
+    int hx, hy, hz;      // origin of the hex window (hex key of the cell's min corner minus the margin)
+    u32 start;           // first arrival
+    int ix2, iy2, iz2;   // 2 * cell index = index of child octant 0 (metadata.rs:100-102 at level + 1)
+    u32 end;             // one past the last arrival
 };
 
 // order-preserving float <-> int (for atomicMin/atomicMax of f32)
@@ -113,6 +123,7 @@ k_l0_key(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, int pb, R
 // Stage 0c: distinct level-0 cells of the sorted keys -> cell list + segment starts.
 struct L0HeadOp {
     typedef u32 State;
+    static constexpr bool kTileLoad = false;
     const u64* keys;
     u32 n;
     int pb;
@@ -177,17 +188,30 @@ __global__ void k_l0_gather(const PcbPoint* __restrict__ in_pts, const u64* __re
 }
 
 // ---------------------------------------------------------------------------------------------
-// Stage 1: per-cell origin of the hex window (hex key of the cell's min corner minus a margin).
-__global__ void k_cellbase(const int* __restrict__ cell_idx, u32 ncell, LevelGeom g, int* __restrict__ cellbase) {
+// Stage 1: per-cell constants (hex window origin, child index base, arrival range).
+__global__ void k_cellgeo(const int* __restrict__ cell_idx, const u32* __restrict__ cell_start, u32 ncell, LevelGeom g,
+                          CellGeo* __restrict__ geo) {
     u32 c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= ncell) return;
-    float x = __fmul_rn((float)cell_idx[3 * c + 0], g.S);
-    float y = __fmul_rn((float)cell_idx[3 * c + 1], g.S);
-    float z = __fmul_rn((float)cell_idx[3 * c + 2], g.S);
+    const int ix = cell_idx[3 * c + 0], iy = cell_idx[3 * c + 1], iz = cell_idx[3 * c + 2];
+    float x = __fmul_rn((float)ix, g.S);
+    float y = __fmul_rn((float)iy, g.S);
+    float z = __fmul_rn((float)iz, g.S);
     HexKey k = hex_from_world(x, y, z, g.R);
-    cellbase[3 * c + 0] = k.x - g.mx;
-    cellbase[3 * c + 1] = k.y - g.my;
-    cellbase[3 * c + 2] = k.z - g.mz;
+    CellGeo o;
+    o.hx = k.x - g.mx; o.hy = k.y - g.my; o.hz = k.z - g.mz;
+    o.start = cell_start[c];
+    o.ix2 = 2 * ix; o.iy2 = 2 * iy; o.iz2 = 2 * iz;
+    o.end = cell_start[c + 1];
+    geo[c] = o;
+}
+__device__ __forceinline__ CellGeo load_geo(const CellGeo* __restrict__ geo, u32 c) {
+    const uint4* p = (const uint4*)(geo + c);
+    uint4 a = __ldg(p), b = __ldg(p + 1);
+    CellGeo o;
+    o.hx = (int)a.x; o.hy = (int)a.y; o.hz = (int)a.z; o.start = a.w;
+    o.ix2 = (int)b.x; o.iy2 = (int)b.y; o.iz2 = (int)b.z; o.end = b.w;
+    return o;
 }
 
 // cell of arrival i: one binary search per warp (on the warp's first element), then a short walk
@@ -202,7 +226,7 @@ __device__ __forceinline__ u32 cell_of_arrival(const u32* __restrict__ cell_star
 template <bool PAIRS>
 __global__ void __launch_bounds__(256)
 k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_start, u32 ncell,
-         const int* __restrict__ cellbase, LevelGeom g, KeyLayout lay, RadixPlan plan, u64* __restrict__ keys,
+         const CellGeo* __restrict__ geo, LevelGeom g, KeyLayout lay, RadixPlan plan, u64* __restrict__ keys,
          u32* __restrict__ vals, u32* __restrict__ ghist, u32* __restrict__ err) {
     __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
     for (int i = threadIdx.x; i < plan.npass * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
@@ -212,16 +236,21 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
     const u64 chunk = (((u64)n + gridDim.x - 1) / gridDim.x + 255ull) & ~255ull;
     const u64 lo = (u64)blockIdx.x * chunk, hi = min((u64)n, lo + chunk);
     u32 c = 0;
-    if (lo + threadIdx.x < hi) c = find_segment(cell_start, ncell, (u32)(lo + threadIdx.x));
+    CellGeo cg;
+    cg.end = 0;
+    if (lo + threadIdx.x < hi) {
+        c = find_segment(cell_start, ncell, (u32)(lo + threadIdx.x));
+        cg = load_geo(geo, c);
+    }
     for (u64 i0 = lo; i0 < hi; i0 += 256) {
         u64 i = i0 + threadIdx.x;
         if (i < hi) {
             PcbPoint p = pts[i];
-            while (__ldg(cell_start + c + 1) <= (u32)i) c++;
+            while (cg.end <= (u32)i) cg = load_geo(geo, ++c);
             HexKey k = hex_from_world(p.x, p.y, p.z, g.R);
-            u32 rx = (u32)(k.x - __ldg(cellbase + 3 * c + 0));
-            u32 ry = (u32)(k.y - __ldg(cellbase + 3 * c + 1));
-            u32 rz = (u32)(k.z - __ldg(cellbase + 3 * c + 2));
+            u32 rx = (u32)(k.x - cg.hx);
+            u32 ry = (u32)(k.y - cg.hy);
+            u32 rz = (u32)(k.z - cg.hz);
             if ((rx >> g.bx) | (ry >> g.by) | (rz >> g.bz)) {
                 bad |= PCB_DERR_HEXRANGE;
                 rx &= (1u << g.bx) - 1u; ry &= (1u << g.by) - 1u; rz &= (1u << g.bz) - 1u;
@@ -261,15 +290,15 @@ struct ContestState {
 template <bool PAIRS>
 struct ContestOp {
     typedef ContestState State;
+    static constexpr bool kTileLoad = true;
+    static constexpr int ITEMS = 8;
     const u64* keys;
     const u32* vals;
     u32 n;
     KeyLayout lay;
     LevelGeom g;
     const PcbPoint* pts;
-    const int* cellbase;
-    const int* cell_idx;
-    const u32* cell_start;
+    const CellGeo* geo;
     u64* em;       // [n] by arrival position: loser's arrival position | octant << 32 | flags
     u32* win_src;  // [#groups] arrival position of each winner, sorted (cell, Z, Y, X)
     u32* win_end;  // [ncell] end of the cell's winners in win_src
@@ -284,35 +313,80 @@ struct ContestOp {
     }
     __device__ u64 gid(u64 key) const { return PAIRS ? key : (key >> lay.pb); }
     __device__ State identity() const { return State{~0ull, 0u, 0u}; }
-    __device__ State load(u32 j) const {
-        const u64 key = keys[j];
-        const u64 G = gid(key);
-        const u32 pos = PAIRS ? vals[j] : (u32)(key & ((1ull << lay.pb) - 1ull));
-        const u32 c = (u32)(G >> g.hexbits);
-        const PcbPoint p = pts[pos];
-        HexKey k;
-        k.x = (i32)((u32)G & ((1u << g.bx) - 1u)) + cellbase[3 * c + 0];
-        k.y = (i32)((u32)(G >> g.bx) & ((1u << g.by) - 1u)) + cellbase[3 * c + 1];
-        k.z = (i32)((u32)(G >> (g.bx + g.by)) & ((1u << g.bz) - 1u)) + cellbase[3 * c + 2];
-        const float d2 = hex_d2(k, p.x, p.y, p.z, g.R);
-        int dx = cell_index_axis(p.x, g.S_child) - 2 * cell_idx[3 * c + 0];
-        int dy = cell_index_axis(p.y, g.S_child) - 2 * cell_idx[3 * c + 1];
-        int dz = cell_index_axis(p.z, g.S_child) - 2 * cell_idx[3 * c + 2];
-        if (((u32)dx | (u32)dy | (u32)dz) > 1u) {
-            atomicOr(err, PCB_DERR_NEST);
-            dx &= 1; dy &= 1; dz &= 1;
+    // meta bits of a single element: 0-3 child octant, 8 group head, 9 group tail, 10 last of its cell in sorted
+    // order, 11 first arrival of its cell, 12 last arrival of its cell
+    __device__ void load_items(u64 base, State (&v)[ITEMS]) const {
+        const int lane = threadIdx.x & 31;
+        u64 key[ITEMS];
+        u32 pos[ITEMS];
+        if (base + ITEMS <= n) {
+            const ulonglong2* src = (const ulonglong2*)(keys + base);
+#pragma unroll
+            for (int k = 0; k < ITEMS / 2; k++) {
+                ulonglong2 t = src[k];
+                key[2 * k] = t.x;
+                key[2 * k + 1] = t.y;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < ITEMS; k++) key[k] = (base + k < n) ? keys[base + k] : ~0ull;
         }
-        u32 meta = (u32)(dx * 4 + dy * 2 + dz);
-        const bool head = (j == 0) || gid(keys[j - 1]) != G;
-        bool tail = true, cell_end = true;
-        if (j + 1 < n) {
-            const u64 Gn = gid(keys[j + 1]);
-            tail = Gn != G;
-            cell_end = (Gn >> g.hexbits) != (G >> g.hexbits);
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            if (PAIRS) pos[k] = (base + k < n) ? vals[base + k] : 0u;
+            else pos[k] = (u32)(key[k] & ((1ull << lay.pb) - 1ull));
         }
-        meta |= (head ? 0x100u : 0u) | (tail ? 0x200u : 0u) | (cell_end ? 0x400u : 0u);
-        return State{((u64)__float_as_uint(d2) << 32) | pos, meta, tail ? 1u : 0u};
+        // the gathers go first: they are the long-latency part
+        uint4 pt[ITEMS];
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) pt[k] = (base + k < n) ? __ldg((const uint4*)(pts + pos[k])) : make_uint4(0, 0, 0, 0);
+        // neighbours across the thread boundary
+        u64 prevk = __shfl_up_sync(0xFFFFFFFFu, key[ITEMS - 1], 1);
+        u64 nextk = __shfl_down_sync(0xFFFFFFFFu, key[0], 1);
+        if (lane == 0) prevk = (base > 0 && base <= n) ? keys[base - 1] : ~0ull;
+        if (lane == 31) nextk = (base + ITEMS < n) ? keys[base + ITEMS] : ~0ull;
+        u32 cprev = PCB_NONE;
+        CellGeo cg;
+        cg.hx = cg.hy = cg.hz = cg.ix2 = cg.iy2 = cg.iz2 = 0;
+        cg.start = cg.end = 0;
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            const u64 i = base + k;
+            if (i >= n) {
+                v[k] = identity();
+                continue;
+            }
+            const u64 G = gid(key[k]);
+            const u64 Gp = gid(k ? key[k - 1] : prevk), Gn = gid(k + 1 < ITEMS ? key[k + 1] : nextk);
+            const u32 c = (u32)(G >> g.hexbits);
+            if (c != cprev) {
+                cg = load_geo(geo, c);
+                cprev = c;
+            }
+            const float px = __uint_as_float(pt[k].x), py = __uint_as_float(pt[k].y), pz = __uint_as_float(pt[k].z);
+            HexKey hk;
+            hk.x = (i32)((u32)G & ((1u << g.bx) - 1u)) + cg.hx;
+            hk.y = (i32)((u32)(G >> g.bx) & ((1u << g.by) - 1u)) + cg.hy;
+            hk.z = (i32)((u32)(G >> (g.bx + g.by)) & ((1u << g.bz) - 1u)) + cg.hz;
+            const float d2 = hex_d2(hk, px, py, pz, g.R, g.half_sqrt3, g.row_pitch);
+            int dx = cell_index_axis(px, g.S_child) - cg.ix2;
+            int dy = cell_index_axis(py, g.S_child) - cg.iy2;
+            int dz = cell_index_axis(pz, g.S_child) - cg.iz2;
+            if (((u32)dx | (u32)dy | (u32)dz) > 1u) {
+                atomicOr(err, PCB_DERR_NEST);
+                dx &= 1; dy &= 1; dz &= 1;
+            }
+            u32 meta = (u32)(dx * 4 + dy * 2 + dz);
+            const bool head = (i == 0) || Gp != G;
+            const bool last = (i + 1 == n);
+            const bool tail = last || Gn != G;
+            const bool cell_end = last || (Gn >> g.hexbits) != (G >> g.hexbits);
+            meta |= (head ? 0x100u : 0u) | (tail ? 0x200u : 0u) | (cell_end ? 0x400u : 0u);
+            meta |= (cg.start == pos[k] ? 0x800u : 0u) | (cg.end == pos[k] + 1u ? 0x1000u : 0u);
+            v[k] = State{((u64)__float_as_uint(d2) << 32) | pos[k], meta, tail ? 1u : 0u};
+        }
     }
+    __device__ State load(u32) const { return identity(); }   // unused (kTileLoad)
     __device__ State combine(const State& a, const State& b) const {
         State r;
         const bool take_b = (b.meta & 0x100u) || b.mn < a.mn;   // equal only for identity: positions are distinct
@@ -331,11 +405,10 @@ struct ContestOp {
         } else {
             e = ((u64)(self.meta & 0xFu) << 32) | pos;
         }
-        const u32 c = (u32)(gid(keys[j]) >> g.hexbits);
         if (self.meta & 0x200u) win_src[excl.ntail] = (u32)incl.mn;
-        if (self.meta & 0x400u) win_end[c] = excl.ntail + 1;
-        if (__ldg(cell_start + c) == pos) e |= PCB_EM_CELL_FIRST;
-        if (__ldg(cell_start + c + 1) == pos + 1u) e |= PCB_EM_CELL_LAST;
+        if (self.meta & 0x400u) win_end[(u32)(gid(keys[j]) >> g.hexbits)] = excl.ntail + 1;
+        if (self.meta & 0x800u) e |= PCB_EM_CELL_FIRST;
+        if (self.meta & 0x1000u) e |= PCB_EM_CELL_LAST;
         em[pos] = e;
     }
     __device__ void finish(const State& total) const { *nwin_out = total.ntail; }
@@ -353,6 +426,7 @@ struct Oct8 {
 };
 struct OctScanOp {
     typedef Oct8 State;
+    static constexpr bool kTileLoad = false;
     const u64* em;
     const u32* bat;
     const u32* cell_start;
@@ -678,6 +752,7 @@ struct LevelTotals {
 };
 struct CellScanOp {
     typedef CellScanState State;
+    static constexpr bool kTileLoad = false;
     const u32* cell_deliver;
     const u32* cell_children;
     const u64* cell_bytes;

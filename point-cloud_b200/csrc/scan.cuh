@@ -276,10 +276,14 @@ __global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 
 
     State v[ITEMS];
     State acc = op.identity();
+    if constexpr (Op::kTileLoad) {
+        op.load_items(base, v);   // whole-thread load (all threads call it: it may shuffle)
+    } else {
 #pragma unroll
-    for (int k = 0; k < ITEMS; k++) {
-        u64 i = base + k;
-        v[k] = (i < n) ? op.load((u32)i) : op.identity();
+        for (int k = 0; k < ITEMS; k++) {
+            u64 i = base + k;
+            v[k] = (i < n) ? op.load((u32)i) : op.identity();
+        }
     }
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) acc = op.combine(acc, v[k]);
