@@ -55,6 +55,9 @@ typedef enum pcb_status {
                                     read back with pcb_node_* (tests, bench e2e) */
 #define PCB_FLAG_DEVICE_ONLY 2u  /* implies NO_FILES; node images stay in device memory (bench `value`) */
 #define PCB_FLAG_PROFILE 4u      /* time every kernel class with CUDA events (pcb_kernel_stat) */
+#define PCB_FLAG_NO_METADATA_FILE 8u /* write node files but not metadata.json (multi-GPU: every rank writes its own
+                                    nodes into the shared directory, rank 0 writes the reduced metadata.json with
+                                    pcb_write_metadata) */
 
 typedef struct pcb_options {
     uint32_t struct_size;   /* sizeof(pcb_options), for ABI growth */
@@ -114,7 +117,18 @@ int pcb_set_stream(pcb_handle* h, void* cuda_stream);
 /* Same, but `d_pts` is a device pointer on the handle's device (resident-input path).  When it is the first
    add on the handle the buffer is aliased, not copied: keep it valid and unchanged until pcb_finish returns. */
 int pcb_add_points_device(pcb_handle* h, const pcb_point* d_pts, uint64_t n);
+/* Multi-GPU ingest: points that were routed to this device by the level-0 exchange, still in the order of the
+   undivided input stream, each with the ordinal (0-based, global) of the batch it belonged to (lib.rs:31-35 cut
+   of the undivided stream).  Device pointers, borrowed until pcb_finish returns; the only add on the handle. */
+int pcb_add_points_device_batched(pcb_handle* h, const pcb_point* d_pts, const uint32_t* d_batch, uint64_t n);
 int pcb_finish(pcb_handle* h, pcb_stats* stats);
+/* Metadata::write_to (metadata.rs:51-53) for a reduced result: used by rank 0 after the per-rank builds. */
+int pcb_write_metadata(const char* out_dir, uint64_t number_of_points, uint32_t hierarchies, const float bbox_min[3],
+                       const float bbox_max[3], uint32_t cell_point_overflow_limit, uint32_t sub_grid_dimension,
+                       float max_cell_size);
+/* Config in force on this handle (defaults, pcb_options override, or the existing metadata.json). */
+int pcb_get_config(const pcb_handle* h, uint32_t* cell_point_overflow_limit, uint32_t* sub_grid_dimension,
+                   float* max_cell_size);
 void pcb_close(pcb_handle* h);
 /* Node images are staged in pinned host buffers that are recycled across handles; this frees the idle ones. */
 void pcb_trim_host_cache(void);

@@ -176,6 +176,35 @@ int pcb_add_points_device(pcb_handle* h, const pcb_point* d_pts, uint64_t n) {
     PCB_GUARD(h, h->builder->add_points(d_pts, n, h->opt.batch_size, true))
 }
 
+int pcb_add_points_device_batched(pcb_handle* h, const pcb_point* d_pts, const uint32_t* d_batch, uint64_t n) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    if (h && n && (!d_pts || !d_batch)) return fail(h, PCB_ERR_ARG, "null points");
+    PCB_GUARD(h, h->builder->add_points_batched(d_pts, d_batch, n))
+}
+
+int pcb_write_metadata(const char* out_dir, uint64_t number_of_points, uint32_t hierarchies, const float bbox_min[3],
+                       const float bbox_max[3], uint32_t limit, uint32_t dim, float max_cell_size) {
+    if (!out_dir || !bbox_min || !bbox_max) return PCB_ERR_ARG;
+    Metadata m;
+    m.number_of_points = number_of_points;
+    m.hierarchies = hierarchies;
+    for (int a = 0; a < 3; a++) { m.bbox_min[a] = bbox_min[a]; m.bbox_max[a] = bbox_max[a]; }
+    m.cell_point_overflow_limit = limit;
+    m.sub_grid_dimension = dim;
+    m.max_cell_size = max_cell_size;
+    std::string js = metadata_to_json(m);
+    if (!mkdir_p(out_dir)) return PCB_ERR_IO;
+    return write_file(std::string(out_dir) + "/metadata.json", js.data(), js.size()) ? PCB_OK : PCB_ERR_IO;
+}
+
+int pcb_get_config(const pcb_handle* h, uint32_t* limit, uint32_t* dim, float* max_cell_size) {
+    if (!h) return PCB_ERR_ARG;
+    if (limit) *limit = h->meta.cell_point_overflow_limit;
+    if (dim) *dim = h->meta.sub_grid_dimension;
+    if (max_cell_size) *max_cell_size = h->meta.max_cell_size;
+    return PCB_OK;
+}
+
 int pcb_add_points_batch(pcb_handle* h, const pcb_point* pts, uint64_t n) {
     if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
     if (h && n && !pts) return fail(h, PCB_ERR_ARG, "null points");
@@ -211,7 +240,8 @@ static void write_outputs(pcb_handle* h, pcb_stats* stats) {
     for (auto& t : th) t.join();
     if (bad) throw Error{PCB_ERR_IO, "failed to write a node file"};
     // converter.rs:226-238 save_metadata
-    if (!write_file(h->out_dir + "/metadata.json", h->meta_json.data(), h->meta_json.size()))
+    if (!(h->opt.flags & PCB_FLAG_NO_METADATA_FILE) &&
+        !write_file(h->out_dir + "/metadata.json", h->meta_json.data(), h->meta_json.size()))
         throw Error{PCB_ERR_IO, "failed to write metadata.json"};
     if (stats) stats->write_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }

@@ -291,6 +291,22 @@ class BuilderImpl {
         if (one_batch) end_run();
     }
 
+    // Points that already carry their global batch ordinal (multi-GPU: the exchange keeps the ordinals of the
+    // undivided stream).  Device pointers, borrowed until build() returns; must be the only add on the handle.
+    void add_batched(const pcb_point* d_pts, const u32* d_batch, u64 n) {
+        CUDA_TRY(cudaSetDevice(device));
+        if (n_in != 0 || batches != 0 || run_open) throw Error{PCB_ERR_ARG, "pcb_add_points_device_batched must be the only add"};
+        if (n >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "more than 2^30-1 points on one device"};
+        batches = 1;            // at least one batch was processed: level 0 is visited (converter.rs:111,120)
+        if (!n) return;
+        d_in = (PcbPoint*)d_pts;
+        in_borrowed = true;
+        cap_in = n_in = n;
+        d_bat_in = (u32*)d_batch;
+        bat_owned = false;
+        segs.push_back(BatchSeg{0u, 0u, 1u, 0u});
+    }
+
     void build(Metadata* meta, NodeSource* existing);
     template <bool PAIRS>
     void build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start, int*& cell_idx, u32& n, u32& ncell,
@@ -715,6 +731,9 @@ void Builder::begin_file() { impl_->begin_file(); }
 void Builder::set_stream(void* stream) { impl_->set_stream((cudaStream_t)stream); }
 void Builder::add_points(const pcb_point* pts, uint64_t n, uint32_t batch_size, bool device_ptr) {
     guarded([&] { impl_->add(pts, n, batch_size ? batch_size : 10000u, device_ptr, false); return 0; });
+}
+void Builder::add_points_batched(const pcb_point* d_pts, const uint32_t* d_batch, uint64_t n) {
+    guarded([&] { impl_->add_batched(d_pts, d_batch, n); return 0; });
 }
 void Builder::add_points_one_batch(const pcb_point* pts, uint64_t n, bool device_ptr) {
     guarded([&] { impl_->add(pts, n, 0, device_ptr, true); return 0; });

@@ -80,6 +80,7 @@ class Builder {
     void begin_file();                                        // lib.rs:17-32: batches never span files
     void add_points(const pcb_point* pts, uint64_t n, uint32_t batch_size, bool device_ptr);
     void add_points_one_batch(const pcb_point* pts, uint64_t n, bool device_ptr);  // converter.rs:106
+    void add_points_batched(const pcb_point* d_pts, const uint32_t* d_batch, uint64_t n);  // explicit batch ordinals
     // Runs the level-synchronous build.  meta: in = state before this run, out = after.
     void build(Metadata* meta, NodeSource* existing);
     const std::vector<NodeRec>& nodes() const;

@@ -22,11 +22,12 @@ POINT_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("rgba", "u1",
 FLAG_NO_FILES = 1
 FLAG_DEVICE_ONLY = 2
 FLAG_PROFILE = 4
+FLAG_NO_METADATA_FILE = 8
 
 EXPORTS = [
     "pcb_open", "pcb_set_stream", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
     "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
-    "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
+    "pcb_add_points_device_batched", "pcb_write_metadata", "pcb_get_config", "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
 
 
@@ -77,6 +78,10 @@ def load_library():
     L.pcb_add_points.argtypes = [vp, vp, C.c_uint64]
     L.pcb_add_points_batch.argtypes = [vp, vp, C.c_uint64]
     L.pcb_add_points_device.argtypes = [vp, vp, C.c_uint64]
+    L.pcb_add_points_device_batched.argtypes = [vp, vp, vp, C.c_uint64]
+    L.pcb_write_metadata.argtypes = [C.c_char_p, C.c_uint64, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_float),
+                                     C.c_uint32, C.c_uint32, C.c_float]
+    L.pcb_get_config.argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_float)]
     L.pcb_reserve.argtypes = [vp, C.c_uint64]
     L.pcb_set_stream.argtypes = [vp, vp]
     L.pcb_finish.argtypes = [vp, C.POINTER(PcbStats)]
@@ -152,6 +157,15 @@ class Converter:
     def add_points_device(self, device_ptr: int, n: int):
         self._check(self._L.pcb_add_points_device(self._h, C.c_void_p(device_ptr), n))
 
+    def add_points_device_batched(self, device_ptr: int, batch_ptr: int, n: int):
+        """Routed points with explicit global batch ordinals (multi-GPU ingest)."""
+        self._check(self._L.pcb_add_points_device_batched(self._h, C.c_void_p(device_ptr), C.c_void_p(batch_ptr), n))
+
+    def config(self):
+        a, b, c = C.c_uint32(), C.c_uint32(), C.c_float()
+        self._check(self._L.pcb_get_config(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
     def finish(self) -> PcbStats:
         """Drop for Converter (converter.rs:241-246): build, write node files + metadata.json."""
         st = PcbStats()
@@ -200,6 +214,15 @@ class Converter:
             self.close()
         except Exception:
             pass
+
+
+def write_metadata(out_dir, number_of_points, hierarchies, bbox_min, bbox_max, config):
+    L = load_library()
+    mn, mx = (C.c_float * 3)(*[float(v) for v in bbox_min]), (C.c_float * 3)(*[float(v) for v in bbox_max])
+    rc = L.pcb_write_metadata(str(out_dir).encode(), int(number_of_points), int(hierarchies), mn, mx,
+                              int(config[0]), int(config[1]), float(config[2]))
+    if rc != 0:
+        raise PcbError(rc, "pcb_write_metadata failed")
 
 
 def convert(files, out_dir=None, *, config=None, batch_size=0, device=0, flags=0):

@@ -1,0 +1,165 @@
+"""Multi-GPU sharding of the octree/LOD build: one process per GPU.
+
+The forest decomposes by level-0 cell: a cell's state depends only on the arrivals from its single parent
+(converter.rs:124-134) and level-0 cells have none.  So the undivided input stream (rank r holds the index
+range [r*n/G, (r+1)*n/G) of it) is routed ONCE, by level-0 cell, to owner ranks; every rank then builds its
+subtrees independently and only three scalars are reduced for metadata.json.
+
+  1. level-0 cell of every local point: floor(p / max_cell_size) per axis, IEEE f32 (metadata.rs:100-102)
+  2. all-gather of the local (cell, count) tables -> the same global table on every rank
+  3. deterministic greedy bin packing (largest cell first, ties by cell id) -> owner rank per cell
+  4. ONE all-to-all-v of the 16-byte point records and ONE of their u32 batch ordinals
+     (batch = global input index // batch_size, lib.rs:31-35 applied to the undivided stream).
+     Chunks are received in source-rank order and every source sends in index order, so each owner holds
+     its points in the order of the undivided stream — the arrival order the reference would have seen.
+  5. per-rank build (pcb_add_points_device_batched), node files of different ranks are disjoint
+  6. all-reduce: number_of_points (sum), hierarchies (max), bounding box (min / max); rank 0 writes
+     metadata.json (pcb_write_metadata).
+
+torch / torch.distributed are plumbing here (device memory, NCCL); the backend is whatever process group the
+caller initialised (NCCL over NVLink on the GPU box, gloo in the CPU tests of the routing logic).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+BIAS = 1 << 20  # level-0 indices are validated to lie in [-2^20, 2^20) (PCB_ERR_RANGE otherwise)
+
+
+def l0_cell_keys(pts_u8: torch.Tensor, max_cell_size: float) -> torch.Tensor:
+    """int64 key of the level-0 cell of every point; key order == (x, y, z) lexicographic index order."""
+    xyz = pts_u8[:, :12].contiguous().view(torch.float32).view(-1, 3)
+    s = torch.tensor(max_cell_size, dtype=torch.float32, device=xyz.device)
+    idx = torch.floor(xyz / s).to(torch.int64)  # true IEEE division, as metadata.rs:101
+    if idx.numel() and (int(idx.min()) < -BIAS or int(idx.max()) >= BIAS):
+        raise ValueError("level-0 cell index outside +-2^20")
+    b = idx + BIAS
+    return (b[:, 0] << 42) | (b[:, 1] << 21) | b[:, 2]
+
+
+def key_to_index(key: int) -> Tuple[int, int, int]:
+    return ((key >> 42) - BIAS, ((key >> 21) & ((1 << 21) - 1)) - BIAS, (key & ((1 << 21) - 1)) - BIAS)
+
+
+def plan_owners(cells: torch.Tensor, counts: torch.Tensor, world: int) -> torch.Tensor:
+    """Greedy bin packing, largest cell first (ties: smaller key first), onto the least loaded rank (ties:
+    lower rank).  Pure function of the global table => identical on every rank.  Returns owner per cell, in
+    the order of `cells` (sorted ascending)."""
+    cells = cells.cpu().tolist()
+    counts = counts.cpu().tolist()
+    order = sorted(range(len(cells)), key=lambda i: (-counts[i], cells[i]))
+    load = [0] * world
+    owner = [0] * len(cells)
+    for i in order:
+        r = min(range(world), key=lambda q: (load[q], q))
+        owner[i] = r
+        load[r] += counts[i]
+    return torch.tensor(owner, dtype=torch.int64)
+
+
+def global_cell_table(keys: torch.Tensor, group=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """All ranks' (cell, count) tables merged: sorted unique cells + total counts (CPU tensors)."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    cells, counts = torch.unique(keys, return_counts=True)
+    if world == 1:
+        return cells.cpu(), counts.cpu()
+    dev = keys.device
+    m = torch.tensor([cells.numel()], dtype=torch.int64, device=dev)
+    sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(sizes, m, group=group)
+    cap = max(int(s.item()) for s in sizes)
+    buf = torch.zeros((2, max(cap, 1)), dtype=torch.int64, device=dev)
+    buf[0, :cells.numel()] = cells
+    buf[1, :cells.numel()] = counts
+    bufs = [torch.zeros_like(buf) for _ in range(world)]
+    dist.all_gather(bufs, buf, group=group)
+    allc = torch.cat([b[0, :int(s.item())] for b, s in zip(bufs, sizes)])
+    alln = torch.cat([b[1, :int(s.item())] for b, s in zip(bufs, sizes)])
+    ucells, inv = torch.unique(allc, return_inverse=True)
+    total = torch.zeros(ucells.numel(), dtype=torch.int64, device=dev).scatter_add_(0, inv, alln)
+    return ucells.cpu(), total.cpu()
+
+
+def route(pts_u8: torch.Tensor, first_index: int, batch_size: int, max_cell_size: float, group=None):
+    """Steps 1-4.  pts_u8: (n, 16) uint8 slice of the undivided stream starting at global index first_index.
+    Returns (points (m,16) uint8, batch ordinals (m,) int32, owner table dict) for this rank."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    dev = pts_u8.device
+    n = pts_u8.shape[0]
+    keys = l0_cell_keys(pts_u8, max_cell_size)
+    cells, counts = global_cell_table(keys, group)
+    owner_of_cell = plan_owners(cells, counts, world)
+    batch = ((torch.arange(n, dtype=torch.int64, device=dev) + first_index) // batch_size).to(torch.int32)
+    table = {"cells": cells, "counts": counts, "owners": owner_of_cell}
+    if world == 1:
+        return pts_u8, batch, table
+    slot = torch.searchsorted(cells.to(dev), keys)
+    dest = owner_of_cell.to(dev)[slot]
+    order = torch.sort(dest, stable=True).indices           # keeps index order inside every destination
+    send_pts = pts_u8[order].contiguous()
+    send_bat = batch[order].contiguous()
+    send_counts = torch.bincount(dest, minlength=world).to(torch.int64)
+    recv_counts = torch.zeros(world, dtype=torch.int64, device=dev)
+    dist.all_to_all_single(recv_counts, send_counts, group=group)
+    ins, outs = send_counts.cpu().tolist(), recv_counts.cpu().tolist()
+    m = int(sum(outs))
+    recv_pts = torch.empty((m, 16), dtype=torch.uint8, device=dev)
+    recv_bat = torch.empty((m,), dtype=torch.int32, device=dev)
+    dist.all_to_all_single(recv_pts, send_pts, outs, ins, group=group)
+    dist.all_to_all_single(recv_bat, send_bat, outs, ins, group=group)
+    table["rank"] = rank
+    return recv_pts, recv_bat, table
+
+
+def reduce_metadata(points_added: int, hierarchies: int, bbox_min, bbox_max, base_points: int = 0,
+                    base_bbox=None, group=None):
+    """Step 6.  base_* = the existing metadata.json (merge mode), identical on every rank.  Ranks that received
+    no points do not contribute a box (Aabb::from of nothing is None, converter.rs:97)."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    dev = torch.device("cuda", torch.cuda.current_device()) if (
+        dist.is_initialized() and dist.get_backend(group) == "nccl") else torch.device("cpu")
+    inf = float("inf")
+    has = points_added > 0
+    lo = torch.tensor(list(bbox_min) if has else [inf] * 3, dtype=torch.float32, device=dev)
+    hi = torch.tensor(list(bbox_max) if has else [-inf] * 3, dtype=torch.float32, device=dev)
+    cnt = torch.tensor([points_added, hierarchies], dtype=torch.int64, device=dev)
+    hmax = cnt[1:].clone()
+    total = cnt[:1].clone()
+    if world > 1:
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(total, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(hmax, op=dist.ReduceOp.MAX, group=group)
+    n_new = int(total.item())
+    if base_points and base_bbox is not None:              # converter.rs:100-102 extend_aabb
+        blo = torch.tensor(base_bbox[0], dtype=torch.float32, device=dev)
+        bhi = torch.tensor(base_bbox[1], dtype=torch.float32, device=dev)
+        lo, hi = (torch.minimum(lo, blo), torch.maximum(hi, bhi)) if n_new else (blo, bhi)
+    elif n_new == 0:
+        lo = torch.zeros(3, dtype=torch.float32)
+        hi = torch.zeros(3, dtype=torch.float32)
+    return base_points + n_new, int(hmax.item()), lo.cpu().tolist(), hi.cpu().tolist()
+
+
+def route_emulated(slices: List[torch.Tensor], batch_size: int, max_cell_size: float):
+    """The same routing for G ranks emulated in ONE process (tests on a single GPU / CPU): `slices` are the
+    consecutive index ranges of the undivided stream.  Returns [(points, batch ordinals)] per owner rank."""
+    world = len(slices)
+    keys = [l0_cell_keys(s, max_cell_size) for s in slices]
+    cells, counts = torch.unique(torch.cat(keys), return_counts=True)
+    owners = plan_owners(cells, counts, world)
+    first, out_p, out_b = 0, [[] for _ in range(world)], [[] for _ in range(world)]
+    for s, k in zip(slices, keys):
+        n = s.shape[0]
+        batch = ((torch.arange(n, dtype=torch.int64, device=s.device) + first) // batch_size).to(torch.int32)
+        dest = owners.to(s.device)[torch.searchsorted(cells.to(s.device), k)]
+        for r in range(world):
+            sel = dest == r
+            out_p[r].append(s[sel])
+            out_b[r].append(batch[sel])
+        first += n
+    return [(torch.cat(p).contiguous(), torch.cat(b).contiguous()) for p, b in zip(out_p, out_b)]
