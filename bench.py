@@ -191,13 +191,33 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     n = args.points
-    # Each rank owns a disjoint block of level-0 cell columns of the terrain (the state after the
-    # level-0 exchange of SURVEY.md §8e); same density, same extent per rank => weak scaling.
-    side = (n / DENSITY) ** 0.5
-    x0 = -side / 2 + rank * side
-    pts = synth.terrain(n, 2 + rank, dev, (x0, x0 + side, -side / 2, side / 2))
+    # Weak scaling: the undivided stream is world * n points of the same terrain over an extent that grows with
+    # the world size (same density); rank r holds the index range [r*n, (r+1)*n) of it, i.e. random points of the
+    # WHOLE extent, so (world-1)/world of them must cross NVLink to reach the owner of their level-0 cell.
+    side_x = (n / DENSITY) ** 0.5 * world
+    side_y = (n / DENSITY) ** 0.5
+    pts = synth.terrain(n, 2 + rank, dev, (-side_x / 2, side_x / 2, -side_y / 2, side_y / 2))
     torch.cuda.synchronize()
     stream = torch.cuda.current_stream()
+    shard = None
+    if world > 1:
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("pcb_shard", ROOT / "point-cloud_b200" / "shard.py")
+        shard = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(shard)
+    route_launches = [0]
+
+    def ingest(cv, src):
+        """single GPU: the resident stream as is; N GPUs: level-0 exchange (libpcb routing kernels + NCCL
+        all-to-all-v), then the routed points with their global batch ordinals."""
+        if world == 1:
+            cv.begin_file()
+            cv.add_points_device(src.data_ptr(), n)
+            return None
+        rp, rb, info = shard.route_device(pcb, src, rank * n, 10_000, 1000.0, stream=stream)
+        route_launches[0] += info["launches"]
+        cv.add_points_device_batched(rp.data_ptr(), rb.data_ptr(), rp.shape[0])
+        return rp, rb   # keep alive until finish
 
     host_log = []
 
@@ -207,8 +227,7 @@ def main():
         cv = pcb.Converter(None, device=local_rank, flags=flags)
         try:
             cv.set_stream(stream.cuda_stream)
-            cv.begin_file()
-            cv.add_points_device(pts.data_ptr(), n)
+            keep = ingest(cv, pts)
             t1 = time.perf_counter()
             st = cv.finish()
             t2 = time.perf_counter()
@@ -229,6 +248,7 @@ def main():
     for _ in range(args.warmup):
         step()
     barrier()
+    route_launches[0] = 0
     sampler.mark_start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches, kstats, last = 0, {}, None
@@ -246,6 +266,7 @@ def main():
                 d[f] += k[f]
     ev1.record(stream)
     barrier()
+    route_timed = route_launches[0]
     sampler.mark_end()
     clocks = sampler.stop()
     ms = ev0.elapsed_time(ev1)
@@ -266,14 +287,20 @@ def main():
         host.copy_(pts)
         torch.cuda.synchronize()
         hnp = host.numpy()
+        stage = torch.empty_like(pts) if world > 1 else None
         times, d2h = [], 0
 
         def e2e_step():
             cv = pcb.Converter(None, device=local_rank, flags=pcb.FLAG_NO_FILES)
             try:
-                cv.reserve(n)
-                cv.begin_file()
-                cv.add_points(hnp)
+                if world == 1:
+                    cv.reserve(n)
+                    cv.begin_file()
+                    cv.add_points(hnp)
+                else:   # host slice -> device, exchange, build
+                    cv.set_stream(stream.cuda_stream)
+                    stage.copy_(host, non_blocking=True)
+                    keep = ingest(cv, stage)
                 st = cv.finish()
                 return st
             finally:
@@ -329,8 +356,10 @@ def main():
                                       f"(5000/96/1000.0), batch 10000", "points_per_gpu": n,
                           "l2": "inputs (1.6 GB/step) larger than L2, no explicit flush",
                           "levels": int(last.levels_built), "arrivals_per_point": round(last.arrivals / n, 3),
-                          "nodes": int(last.nodes_written), "sharding": "disjoint level-0 cell blocks per rank", "step_ms": step_ms},
-               "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+                          "nodes": int(last.nodes_written), "sharding": ("none (1 GPU)" if world == 1 else
+                                       "level-0 cell owners; exchange = libpcb routing kernels + NCCL all-to-all-v, "
+                                       "inside the timed step"), "step_ms": step_ms},
+               "e2e": e2e, "gpu_launches": int(launches) + route_timed, "roofline": roofline, "cpu_baseline": cpu,
                "clocks": clocks}
         print(json.dumps(out))
     if world > 1:

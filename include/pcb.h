@@ -141,6 +141,23 @@ int pcb_metadata_json(const pcb_handle* h, char* buf, uint64_t cap); /* returns 
 int pcb_kernel_stat_count(const pcb_handle* h);
 int pcb_kernel_stat_get(const pcb_handle* h, int i, pcb_kernel_stat* out);
 
+/* ---- multi-GPU routing by level-0 cell (one process per GPU).  Device pointers on `device`,
+   work runs on `stream` (a cudaStream_t).  Return >= 0: kernels launched; < 0: a pcb_status code, message through
+   pcb_last_error(NULL).  The reference has no counterpart: it is single-process.
+   1. pcb_route_bbox: min / max of the local slice (+inf / -inf when n == 0), validates coordinates.
+   2. pcb_route_histogram: points per level-0 cell (metadata.rs:100-102 at level 0) inside the dense index box
+      [origin, origin + dims), x fastest; the caller all-reduces the table and plans owners.
+   3. pcb_route_pack: stable partition of the slice by owner[cell] into the all-to-all send buffer, with the
+      global batch ordinal (first_index + i) / batch_size of every point; send_counts[world] on the host. */
+int pcb_route_bbox(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size, float out_min[3],
+                   float out_max[3]);
+int pcb_route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size,
+                        const int32_t origin[3], const uint32_t dims[3], uint32_t* d_hist);
+int pcb_route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index,
+                   uint32_t batch_size, float max_cell_size, const int32_t origin[3], const uint32_t dims[3],
+                   const uint8_t* d_owner, uint32_t world, pcb_point* d_send_pts, uint32_t* d_send_batch,
+                   uint64_t* send_counts);
+
 const char* pcb_version(void);
 int pcb_device_count(void);
 

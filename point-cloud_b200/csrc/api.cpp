@@ -23,6 +23,12 @@ using namespace pcb;
 namespace pcb {
 int device_count();
 void trim_host_cache();
+int route_bbox(int device, void* stream, const pcb_point* d_pts, uint64_t n, float S0, float out_min[3], float out_max[3]);
+int route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n, float S0, const int32_t origin[3],
+                    const uint32_t dims[3], uint32_t* d_hist);
+int route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
+               float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner, uint32_t world,
+               pcb_point* d_send_pts, uint32_t* d_send_batch, uint64_t* send_counts);
 }
 
 struct pcb_handle {
@@ -195,6 +201,34 @@ int pcb_write_metadata(const char* out_dir, uint64_t number_of_points, uint32_t 
     std::string js = metadata_to_json(m);
     if (!mkdir_p(out_dir)) return PCB_ERR_IO;
     return write_file(std::string(out_dir) + "/metadata.json", js.data(), js.size()) ? PCB_OK : PCB_ERR_IO;
+}
+
+#define PCB_ROUTE_GUARD(body)                          \
+    try {                                              \
+        return body;                                   \
+    } catch (const Error& e) {                         \
+        return fail(nullptr, e.status, e.message);     \
+    } catch (const std::exception& e) {                \
+        return fail(nullptr, PCB_ERR_ARG, e.what());   \
+    }
+
+int pcb_route_bbox(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size, float out_min[3],
+                   float out_max[3]) {
+    if (!out_min || !out_max || (n && !d_pts)) return PCB_ERR_ARG;
+    PCB_ROUTE_GUARD(pcb::route_bbox(device, stream, d_pts, n, max_cell_size, out_min, out_max))
+}
+int pcb_route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size,
+                        const int32_t origin[3], const uint32_t dims[3], uint32_t* d_hist) {
+    if (!origin || !dims || !d_hist || (n && !d_pts)) return PCB_ERR_ARG;
+    PCB_ROUTE_GUARD(pcb::route_histogram(device, stream, d_pts, n, max_cell_size, origin, dims, d_hist))
+}
+int pcb_route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index,
+                   uint32_t batch_size, float max_cell_size, const int32_t origin[3], const uint32_t dims[3],
+                   const uint8_t* d_owner, uint32_t world, pcb_point* d_send_pts, uint32_t* d_send_batch,
+                   uint64_t* send_counts) {
+    if (!origin || !dims || !d_owner || !send_counts || (n && (!d_pts || !d_send_pts || !d_send_batch))) return PCB_ERR_ARG;
+    PCB_ROUTE_GUARD(pcb::route_pack(device, stream, d_pts, n, first_index, batch_size, max_cell_size, origin, dims,
+                                    d_owner, world, d_send_pts, d_send_batch, send_counts))
 }
 
 int pcb_get_config(const pcb_handle* h, uint32_t* limit, uint32_t* dim, float* max_cell_size) {

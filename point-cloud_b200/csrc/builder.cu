@@ -16,6 +16,7 @@
 #include "level.cuh"
 #include "radix.cuh"
 #include "scan.cuh"
+#include "route.cuh"
 
 namespace pcb {
 
@@ -751,6 +752,93 @@ uint32_t Builder::levels_built() const { return impl_->levels_built; }
 double Builder::h2d_seconds() const { return impl_->h2d_s; }
 double Builder::build_seconds() const { return impl_->build_s; }
 double Builder::d2h_seconds() const { return impl_->d2h_s; }
+
+// ---- multi-GPU routing (free functions: they run before a handle exists) ---------------------------------
+struct NoProf {
+    void pb() {}
+    void pe(const char*, u64, u64, u64) {}
+};
+
+static L0Box make_box(const int32_t origin[3], const uint32_t dims[3]) {
+    L0Box box;
+    box.ox = origin[0]; box.oy = origin[1]; box.oz = origin[2];
+    box.nx = dims[0]; box.ny = dims[1]; box.nz = dims[2];
+    return box;
+}
+
+int route_bbox(int device, void* stream, const pcb_point* d_pts, uint64_t n, float S0, float out_min[3], float out_max[3]) {
+    return guarded([&] {
+        CUDA_TRY(cudaSetDevice(device));
+        cudaStream_t st = (cudaStream_t)stream;
+        int init[8] = {INT_MAX, INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MIN, 0, 0};
+        int* d = nullptr;
+        CUDA_TRY(cudaMallocAsync((void**)&d, sizeof init, st));
+        CUDA_TRY(cudaMemcpyAsync(d, init, sizeof init, cudaMemcpyHostToDevice, st));
+        if (n) k_bbox_check<<<148 * 8, 256, 0, st>>>((const PcbPoint*)d_pts, (u32)n, S0, d, (u32*)(d + 6));
+        int res[8];
+        CUDA_TRY(cudaMemcpyAsync(res, d, sizeof res, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        CUDA_TRY(cudaFreeAsync(d, st));
+        if (res[6] & PCB_DERR_NONFINITE) throw Error{PCB_ERR_RANGE, "non-finite coordinate in input"};
+        if (res[6] & PCB_DERR_L0RANGE) throw Error{PCB_ERR_RANGE, "level-0 cell index outside +-2^20"};
+        for (int a = 0; a < 3; a++) {
+            out_min[a] = n ? ord2f_host(res[a]) : INFINITY;
+            out_max[a] = n ? ord2f_host(res[3 + a]) : -INFINITY;
+        }
+        return n ? 1 : 0;
+    });
+}
+
+int route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n, float S0, const int32_t origin[3],
+                    const uint32_t dims[3], uint32_t* d_hist) {
+    return guarded([&] {
+        CUDA_TRY(cudaSetDevice(device));
+        cudaStream_t st = (cudaStream_t)stream;
+        const u64 vol = (u64)dims[0] * dims[1] * dims[2];
+        if (vol == 0 || vol > (1ull << 26)) throw Error{PCB_ERR_RANGE, "level-0 index box too large for the dense routing table"};
+        CUDA_TRY(cudaMemsetAsync(d_hist, 0, vol * 4, st));
+        if (n) k_route_hist<<<148 * 4, 256, 0, st>>>((const PcbPoint*)d_pts, (u32)n, S0, make_box(origin, dims), (u32)vol, d_hist);
+        return n ? 1 : 0;
+    });
+}
+
+int route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
+               float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner, uint32_t world,
+               pcb_point* d_send_pts, uint32_t* d_send_batch, uint64_t* send_counts) {
+    return guarded([&] {
+        CUDA_TRY(cudaSetDevice(device));
+        cudaStream_t st = (cudaStream_t)stream;
+        for (u32 r = 0; r < world; r++) send_counts[r] = 0;
+        if (!n) return 0;
+        if (n >= (1ull << 30) || world == 0 || world > 256 || batch_size == 0) throw Error{PCB_ERR_ARG, "bad routing arguments"};
+        const u32 n32 = (u32)n;
+        const int pb = std::max(1, bits_count(n));
+        const RadixPlan plan = radix_plan(pb, std::max(1, bits_count(world)));
+        u64 *kA = nullptr, *kB = nullptr;
+        u32* ghist = nullptr;
+        const u64 rwords = RadixTemp::ghist_words() + RadixTemp::status_words(n, plan);
+        CUDA_TRY(cudaMallocAsync((void**)&kA, 8 * n, st));
+        CUDA_TRY(cudaMallocAsync((void**)&kB, 8 * n, st));
+        CUDA_TRY(cudaMallocAsync((void**)&ghist, 4 * rwords, st));
+        CUDA_TRY(cudaMemsetAsync(ghist, 0, 4 * rwords, st));
+        RadixTemp rt;
+        rt.ghist = ghist;
+        rt.status = ghist + RadixTemp::ghist_words();
+        k_route_key<<<148 * 8, 256, 0, st>>>((const PcbPoint*)d_pts, n32, S0, make_box(origin, dims), d_owner, pb, plan, kA, ghist);
+        NoProf np;
+        int cur = radix_sort<false>(kA, nullptr, kB, nullptr, n32, plan, rt, st, np);
+        k_route_gather<<<div_up(n, 256), 256, 0, st>>>((const PcbPoint*)d_pts, cur ? kB : kA, n32, pb, first_index, batch_size,
+                                                       (PcbPoint*)d_send_pts, d_send_batch);
+        std::vector<u32> h(RADIX_MAX_BINS);
+        CUDA_TRY(cudaMemcpyAsync(h.data(), ghist, 4 * RADIX_MAX_BINS, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        for (u32 r = 0; r < world; r++) send_counts[r] = h[r];
+        CUDA_TRY(cudaFreeAsync(kA, st));
+        CUDA_TRY(cudaFreeAsync(kB, st));
+        CUDA_TRY(cudaFreeAsync(ghist, st));
+        return 2 + plan.npass;
+    });
+}
 
 void trim_host_cache() { g_pinned.trim(); }
 

@@ -27,6 +27,7 @@ FLAG_NO_METADATA_FILE = 8
 EXPORTS = [
     "pcb_open", "pcb_set_stream", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
     "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
+    "pcb_route_bbox", "pcb_route_histogram", "pcb_route_pack",
     "pcb_add_points_device_batched", "pcb_write_metadata", "pcb_get_config", "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
 
@@ -82,6 +83,11 @@ def load_library():
     L.pcb_write_metadata.argtypes = [C.c_char_p, C.c_uint64, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_float),
                                      C.c_uint32, C.c_uint32, C.c_float]
     L.pcb_get_config.argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_float)]
+    L.pcb_route_bbox.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    L.pcb_route_histogram.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_float, C.POINTER(C.c_int32),
+                                      C.POINTER(C.c_uint32), vp]
+    L.pcb_route_pack.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_uint64, C.c_uint32, C.c_float, C.POINTER(C.c_int32),
+                                 C.POINTER(C.c_uint32), vp, C.c_uint32, vp, vp, C.POINTER(C.c_uint64)]
     L.pcb_reserve.argtypes = [vp, C.c_uint64]
     L.pcb_set_stream.argtypes = [vp, vp]
     L.pcb_finish.argtypes = [vp, C.POINTER(PcbStats)]
@@ -214,6 +220,35 @@ class Converter:
             self.close()
         except Exception:
             pass
+
+
+def _route_check(rc):
+    if rc < 0:
+        raise PcbError(rc, (load_library().pcb_last_error(None) or b"").decode())
+    return rc
+
+
+def route_bbox(device, stream, pts_ptr, n, max_cell_size):
+    lo, hi = (C.c_float * 3)(), (C.c_float * 3)()
+    nl = _route_check(load_library().pcb_route_bbox(device, C.c_void_p(stream), C.c_void_p(pts_ptr), n,
+                                                    max_cell_size, lo, hi))
+    return list(lo), list(hi), nl
+
+
+def route_histogram(device, stream, pts_ptr, n, max_cell_size, origin, dims, hist_ptr):
+    o, d = (C.c_int32 * 3)(*origin), (C.c_uint32 * 3)(*dims)
+    return _route_check(load_library().pcb_route_histogram(device, C.c_void_p(stream), C.c_void_p(pts_ptr), n,
+                                                           max_cell_size, o, d, C.c_void_p(hist_ptr)))
+
+
+def route_pack(device, stream, pts_ptr, n, first_index, batch_size, max_cell_size, origin, dims, owner_ptr, world,
+               send_pts_ptr, send_bat_ptr):
+    o, d = (C.c_int32 * 3)(*origin), (C.c_uint32 * 3)(*dims)
+    counts = (C.c_uint64 * world)()
+    nl = _route_check(load_library().pcb_route_pack(device, C.c_void_p(stream), C.c_void_p(pts_ptr), n, first_index,
+                                                    batch_size, max_cell_size, o, d, C.c_void_p(owner_ptr), world,
+                                                    C.c_void_p(send_pts_ptr), C.c_void_p(send_bat_ptr), counts))
+    return list(counts), nl
 
 
 def write_metadata(out_dir, number_of_points, hierarchies, bbox_min, bbox_max, config):

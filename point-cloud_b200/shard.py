@@ -163,3 +163,61 @@ def route_emulated(slices: List[torch.Tensor], batch_size: int, max_cell_size: f
             out_b[r].append(batch[sel])
         first += n
     return [(torch.cat(p).contiguous(), torch.cat(b).contiguous()) for p, b in zip(out_p, out_b)]
+
+
+# ---- device path: the partition runs in the library's own kernels (route.cuh) --------------------------------
+def route_device(pcb, pts_u8: torch.Tensor, first_index: int, batch_size: int, max_cell_size: float, group=None,
+                 stream=None):
+    """Steps 1-4 on the GPU with libpcb's kernels: bounding box -> dense level-0 histogram -> all-reduce ->
+    owner plan -> ONE onesweep pass (owner digit) that writes the all-to-all send buffer -> all-to-all-v.
+    Returns (points, batch ordinals (int32), info dict with launch count)."""
+    import math
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    dev = pts_u8.device
+    n = pts_u8.shape[0]
+    st = stream if stream is not None else torch.cuda.current_stream(dev)
+    sp = st.cuda_stream
+    launches = 0
+    lo, hi, nl = pcb.route_bbox(dev.index, sp, pts_u8.data_ptr(), n, max_cell_size)
+    launches += nl
+    box = torch.tensor(lo + [-v for v in hi], dtype=torch.float32, device=dev)   # min of (lo, -hi)
+    if world > 1:
+        dist.all_reduce(box, op=dist.ReduceOp.MIN, group=group)
+    b = box.cpu().tolist()
+    glo, ghi = b[:3], [-v for v in b[3:]]
+    if not all(math.isfinite(v) for v in glo + ghi):       # no points anywhere
+        return pts_u8[:0], torch.zeros(0, dtype=torch.int32, device=dev), {"launches": launches, "cells": 0}
+    import numpy as np
+    s = np.float32(max_cell_size)
+    origin = [int(np.floor(np.float32(v) / s)) for v in glo]      # metadata.rs:100-102 at level 0
+    dims = [int(np.floor(np.float32(v) / s)) - o + 1 for v, o in zip(ghi, origin)]
+    vol = dims[0] * dims[1] * dims[2]
+    hist = torch.empty(vol, dtype=torch.int32, device=dev)
+    launches += pcb.route_histogram(dev.index, sp, pts_u8.data_ptr(), n, max_cell_size, origin, dims, hist.data_ptr())
+    if world > 1:
+        dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
+    h = hist.cpu()
+    cells = torch.nonzero(h).flatten()
+    owners = plan_owners(cells, h[cells].to(torch.int64), world)
+    owner_tab = torch.zeros(vol, dtype=torch.uint8)
+    owner_tab[cells] = owners.to(torch.uint8)
+    owner_dev = owner_tab.to(dev)
+    send_pts = torch.empty((n, 16), dtype=torch.uint8, device=dev)
+    send_bat = torch.empty((n,), dtype=torch.int32, device=dev)
+    ins, nl = pcb.route_pack(dev.index, sp, pts_u8.data_ptr(), n, first_index, batch_size, max_cell_size, origin, dims,
+                             owner_dev.data_ptr(), world, send_pts.data_ptr(), send_bat.data_ptr())
+    launches += nl
+    info = {"launches": launches, "cells": int(cells.numel()), "box": (origin, dims)}
+    if world == 1:
+        return send_pts, send_bat, info
+    send_counts = torch.tensor(ins, dtype=torch.int64, device=dev)
+    recv_counts = torch.zeros(world, dtype=torch.int64, device=dev)
+    dist.all_to_all_single(recv_counts, send_counts, group=group)
+    outs = recv_counts.cpu().tolist()
+    m = int(sum(outs))
+    recv_pts = torch.empty((m, 16), dtype=torch.uint8, device=dev)
+    recv_bat = torch.empty((m,), dtype=torch.int32, device=dev)
+    dist.all_to_all_single(recv_pts, send_pts, outs, ins, group=group)
+    dist.all_to_all_single(recv_bat, send_bat, outs, ins, group=group)
+    info["sent_bytes"] = 20 * (n - ins[dist.get_rank(group)])
+    return recv_pts, recv_bat, info

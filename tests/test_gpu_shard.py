@@ -67,3 +67,40 @@ def test_sharded_build_files_and_metadata():
         _build_sharded(pts, 2, cfg, bs, out_dir=d_g)
         compare_trees(read_tree(d_o), read_tree(d_g), "oracle", "2 ranks")
         assert open(f"{d_o}/metadata.json").read() == open(f"{d_g}/metadata.json").read()
+
+
+def test_route_device_kernels_match_reference_routing():
+    """libpcb's routing kernels (bbox, dense histogram, owner-digit onesweep pack) against the torch routing."""
+    pcb, shard = load_pcb(), _shard()
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(23)
+    pts = make_points(rng.random((300_000, 3)) * [5000, 3000, 200] - [2500, 1500, 50])
+    raw = torch.from_numpy(pts.view(np.uint8).reshape(-1, 16)).to(dev)
+    n, world, bs, first = raw.shape[0], 4, 777, 123_456
+    sp = torch.cuda.current_stream().cuda_stream
+    lo, hi, _ = pcb.route_bbox(0, sp, raw.data_ptr(), n, 1000.0)
+    xyz = pts.view(np.uint8).reshape(-1, 16)[:, :12].copy().view(np.float32).reshape(-1, 3)
+    assert np.array_equal(np.float32(lo), xyz.min(0)) and np.array_equal(np.float32(hi), xyz.max(0))
+    origin = [int(np.floor(np.float32(v) / np.float32(1000.0))) for v in lo]
+    dims = [int(np.floor(np.float32(v) / np.float32(1000.0))) - o + 1 for v, o in zip(hi, origin)]
+    vol = dims[0] * dims[1] * dims[2]
+    hist = torch.empty(vol, dtype=torch.int32, device=dev)
+    pcb.route_histogram(0, sp, raw.data_ptr(), n, 1000.0, origin, dims, hist.data_ptr())
+    idx = np.floor(xyz / np.float32(1000.0)).astype(np.int64) - np.array(origin)
+    dense = (idx[:, 2] * dims[1] + idx[:, 1]) * dims[0] + idx[:, 0]
+    assert np.array_equal(hist.cpu().numpy(), np.bincount(dense, minlength=vol))
+    cells = np.nonzero(np.bincount(dense, minlength=vol))[0]
+    owners = shard.plan_owners(torch.from_numpy(cells), torch.from_numpy(np.bincount(dense, minlength=vol)[cells]), world)
+    tab = torch.zeros(vol, dtype=torch.uint8)
+    tab[torch.from_numpy(cells)] = owners.to(torch.uint8)
+    tab_dev = tab.to(dev)
+    send_pts = torch.empty((n, 16), dtype=torch.uint8, device=dev)
+    send_bat = torch.empty((n,), dtype=torch.int32, device=dev)
+    counts, _ = pcb.route_pack(0, sp, raw.data_ptr(), n, first, bs, 1000.0, origin, dims, tab_dev.data_ptr(), world,
+                               send_pts.data_ptr(), send_bat.data_ptr())
+    torch.cuda.synchronize()
+    dest = tab.numpy()[dense]
+    order = np.argsort(dest, kind="stable")
+    assert counts == np.bincount(dest, minlength=world).tolist()
+    assert np.array_equal(send_pts.cpu().numpy(), pts.view(np.uint8).reshape(-1, 16)[order])
+    assert np.array_equal(send_bat.cpu().numpy(), ((first + order) // bs).astype(np.int32))
