@@ -167,6 +167,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-scale", type=float, default=1.0, help="scales the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-profile", action="store_true", help="debug: no per-kernel CUDA events in the timed steps")
     ap.add_argument("--no-clocks", action="store_true", help="debug: do not run the nvidia-smi sampler")
     ap.add_argument("--host-log", action="store_true", help="debug: per-step host times (open, finish, close) on stderr")
     args = ap.parse_args()
@@ -221,7 +222,7 @@ def main():
 
     host_log = []
 
-    def step(profile=True):
+    def step(profile=not args.no_profile):
         flags = pcb.FLAG_DEVICE_ONLY | (pcb.FLAG_PROFILE if profile else 0)
         t0 = time.perf_counter()
         cv = pcb.Converter(None, device=local_rank, flags=flags)

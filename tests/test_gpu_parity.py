@@ -111,3 +111,46 @@ def test_point_conservation_large():
     stored = tree_points(nodes)
     assert len(stored) == len(pts) == st.number_of_points
     assert np.array_equal(sort_records(stored), sort_records(pts))
+
+
+def test_clustered_blobs_skewed_tree():
+    """BASELINE.json configs[3] in miniature: Zipf-weighted Gaussian blobs (deep, skewed subtrees)."""
+    rng = np.random.default_rng(17)
+    centres = rng.random((12, 3)) * [800, 800, 50] - [400, 400, 0]
+    sigma = 100.0 ** rng.random(12) * 0.05
+    w = 1.0 / np.arange(1, 13)
+    k = rng.choice(12, size=400_000, p=w / w.sum())
+    xyz = centres[k] + rng.standard_normal((400_000, 3)) * sigma[k, None]
+    st = _check([make_points(xyz)])
+    assert st.hierarchies >= 8
+
+
+def test_terrain_like_default_config():
+    """BASELINE.json configs[1] in miniature: 2.5-D surface over several level-0 cells, default config."""
+    rng = np.random.default_rng(18)
+    xy = rng.random((500_000, 2)) * 900 - 450
+    z = 30 * np.sin(xy[:, 0] / 80) * np.cos(xy[:, 1] / 60) + rng.standard_normal(500_000) * 0.05
+    _check([make_points(np.column_stack([xy, z]))])
+
+
+def test_payload_sort_path_forced():
+    """The (key, position) pairs fallback of the level sort (taken when cell + hex + position bits exceed 64)
+    must give the same trees; forced through PCB_FORCE_PAIRS in a fresh process."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "import numpy as np\n"
+        "from pcutil import compare_trees, load_pcb, make_points, oracle_convert\n"
+        "rng = np.random.default_rng(19)\n"
+        "for cfg, bs, n, ext in (((100, 8, 10.0), 1000, 40000, 50), ((5000, 96, 1000.0), 10000, 200000, 2500)):\n"
+        "    pts = make_points(rng.random((n, 3)) * ext - ext / 2)\n"
+        "    o = oracle_convert([pts], config=cfg, batch_size=bs)\n"
+        "    nodes, mj, st, _ = load_pcb().convert([pts], config=cfg, batch_size=bs)\n"
+        "    compare_trees(o.nodes, nodes, 'oracle', 'gpu-pairs')\n"
+        "    assert mj == o.meta_json and all(o.nodes[k] == nodes[k] for k in nodes)\n"
+        "print('pairs ok')\n") % os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, PCB_FORCE_PAIRS="1")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "pairs ok" in r.stdout, r.stdout + r.stderr
