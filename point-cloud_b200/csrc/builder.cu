@@ -73,6 +73,51 @@ struct PinnedCache {
 };
 static PinnedCache g_pinned;
 
+// Process-wide cache of device work arenas.  The stream-ordered pool re-maps virtual memory when blocks of
+// varying sizes are recycled (measured: milliseconds inside cudaMallocAsync while the GPU idles), so the
+// per-level arrays are bump-allocated from three big blocks instead: [0]/[1] alternate between levels (level h
+// allocates from h & 1 and reads its inputs from the other one), [2] holds the node images of a build.
+// Anything that does not fit falls back to cudaMallocAsync.
+struct Arena {
+    unsigned char* base = nullptr;
+    u64 cap = 0, off = 0;
+};
+struct ArenaSet {
+    int device = -1;
+    bool in_use = false;
+    Arena a[3];
+};
+struct ArenaCache {
+    std::mutex mu;
+    std::vector<ArenaSet*> sets;
+    ArenaSet* acquire(int device) {
+        std::lock_guard<std::mutex> g(mu);
+        for (auto* s : sets)
+            if (s->device == device && !s->in_use) { s->in_use = true; return s; }
+        ArenaSet* s = new ArenaSet();
+        s->device = device;
+        s->in_use = true;
+        sets.push_back(s);
+        return s;
+    }
+    void release(ArenaSet* s) {
+        std::lock_guard<std::mutex> g(mu);
+        s->in_use = false;
+    }
+    void trim() {
+        std::lock_guard<std::mutex> g(mu);
+        for (auto* s : sets) {
+            if (s->in_use) continue;
+            cudaSetDevice(s->device);
+            for (auto& a : s->a) {
+                if (a.base) cudaFree(a.base);
+                a = Arena();
+            }
+        }
+    }
+};
+static ArenaCache g_arenas;
+
 struct Scratch {  // small device-resident results, mirrored in pinned host memory
     u64 diffmask;
     u32 err;
@@ -142,7 +187,7 @@ class BuilderImpl {
         cudaStreamSynchronize(st);
         cudaStreamSynchronize(copy_st);
         for (auto& l : levels) {
-            if (l.d_image) cudaFreeAsync(l.d_image, st);
+            if (l.d_image && !in_arena(l.d_image)) cudaFreeAsync(l.d_image, st);
             if (l.h_image) g_pinned.put(l.h_image, l.h_cap);
         }
         if (d_in && !in_borrowed) cudaFree(d_in);
@@ -150,18 +195,54 @@ class BuilderImpl {
         if (d_scr) cudaFreeAsync(d_scr, st);
         if (h_scr) g_pinned.put(h_scr, h_scr_cap);
         cudaStreamSynchronize(st);
+        if (arenas) g_arenas.release(arenas);
         if (st && own_stream) cudaStreamDestroy(st);
         if (copy_st) cudaStreamDestroy(copy_st);
     }
 
+    ArenaSet* arenas = nullptr;
+    int cur_arena = 0;
+    void arena_prepare(int which, u64 bytes) {   // (re)size an arena; only while nothing of it is in use
+        Arena& a = arenas->a[which];
+        a.off = 0;
+        if (a.cap >= bytes) return;
+        CUDA_TRY(cudaStreamSynchronize(st));
+        if (a.base) CUDA_TRY(cudaFree(a.base));
+        a.base = nullptr;
+        a.cap = 0;
+        if (cudaMalloc((void**)&a.base, bytes) != cudaSuccess) {   // not fatal: everything falls back to the pool
+            cudaGetLastError();
+            a.base = nullptr;
+            return;
+        }
+        a.cap = bytes;
+    }
+    void* arena_alloc(int which, u64 bytes) {
+        if (!arenas) return nullptr;
+        Arena& a = arenas->a[which];
+        u64 start = (a.off + 255) & ~255ull;
+        if (!a.base || start + bytes > a.cap) return nullptr;
+        a.off = start + bytes;
+        return a.base + start;
+    }
+    bool in_arena(const void* p) const {
+        if (!arenas) return false;
+        for (auto& a : arenas->a)
+            if (a.base && (const unsigned char*)p >= a.base && (const unsigned char*)p < a.base + a.cap) return true;
+        return false;
+    }
     template <class T>
-    T* dalloc(u64 n) {
+    T* dalloc_from(int which, u64 n) {
+        const u64 bytes = std::max<u64>(n, 1) * sizeof(T);
+        if (void* q = arena_alloc(which, bytes)) return (T*)q;
         void* p = nullptr;
-        CUDA_TRY(cudaMallocAsync(&p, std::max<u64>(n, 1) * sizeof(T), st));
+        CUDA_TRY(cudaMallocAsync(&p, bytes, st));
         return (T*)p;
     }
+    template <class T>
+    T* dalloc(u64 n) { return dalloc_from<T>(cur_arena, n); }
     void dfree(void* p) {
-        if (p) CUDA_TRY(cudaFreeAsync(p, st));
+        if (p && !in_arena(p)) CUDA_TRY(cudaFreeAsync(p, st));
     }
 
     int cls(const char* name) {
@@ -366,7 +447,12 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     if (n_in == 0) return;
     const u32 n0 = (u32)n_in;
     const float S0 = max_cell_size;
-    if (!d_scr) d_scr = dalloc<Scratch>(1);
+    if (!d_scr) CUDA_TRY(cudaMallocAsync((void**)&d_scr, sizeof(Scratch), st));
+    if (!arenas) arenas = g_arenas.acquire(device);
+    arena_prepare(0, 68ull * n_in + (64ull << 20));
+    arena_prepare(1, 68ull * n_in + (64ull << 20));
+    arena_prepare(2, 18ull * n_in + (64ull << 20));
+    cur_arena = 1;   // level-0 staging and level 0's inputs; level h then allocates from arena h & 1
 
     // ---- stage 0a: bounding box + validation
     Scratch init;
@@ -484,6 +570,8 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                               NodeSource* existing) {
     const LevelGeom g = make_geom(max_cell_size, dim, h);
     const u32 n_new = n;  // arrivals proper (incumbents of merge mode are added below)
+    cur_arena = (int)(h & 1u);          // the other arena holds this level's inputs (written by the previous level)
+    arenas->a[cur_arena].off = 0;
     arrivals += n_new;
 
     // ---- merge mode: read the node files of the cells that receive arrivals (converter.rs:160-207)
@@ -645,7 +733,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     LevelImage img;
     img.hierarchy = h;
     img.bytes = tot.image_bytes;
-    img.d_image = dalloc<unsigned char>(std::max<u64>(img.bytes, 16));
+    img.d_image = dalloc_from<unsigned char>(2, std::max<u64>(img.bytes, 16));
     PcbPoint* next_pts = dalloc<PcbPoint>(tot.n_next);
     u32* next_bat = dalloc<u32>(tot.n_next);
     u32* next_cell_start = dalloc<u32>((u64)tot.ncell_next + 1);
@@ -840,7 +928,10 @@ int route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uin
     });
 }
 
-void trim_host_cache() { g_pinned.trim(); }
+void trim_host_cache() {
+    g_pinned.trim();
+    g_arenas.trim();
+}
 
 int device_count() {
     int c = 0;
