@@ -669,7 +669,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     rt.status = rt.ghist + RadixTemp::ghist_words();
     CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
     pb();
-    k_cellgeo<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, cell_start, ncell, g, geo);
+    k_cellgeo<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, cell_start, ncell, g, geo, &d_scr->err);
     k_hexkey<PAIRS><<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay,
                                                                             plan, kA, vA, rt.ghist, &d_scr->err);
     pe("hexkey", 2, n, (PAIRS ? 28ull : 24ull) * n);
@@ -685,15 +685,18 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     // ---- stage 4: contest
     u32* win_src = dalloc<u32>(n);
     u32* win_end = dalloc<u32>(ncell);
-    const u64 tmp_bytes = std::max<u64>(std::max<u64>(chain_scan_temp_bytes<256, 8>(n),
-                                                      chain_scan_temp_bytes<OCT_THREADS, OCT_ITEMS>(n)),
+    const u64 tmp_bytes = std::max<u64>(std::max<u64>(chain_scan_temp_bytes<64, 8>(n),
+                                                      chain_scan_temp_bytes<64, 8>(n)),
                                         chain_scan_temp_bytes<256, 4>(ncell));
     void* scan_tmp = dalloc<unsigned char>(tmp_bytes);
     ContestOp<PAIRS> cop{ks, vs, n, lay, g, pts, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
     pb();
     static const int contest_minb = getenv("PCB_CONTEST_MINB") ? atoi(getenv("PCB_CONTEST_MINB")) : 3;  // tuning hook
-    int nl = contest_minb == 4 ? chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, n, scan_tmp, st)
-                               : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, n, scan_tmp, st);
+    int nl = contest_minb == 4   ? chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, n, scan_tmp, st)
+             : contest_minb == 6 ? chain_scan<ContestOp<PAIRS>, 128, 8, 6>(cop, n, scan_tmp, st)
+             : contest_minb == 8 ? chain_scan<ContestOp<PAIRS>, 128, 8, 8>(cop, n, scan_tmp, st)
+             : contest_minb == 12 ? chain_scan<ContestOp<PAIRS>, 64, 8, 12>(cop, n, scan_tmp, st)
+                                 : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, n, scan_tmp, st);
     pe("contest", nl, n, (PAIRS ? 36ull : 32ull) * n);
     trace_mark(st, "contest", h, n);
 

@@ -27,7 +27,7 @@ struct LevelGeom {
 struct __align__(16) CellGeo {
     int hx, hy, hz;      // origin of the hex window (hex key of the cell's min corner minus the margin)
     u32 start;           // first arrival
-    int ix2, iy2, iz2;   // 2 * cell index = index of child octant 0 (metadata.rs:100-102 at level + 1)
+    float tx, ty, tz;    // octant thresholds: floor(p / S_child) >= 2 * index + 1  <=>  p >= t   (see octant_threshold)
     u32 end;             // one past the last arrival
 };
 
@@ -188,9 +188,26 @@ __global__ void k_l0_gather(const PcbPoint* __restrict__ in_pts, const u64* __re
 }
 
 // ---------------------------------------------------------------------------------------------
-// Stage 1: per-cell constants (hex window origin, child index base, arrival range).
+// The child octant of a loser is bit-for-bit cell_index(p, level + 1) - 2 * cell_index (converter.rs:68,
+// metadata.rs:100-102).  x -> floor(x / S_child) is monotone, so for the odd child index m = 2 * i + 1 there is
+// one smallest float t with floor(t / S_child) >= m, and "p lands in the upper half" is exactly p >= t.  The
+// threshold is found once per cell and axis with the reference's own division, so that the per-point work is a
+// compare instead of an IEEE division.
+__device__ __forceinline__ float octant_threshold(int i, float S_child, u32* err) {
+    const long long m = 2ll * i + 1ll;
+    float t = __fmul_rn((float)m, S_child);
+    int guard = 0;
+    // walk down while the predecessor still reaches m, then up until t itself does
+    while (guard++ < 64 && (long long)cell_index_axis(nextafterf(t, -INFINITY), S_child) >= m) t = nextafterf(t, -INFINITY);
+    while (guard++ < 128 && (long long)cell_index_axis(t, S_child) < m) t = nextafterf(t, INFINITY);
+    if ((long long)cell_index_axis(t, S_child) < m || (long long)cell_index_axis(nextafterf(t, -INFINITY), S_child) >= m)
+        atomicOr(err, PCB_DERR_NEST);
+    return t;
+}
+
+// Stage 1: per-cell constants (hex window origin, octant thresholds, arrival range).
 __global__ void k_cellgeo(const int* __restrict__ cell_idx, const u32* __restrict__ cell_start, u32 ncell, LevelGeom g,
-                          CellGeo* __restrict__ geo) {
+                          CellGeo* __restrict__ geo, u32* __restrict__ err) {
     u32 c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= ncell) return;
     const int ix = cell_idx[3 * c + 0], iy = cell_idx[3 * c + 1], iz = cell_idx[3 * c + 2];
@@ -201,7 +218,9 @@ __global__ void k_cellgeo(const int* __restrict__ cell_idx, const u32* __restric
     CellGeo o;
     o.hx = k.x - g.mx; o.hy = k.y - g.my; o.hz = k.z - g.mz;
     o.start = cell_start[c];
-    o.ix2 = 2 * ix; o.iy2 = 2 * iy; o.iz2 = 2 * iz;
+    o.tx = octant_threshold(ix, g.S_child, err);
+    o.ty = octant_threshold(iy, g.S_child, err);
+    o.tz = octant_threshold(iz, g.S_child, err);
     o.end = cell_start[c + 1];
     geo[c] = o;
 }
@@ -210,7 +229,7 @@ __device__ __forceinline__ CellGeo load_geo(const CellGeo* __restrict__ geo, u32
     uint4 a = __ldg(p), b = __ldg(p + 1);
     CellGeo o;
     o.hx = (int)a.x; o.hy = (int)a.y; o.hz = (int)a.z; o.start = a.w;
-    o.ix2 = (int)b.x; o.iy2 = (int)b.y; o.iz2 = (int)b.z; o.end = b.w;
+    o.tx = __uint_as_float(b.x); o.ty = __uint_as_float(b.y); o.tz = __uint_as_float(b.z); o.end = b.w;
     return o;
 }
 
@@ -347,7 +366,8 @@ struct ContestOp {
         if (lane == 31) nextk = (base + ITEMS < n) ? keys[base + ITEMS] : ~0ull;
         u32 cprev = PCB_NONE;
         CellGeo cg;
-        cg.hx = cg.hy = cg.hz = cg.ix2 = cg.iy2 = cg.iz2 = 0;
+        cg.hx = cg.hy = cg.hz = 0;
+        cg.tx = cg.ty = cg.tz = 0.0f;
         cg.start = cg.end = 0;
 #pragma unroll
         for (int k = 0; k < ITEMS; k++) {
@@ -369,14 +389,7 @@ struct ContestOp {
             hk.y = (i32)((u32)(G >> g.bx) & ((1u << g.by) - 1u)) + cg.hy;
             hk.z = (i32)((u32)(G >> (g.bx + g.by)) & ((1u << g.bz) - 1u)) + cg.hz;
             const float d2 = hex_d2(hk, px, py, pz, g.R, g.half_sqrt3, g.row_pitch);
-            int dx = cell_index_axis(px, g.S_child) - cg.ix2;
-            int dy = cell_index_axis(py, g.S_child) - cg.iy2;
-            int dz = cell_index_axis(pz, g.S_child) - cg.iz2;
-            if (((u32)dx | (u32)dy | (u32)dz) > 1u) {
-                atomicOr(err, PCB_DERR_NEST);
-                dx &= 1; dy &= 1; dz &= 1;
-            }
-            u32 meta = (u32)(dx * 4 + dy * 2 + dz);
+            u32 meta = (px >= cg.tx ? 4u : 0u) | (py >= cg.ty ? 2u : 0u) | (pz >= cg.tz ? 1u : 0u);
             const bool head = (i == 0) || Gp != G;
             const bool last = (i + 1 == n);
             const bool tail = last || Gn != G;
@@ -509,9 +522,7 @@ struct OctScanOp {
 
 // Specialised single-pass kernel for the scan above: inside a tile the eight counters are packed 4 x 16 bit
 // into two 64-bit words (a tile has 2048 arrivals), only the cross-tile prefix uses the 9-word state.
-#define OCT_THREADS 256
-#define OCT_ITEMS 8
-#define OCT_TILE (OCT_THREADS * OCT_ITEMS)
+#define OCT_TILE_MAX 4096   // 16-bit packed counters hold a whole tile
 struct OctPacked {
     u64 lo, hi;   // counters of octants 0-3 / 4-7, 16 bits each
     u32 head;
@@ -523,9 +534,12 @@ __device__ __forceinline__ OctPacked oct_combine(const OctPacked& a, const OctPa
     r.head = a.head | b.head;
     return r;
 }
+template <int OCT_THREADS, int OCT_ITEMS>
 __global__ void __launch_bounds__(OCT_THREADS)
 k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     constexpr int WARPS = OCT_THREADS / 32;
+    constexpr int OCT_TILE = OCT_THREADS * OCT_ITEMS;
+    static_assert(OCT_TILE <= OCT_TILE_MAX && OCT_ITEMS % 8 == 0, "tile shape");
     __shared__ OctPacked s_warp[WARPS];
     __shared__ Oct8 s_prefix;
     __shared__ u32 s_tile;
@@ -648,20 +662,29 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     }
     if (base + OCT_ITEMS <= n) {
         uint4* dst = (uint4*)(op.rank + base);
-        dst[0] = make_uint4(rk[0], rk[1], rk[2], rk[3]);
-        dst[1] = make_uint4(rk[4], rk[5], rk[6], rk[7]);
+#pragma unroll
+        for (int k = 0; k < OCT_ITEMS / 4; k++) dst[k] = make_uint4(rk[4 * k], rk[4 * k + 1], rk[4 * k + 2], rk[4 * k + 3]);
     } else {
 #pragma unroll
         for (int k = 0; k < OCT_ITEMS; k++)
             if (base + k < n) op.rank[base + k] = rk[k];
     }
 }
-static inline int octscan(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
-    const u32 ntiles = div_up(n, OCT_TILE);
+template <int T, int I>
+static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
+    const u32 ntiles = div_up(n, T * I);
     if (!ntiles) return 0;
     cudaMemsetAsync(temp, 0, chain_temp_bytes(ntiles), st);
-    k_octscan<<<ntiles, OCT_THREADS, 0, st>>>(op, n, ntiles, (uint4*)temp);
+    k_octscan<T, I><<<ntiles, T, 0, st>>>(op, n, ntiles, (uint4*)temp);
     return 1;
+}
+static inline int octscan(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
+    static const int variant = getenv("PCB_OCT_VARIANT") ? atoi(getenv("PCB_OCT_VARIANT")) : 0;   // tuning hook
+    switch (variant) {
+        case 1: return octscan_launch<256, 8>(op, n, temp, st);
+        case 2: return octscan_launch<128, 16>(op, n, temp, st);
+        default: return octscan_launch<256, 16>(op, n, temp, st);   // measured best of the three on C2
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
