@@ -130,6 +130,11 @@ class ClockSampler:
                 "samples": len(inside), "source": self.mode, "reasons": sorted(reasons)}
 
 
+def workload_name(n):
+    return (f"C2 terrain, {n} points per GPU, 2.5-D heightfield + noise, default config (5000/96/1000.0), "
+            f"batch 10000")
+
+
 def run_reference(args, rank, world):
     """CPU arm: the oracle port on the host cores.  Rank 0 only."""
     if rank != 0:
@@ -151,7 +156,8 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": round(v, 4), "unit": UNIT, "n_gpus": args.gpus,
         "steps": len(vals), "warmup": 0, "ms_per_step": round(dt * 1e3, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32+u64", "data": "synthetic",
-        "config": {"workload": "C2 terrain 100M (bounded CPU sample)", "sample_points": n},
+        "config": {"workload": workload_name(args.points), "points_per_gpu": args.points,
+                   "sample_points": n, "sample": sample},
         "cpu_baseline": {"value": round(v, 4), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": round(v, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -353,8 +359,7 @@ def main():
         out = {"metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                "warmup": args.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True,
                "scaling": "weak", "vs_baseline": None, "dtype": "f32+u64", "data": "synthetic",
-               "config": {"workload": f"C2 terrain, {n} points per GPU, 2.5-D heightfield + noise, default config "
-                                      f"(5000/96/1000.0), batch 10000", "points_per_gpu": n,
+               "config": {"workload": workload_name(n), "points_per_gpu": n,
                           "l2": "inputs (1.6 GB/step) larger than L2, no explicit flush",
                           "levels": int(last.levels_built), "arrivals_per_point": round(last.arrivals / n, 3),
                           "nodes": int(last.nodes_written), "sharding": ("none (1 GPU)" if world == 1 else

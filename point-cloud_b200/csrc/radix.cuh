@@ -27,6 +27,9 @@
 #define RADIX_FLAG_AGG 0x40000000u
 #define RADIX_FLAG_INCL 0x80000000u
 #define RADIX_COUNT_MASK 0x3FFFFFFFu
+#ifndef RADIX_WINDOW
+#define RADIX_WINDOW 8   // predecessors polled per look-back step (independent loads)
+#endif
 
 struct RadixPlan {
     int npass;
@@ -253,12 +256,13 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
                 const volatile u32* sp = my_status + q - bins;   // status word of tile t, digit d
                 const u32 back = bins;
                 bool done = false;
-                while (!done) {   // 8 predecessors per step: their status words are independent loads
-                    u32 w[8];
+                while (!done) {   // RADIX_WINDOW predecessors per step: their status words are independent loads
+                    u32 w[RADIX_WINDOW];
 #pragma unroll
-                    for (int x = 0; x < 8; x++) w[x] = (t - x >= 0) ? *(sp - (size_t)x * back) : RADIX_FLAG_INCL;
+                    for (int x = 0; x < RADIX_WINDOW; x++)
+                        w[x] = (t - x >= 0) ? *(sp - (size_t)x * back) : RADIX_FLAG_INCL;
 #pragma unroll
-                    for (int x = 0; x < 8; x++) {
+                    for (int x = 0; x < RADIX_WINDOW; x++) {
                         if (!done) {
                             u32 s = w[x];
                             while ((s & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u) s = *(sp - (size_t)x * back);
@@ -266,8 +270,8 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
                             done = (s & RADIX_FLAG_INCL) != 0u;
                         }
                     }
-                    t -= 8;
-                    sp -= (size_t)8 * back;
+                    t -= RADIX_WINDOW;
+                    sp -= (size_t)RADIX_WINDOW * back;
                 }
                 *(volatile u32*)&my_status[q] = ((prev + count[q]) & RADIX_COUNT_MASK) | RADIX_FLAG_INCL;
             }
