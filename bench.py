@@ -203,7 +203,7 @@ def main():
     # WHOLE extent, so (world-1)/world of them must cross NVLink to reach the owner of their level-0 cell.
     side_x = (n / DENSITY) ** 0.5 * world
     side_y = (n / DENSITY) ** 0.5
-    pts = synth.terrain(n, 2 + rank, dev, (-side_x / 2, side_x / 2, -side_y / 2, side_y / 2))
+    pts = synth.terrain(n, 2 + rank, dev, (-side_x / 2, side_x / 2, -side_y / 2, side_y / 2), surface_seed=2)
     torch.cuda.synchronize()
     stream = torch.cuda.current_stream()
     shard = None
@@ -283,6 +283,16 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     ms_per_step = ms / args.steps
+    # per-rank share of the job (points owned after the exchange, arrivals over all levels, own device time)
+    ranks_info = None
+    if world > 1:
+        mine = torch.tensor([float(last.points_added), float(last.arrivals), ev0.elapsed_time(ev1) / args.steps],
+                            device=dev, dtype=torch.float64)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        ranks_info = {"points_owned": [int(x[0].item()) for x in allr],
+                      "arrivals": [int(x[1].item()) for x in allr],
+                      "ms_per_step": [round(float(x[2].item()), 2) for x in allr]}
     if args.host_log:
         print("host_log (open, finish, close) ms:", host_log[-args.steps:], file=sys.stderr)
     value = n * world / (ms_per_step * 1e-3) / 1e6
@@ -364,7 +374,8 @@ def main():
                           "levels": int(last.levels_built), "arrivals_per_point": round(last.arrivals / n, 3),
                           "nodes": int(last.nodes_written), "sharding": ("none (1 GPU)" if world == 1 else
                                        "level-0 cell owners; exchange = libpcb routing kernels + NCCL all-to-all-v, "
-                                       "inside the timed step"), "step_ms": step_ms},
+                                       "inside the timed step"), "step_ms": step_ms,
+                          **({"ranks": ranks_info} if ranks_info else {})},
                "e2e": e2e, "gpu_launches": int(launches) + route_timed, "roofline": roofline, "cpu_baseline": cpu,
                "clocks": clocks}
         print(json.dumps(out))

@@ -37,10 +37,12 @@ def _pack(xyz: torch.Tensor, gen: torch.Generator) -> torch.Tensor:
     return out
 
 
-def terrain(n: int, seed: int = 2, device="cpu", extent=(-2000.0, 2000.0, -2000.0, 2000.0), chunk=1 << 24) -> torch.Tensor:
+def terrain(n: int, seed: int = 2, device="cpu", extent=(-2000.0, 2000.0, -2000.0, 2000.0), chunk=1 << 24,
+            surface_seed: int | None = None) -> torch.Tensor:
     """C2: 2.5-D LiDAR-like terrain: x, y uniform in the extent, z = 3-octave value noise (amplitude 120 m,
     base wavelength 1 km) + Gaussian sensor noise sigma = 0.05 m.  Density for the named config:
-    1e8 points over 4 km x 4 km = 6.25 points/m^2."""
+    1e8 points over 4 km x 4 km = 6.25 points/m^2.  `surface_seed` (default: seed) picks the height field, `seed`
+    the sample positions: slices of one big survey share the surface and differ in the positions."""
     gen = torch.Generator(device=device)
     gen.manual_seed(seed)
     out = torch.empty((n, 16), dtype=torch.uint8, device=device)
@@ -49,8 +51,9 @@ def terrain(n: int, seed: int = 2, device="cpu", extent=(-2000.0, 2000.0, -2000.
         m = min(chunk, n - s)
         x = torch.rand(m, device=device, generator=gen) * (x1 - x0) + x0
         y = torch.rand(m, device=device, generator=gen) * (y1 - y0) + y0
-        z = (_value_noise(x, y, 1000.0, seed) + 0.5 * _value_noise(x, y, 500.0, seed + 1) +
-             0.25 * _value_noise(x, y, 250.0, seed + 2)) * (120.0 / 1.75)
+        ss = seed if surface_seed is None else surface_seed
+        z = (_value_noise(x, y, 1000.0, ss) + 0.5 * _value_noise(x, y, 500.0, ss + 1) +
+             0.25 * _value_noise(x, y, 250.0, ss + 2)) * (120.0 / 1.75)
         z = z + torch.randn(m, device=device, generator=gen) * 0.05
         out[s:s + m] = _pack(torch.stack([x, y, z], dim=1).to(torch.float32), gen)
     return out
