@@ -542,11 +542,8 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     static_assert(OCT_TILE <= OCT_TILE_MAX && OCT_ITEMS % 8 == 0, "tile shape");
     __shared__ OctPacked s_warp[WARPS];
     __shared__ Oct8 s_prefix;
-    __shared__ u32 s_tile;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd((u32*)(desc + 2 * (u64)ntiles), 1u);
-    __syncthreads();
-    const u32 tile = s_tile;
+    const u32 tile = blockIdx.x;   // see k_chain_scan
     const u64 base = (u64)tile * OCT_TILE + (u64)tid * OCT_ITEMS;
 
     // per element: octant (8 = none) | first << 4 | last << 5

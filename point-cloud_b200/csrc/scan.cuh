@@ -267,11 +267,13 @@ __global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 
     constexpr int WARPS = THREADS / 32;
     __shared__ State s_warp[WARPS];
     __shared__ State s_prefix;
-    __shared__ u32 s_tile;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd((u32*)(desc + 2 * (u64)ntiles), 1u);
-    __syncthreads();
-    const u32 tile = s_tile;
+    // Tile = block index.  The look-back needs every earlier tile to be running or done: blocks of a 1-D grid are
+    // dispatched in index order (the assumption CUB's decoupled look-back scan makes as well).  An atomic ticket
+    // instead costs its round trip (about 1 us, a third of a tile's lifetime here) before the first load is
+    // issued; taking the ticket one tile ahead in a persistent block hides that but leaves tickets idle for a
+    // tile's duration, which the tiles behind pay for in their look-back (measured: 2x slower).
+    const u32 tile = blockIdx.x;
     const u64 base = (u64)tile * (THREADS * ITEMS) + (u64)tid * ITEMS;
 
     State v[ITEMS];

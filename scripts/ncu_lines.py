@@ -1,10 +1,11 @@
 #!/usr/bin/env python
 """Executed warp instructions and stall samples per CUDA source line for one kernel of an .ncu-rep
-(needs -lineinfo and --import-source on).  usage: ncu_lines.py rep kernel_regex [topN] [instance]"""
+(needs -lineinfo and --import-source on).  usage: ncu_lines.py rep kernel_regex [topN] [instance] [file suffix, default: the kernel's own file]"""
 import csv, subprocess, sys, collections
 rep, rx = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
 inst = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+want_file = sys.argv[5] if len(sys.argv) > 5 else None
 out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--print-source', 'cuda,sass',
                       '--kernel-name', 'regex:' + rx], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
@@ -12,14 +13,16 @@ rows = list(csv.reader(out.splitlines()))
 # the page is a sequence of (File Path, Function Name, table) blocks; a launch contributes one block per source
 # file that has inlined code in it, the kernel's own file first.  Only that first block is used: its lines carry
 # the inlined instructions too.
-kern, k, fpath, first = [], None, '?', None
+kern, k, fpath, first, launch = [], None, '?', None, -1
 for r in rows:
     if r and r[0] == 'File Path':
         fpath = r[1]
         first = first or fpath
+        if fpath == first:
+            launch += 1
         k = None
     elif r and r[0] == 'Function Name':
-        if fpath == first:
+        if (fpath.endswith(want_file) if want_file else fpath == first):
             k = [['File Name', fpath]]
             kern.append((r[1], k))
     elif k is not None:
