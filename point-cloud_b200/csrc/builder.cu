@@ -57,7 +57,7 @@ struct PinnedCache {
         }
         void* p = nullptr;
         u64 sz = (bytes + (1u << 20) - 1) & ~((u64)(1u << 20) - 1);
-        CUDA_TRY(cudaHostAlloc(&p, sz, cudaHostAllocDefault));
+        CUDA_TRY(cudaHostAlloc(&p, sz, cudaHostAllocMapped));   // mapped: kernels publish small results into it
         *got = sz;
         return p;
     }
@@ -85,7 +85,7 @@ struct Arena {
 struct ArenaSet {
     int device = -1;
     bool in_use = false;
-    Arena a[3];
+    Arena a[4];   // 0/1: per-level arrays (ping-pong), 2: node images, 3: level-0 arrivals of the whole run
 };
 struct ArenaCache {
     std::mutex mu;
@@ -118,6 +118,23 @@ struct ArenaCache {
 };
 static ArenaCache g_arenas;
 
+// Small results go to the host by kernel stores into mapped pinned memory, not through the copy engine: a
+// device-to-host memcpy queues behind the node-image download that is in flight on the other stream (hundreds of
+// MB), and the host needs these few bytes to size the next level - measured 2-4 ms of build stall per level.
+__global__ void k_publish(const unsigned char* __restrict__ src, unsigned char* __restrict__ dst, u64 bytes,
+                          int vec16) {
+    const u64 i = ((u64)blockIdx.x * blockDim.x + threadIdx.x) * 16ull;
+    if (i >= bytes) return;
+    if (vec16 && i + 16 <= bytes) {
+        *(uint4*)(dst + i) = *(const uint4*)(src + i);
+    } else {   // 4-byte aligned data (slices of index tables), or the tail
+        const u64 e = i + 16 < bytes ? i + 16 : bytes;
+        u64 b = i;
+        for (; b + 4 <= e; b += 4) *(u32*)(dst + b) = *(const u32*)(src + b);
+        for (; b < e; b++) dst[b] = src[b];
+    }
+}
+
 struct Scratch {  // small device-resident results, mirrored in pinned host memory
     u64 diffmask;
     u32 err;
@@ -148,6 +165,7 @@ class BuilderImpl {
 
     Scratch* d_scr = nullptr;
     Scratch* h_scr = nullptr;
+    std::vector<std::pair<void*, u64>> host_tmps;
     u64 h_scr_cap = 0;
     u32* d_bat_in = nullptr;   // optional per-point batch ordinals (pcb_add_points_device_batched)
     bool bat_owned = false;
@@ -163,6 +181,7 @@ class BuilderImpl {
     cudaEvent_t prof_a = nullptr;
     u64 launches = 0, arrivals = 0;
     u32 levels_built = 0;
+    bool inputs_borrowed = false;   // build_level must not free its inputs (slices of the run's level-0 arrays)
     double h2d_s = 0, build_s = 0, d2h_s = 0;
 
     BuilderImpl(int dev, uint32_t fl) : device(dev), flags(fl), profile((fl & PCB_FLAG_PROFILE) != 0) {
@@ -195,6 +214,7 @@ class BuilderImpl {
         if (d_scr) cudaFreeAsync(d_scr, st);
         if (h_scr) g_pinned.put(h_scr, h_scr_cap);
         cudaStreamSynchronize(st);
+        for (auto& t : host_tmps) g_pinned.put(t.first, t.second);
         if (arenas) g_arenas.release(arenas);
         if (st && own_stream) cudaStreamDestroy(st);
         if (copy_st) cudaStreamDestroy(copy_st);
@@ -288,8 +308,26 @@ class BuilderImpl {
         st = s;
         own_stream = false;
     }
+    // device -> pinned host, stream-ordered; both 16-byte aligned
+    void publish(void* host_pinned, const void* dev, u64 bytes) {
+        if (!bytes) return;
+        if (bytes <= (4ull << 20)) {
+            const int vec16 = (((uintptr_t)dev | (uintptr_t)host_pinned) & 15u) == 0;
+            if ((((uintptr_t)dev | (uintptr_t)host_pinned) & 3u) != 0) throw Error{PCB_ERR_ARG, "internal: unaligned publish"};
+            k_publish<<<div_up(div_up(bytes, 16), 256), 256, 0, st>>>((const unsigned char*)dev,
+                                                                       (unsigned char*)host_pinned, bytes, vec16);
+        } else {
+            CUDA_TRY(cudaMemcpyAsync(host_pinned, dev, bytes, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    void* host_tmp(u64 bytes) {   // pinned scratch that lives until the end of the run
+        u64 got = 0;
+        void* p = g_pinned.get(std::max<u64>(bytes, 16), &got);
+        host_tmps.emplace_back(p, got);
+        return p;
+    }
     void fetch_scratch() {
-        CUDA_TRY(cudaMemcpyAsync(h_scr, d_scr, sizeof(Scratch), cudaMemcpyDeviceToHost, st));
+        publish(h_scr, d_scr, sizeof(Scratch));
         CUDA_TRY(cudaStreamSynchronize(st));
     }
     void check_err() {
@@ -394,6 +432,15 @@ class BuilderImpl {
     void build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start, int*& cell_idx, u32& n, u32& ncell,
                      NodeSource* existing);
     bool pairs_mode_for(u32 n, u32 ncell, const LevelGeom& g);
+    // Level-0 arrivals per wave.  With node images going to the host a quarter of the run per wave lets the
+    // downloads overlap the build; device-only runs have nothing to overlap and keep one wave (fewer, larger
+    // launches) until the per-level arrays (68 B per arrival, twice) would crowd the device.
+    u64 wave_points(u64 n0) const {
+        static const u64 forced = getenv("PCB_WAVE_POINTS") ? strtoull(getenv("PCB_WAVE_POINTS"), nullptr, 10) : 0;
+        if (forced) return forced;
+        if (flags & PCB_FLAG_DEVICE_ONLY) return 400ull << 20;
+        return std::min<u64>(std::max<u64>(n0 / 4, 16ull << 20), 400ull << 20);
+    }
 };
 
 static int bits_for(u32 range) {
@@ -449,10 +496,12 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     const float S0 = max_cell_size;
     if (!d_scr) CUDA_TRY(cudaMallocAsync((void**)&d_scr, sizeof(Scratch), st));
     if (!arenas) arenas = g_arenas.acquire(device);
-    arena_prepare(0, 68ull * n_in + (64ull << 20));
-    arena_prepare(1, 68ull * n_in + (64ull << 20));
+    // Arena 0 first serves the level-0 staging (keys A/B, histograms, look-back state: ~17 B per point); arenas 0/1
+    // are sized for the largest wave once the level-0 cells are known (below).  Sizes only ever grow, so a process
+    // that converts clouds of one size allocates once.
+    arena_prepare(0, std::max<u64>(arenas->a[0].cap, 17ull * n_in + (64ull << 20)));
     arena_prepare(2, 18ull * n_in + (64ull << 20));
-    cur_arena = 1;   // level-0 staging and level 0's inputs; level h then allocates from arena h & 1
+    cur_arena = 0;
 
     // ---- stage 0a: bounding box + validation
     Scratch init;
@@ -511,8 +560,9 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     u32* vs = cur ? vB : vA;
     trace_mark(st, "l0_sort", 0, n0);
     u32 ncell_ub = (u32)std::min<u64>(n0, vol);
-    u32* cell_start = dalloc<u32>((u64)ncell_ub + 1);
-    int* cell_idx = dalloc<int>(3ull * ncell_ub);
+    arena_prepare(3, 20ull * n0 + 16ull * ncell_ub + (1ull << 20));
+    u32* cell_start = dalloc_from<u32>(3, (u64)ncell_ub + 1);
+    int* cell_idx = dalloc_from<int>(3, 3ull * ncell_ub);
     void* scan_tmp = dalloc<unsigned char>(chain_scan_temp_bytes<256, 8>(n0));
     L0HeadOp hop{ks, n0, pb0, box, cell_start, cell_idx, &d_scr->ncell};
     pb();
@@ -520,8 +570,8 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     pe("l0_heads", nl, n0, 8ull * n0);
     BatchSeg* d_segs = dalloc<BatchSeg>(segs.size());
     CUDA_TRY(cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(BatchSeg), cudaMemcpyHostToDevice, st));
-    PcbPoint* pts = dalloc<PcbPoint>(n0);
-    u32* bat = dalloc<u32>(n0);
+    PcbPoint* pts = dalloc_from<PcbPoint>(3, n0);
+    u32* bat = dalloc_from<u32>(3, n0);
     pb();
     k_l0_gather<<<div_up(n0, 256), 256, 0, st>>>(d_in, ks, vs, n0, pb0, d_segs, (u32)segs.size(), d_bat_in, pts, bat);
     pe("l0_gather", 1, n0, 44ull * n0);
@@ -530,17 +580,65 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     trace_mark(st, "l0_gather", 0, n0);
     dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp); dfree(d_segs);
 
-    // ---- levels
-    u32 n = n0, h = 0;
-    while (n) {
-        if (h >= 32) throw Error{PCB_ERR_RANGE, "octree deeper than 31 levels (reference overflows 2u32.pow, metadata.rs:92)"};
-        meta->hierarchies = std::max<uint32_t>(meta->hierarchies, h + 1);  // converter.rs:141-144
-        if (pairs_mode_for(n, ncell, make_geom(max_cell_size, dim, h)))
-            build_level<true>(h, pts, bat, cell_start, cell_idx, n, ncell, existing);
-        else
-            build_level<false>(h, pts, bat, cell_start, cell_idx, n, ncell, existing);
-        h++;
+    // ---- waves of level-0 cells.  Level-0 cells never interact (converter.rs:124-134: a cell only receives from
+    // its parent), so the forest is built a contiguous group of level-0 cells at a time: the node images of one
+    // wave travel to the host while the next wave is built, and the per-level arrays are sized for a wave, not
+    // for the run.
+    u32* const h_cs = (u32*)host_tmp(4ull * ((u64)ncell + 1));
+    publish(h_cs, cell_start, 4ull * ((u64)ncell + 1));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const u64 wave_target = wave_points(n0);
+    std::vector<u32> wave_end;   // exclusive cell ordinal per wave
+    u64 wave_max = 0;
+    {   // equal shares of the arrivals, cut at the nearest cell boundary
+        const u32 nw = (u32)std::min<u64>(ncell, std::max<u64>(1, ((u64)n0 + wave_target - 1) / wave_target));
+        u32 c = 0;
+        for (u32 w = 1; w <= nw && c < ncell; w++) {
+            const u64 goal = (u64)n0 * w / nw;
+            u32 e = c + 1;
+            while (e < ncell && h_cs[e] < goal && (h_cs[e + 1] <= goal || goal - h_cs[e] > h_cs[e + 1] - goal)) e++;
+            if (w == nw) e = ncell;
+            wave_end.push_back(e);
+            wave_max = std::max<u64>(wave_max, h_cs[e] - h_cs[c]);
+            c = e;
+        }
+        if (wave_end.empty() || wave_end.back() != ncell) {
+            wave_end.push_back(ncell);
+            wave_max = std::max<u64>(wave_max, (u64)h_cs[ncell] - h_cs[c]);
+        }
     }
+    arena_prepare(0, std::max<u64>(arenas->a[0].cap, 68ull * wave_max + (64ull << 20)));
+    arena_prepare(1, std::max<u64>(arenas->a[1].cap, 68ull * wave_max + (64ull << 20)));
+    u32 hmax = 0, c0 = 0;
+    for (u32 c1 : wave_end) {
+        u32 n = h_cs[c1] - h_cs[c0], wcell = c1 - c0, h = 0;
+        PcbPoint* wpts = pts + h_cs[c0];
+        u32* wbat = bat + h_cs[c0];
+        int* widx = cell_idx + 3ull * c0;
+        u32* wstart = cell_start;
+        if (wave_end.size() > 1) {
+            cur_arena = 1;                    // level 0 of the wave resets arena 0 and reads its inputs from arena 1
+            arenas->a[1].off = 0;
+            wstart = dalloc<u32>((u64)wcell + 1);
+            k_wave_starts<<<div_up(wcell + 1, 256), 256, 0, st>>>(cell_start + c0, h_cs[c0], wcell + 1, wstart);
+        }
+        inputs_borrowed = true;               // the wave's level-0 inputs are slices of the run's arrays
+        while (n) {
+            if (h >= 32) throw Error{PCB_ERR_RANGE, "octree deeper than 31 levels (reference overflows 2u32.pow, metadata.rs:92)"};
+            meta->hierarchies = std::max<uint32_t>(meta->hierarchies, h + 1);  // converter.rs:141-144
+            if (pairs_mode_for(n, wcell, make_geom(max_cell_size, dim, h)))
+                build_level<true>(h, wpts, wbat, wstart, widx, n, wcell, existing);
+            else
+                build_level<false>(h, wpts, wbat, wstart, widx, n, wcell, existing);
+            inputs_borrowed = false;
+            h++;
+        }
+        dfree(wpts); dfree(wbat); dfree(wstart); dfree(widx);   // (empty) inputs of the level that was not built
+        hmax = std::max(hmax, h);
+        c0 = c1;
+        trace_mark(st, "wave done", hmax, c1);
+    }
+    const u32 h = hmax;
     levels_built = h;
     trace_mark(st, "levels done");
     dfree(pts); dfree(bat); dfree(cell_start); dfree(cell_idx);
@@ -570,6 +668,8 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                               NodeSource* existing) {
     const LevelGeom g = make_geom(max_cell_size, dim, h);
     const u32 n_new = n;  // arrivals proper (incumbents of merge mode are added below)
+    bool own_pts = !inputs_borrowed;          // level 0 of a wave reads slices of the run's level-0 arrays
+    const bool own_cells = !inputs_borrowed;
     cur_arena = (int)(h & 1u);          // the other arena holds this level's inputs (written by the previous level)
     arenas->a[cur_arena].off = 0;
     arrivals += n_new;
@@ -579,9 +679,17 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     u32 *ex_m0 = nullptr, *ex_bucket = nullptr, *ex_rank = nullptr;
     PcbPoint* ex_pts = nullptr;
     u32 nex = 0;
-    std::vector<int> hidx(3ull * ncell);
+    // pinned node table of this level: cell indices, node offsets, node sizes (recycled when the level is done)
+    const u64 tab_idx = (12ull * ncell + 15) & ~15ull;
+    u64 tab_cap = 0;
+    unsigned char* const tab = (unsigned char*)g_pinned.get(tab_idx + 16ull * ncell + 32, &tab_cap);
+    struct TabGuard {
+        unsigned char* p; u64 cap;
+        ~TabGuard() { g_pinned.put(p, cap); }
+    } tab_guard{tab, tab_cap};
+    int* const hidx = (int*)tab;
     if (existing) {
-        CUDA_TRY(cudaMemcpyAsync(hidx.data(), cell_idx, hidx.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+        publish(hidx, cell_idx, 12ull * ncell);
         CUDA_TRY(cudaStreamSynchronize(st));
         std::vector<u32> inc_start(ncell + 1, 0);
         std::vector<pcb_point> inc_pts, exl_pts;
@@ -642,8 +750,10 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                 k_merge_starts<<<div_up(ncell + 1, 256), 256, 0, st>>>(cell_start, d_inc_start, ncell);
                 pe("merge_incumbents", 3, (u64)n + ninc, 40ull * ((u64)n + ninc));
                 CUDA_TRY(cudaStreamSynchronize(st));  // host vectors above must outlive the copies
-                dfree(pts); dfree(bat); dfree(d_inc_start); dfree(d_inc);
+                if (own_pts) { dfree(pts); dfree(bat); }
+                dfree(d_inc_start); dfree(d_inc);
                 pts = mp; bat = mb;
+                own_pts = true;
                 n += ninc;
             } else {
                 CUDA_TRY(cudaStreamSynchronize(st));
@@ -722,10 +832,11 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     nl = chain_scan<CellScanOp, 256, 4>(sop, ncell, scan_tmp, st);
     pe("bucket_decide", 1 + nl, ncell, 200ull * ncell);
     // node table for the host
-    std::vector<u64> hoff(ncell), hbytes(ncell);
-    if (!existing) CUDA_TRY(cudaMemcpyAsync(hidx.data(), cell_idx, hidx.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaMemcpyAsync(hoff.data(), node_off, 8ull * ncell, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(cudaMemcpyAsync(hbytes.data(), cell_bytes, 8ull * ncell, cudaMemcpyDeviceToHost, st));
+    u64* const hoff = (u64*)(tab + tab_idx);
+    u64* const hbytes = (u64*)(tab + tab_idx + ((8ull * ncell + 15) & ~15ull));
+    if (!existing) publish(hidx, cell_idx, 12ull * ncell);
+    publish(hoff, node_off, 8ull * ncell);
+    publish(hbytes, cell_bytes, 8ull * ncell);
     fetch_scratch();
     check_err();
     const LevelTotals tot = h_scr->totals;
@@ -788,7 +899,8 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     dfree(win_src); dfree(win_end); dfree(rank); dfree(bcnt); dfree(special); dfree(bdst);
     dfree(cell_deliver); dfree(cell_children); dfree(cell_dbase); dfree(cell_cbase); dfree(cell_bytes); dfree(node_off);
     dfree(ex_state); dfree(ex_m0); dfree(ex_pts); dfree(ex_bucket); dfree(ex_rank);
-    dfree(pts); dfree(bat); dfree(cell_start); dfree(cell_idx);
+    if (own_pts) { dfree(pts); dfree(bat); }
+    if (own_cells) { dfree(cell_start); dfree(cell_idx); }
     pts = next_pts; bat = next_bat; cell_start = next_cell_start; cell_idx = next_cell_idx;
     n = tot.n_next;
     ncell = tot.ncell_next;

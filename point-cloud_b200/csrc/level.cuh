@@ -966,6 +966,11 @@ __global__ void k_merge_incumbents(const PcbPoint* __restrict__ inc_pts, u32 nin
     out_pts[dst] = inc_pts[i];
     out_bat[dst] = 0;
 }
+// CSR of one wave of level-0 cells: the global starts rebased to the wave's first arrival
+__global__ void k_wave_starts(const u32* __restrict__ cell_start, u32 first, u32 count, u32* __restrict__ out) {
+    u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < count) out[c] = cell_start[c] - first;
+}
 __global__ void k_merge_starts(u32* __restrict__ cell_start, const u32* __restrict__ inc_start, u32 ncell) {
     u32 c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c <= ncell) cell_start[c] += inc_start[c];

@@ -154,3 +154,38 @@ def test_payload_sort_path_forced():
     env = dict(os.environ, PCB_FORCE_PAIRS="1")
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "pairs ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_waves_of_level0_cells_forced():
+    """The forest is built a group of level-0 cells ("wave") at a time.  Tiny waves (PCB_WAVE_POINTS, fresh
+    process) must give the same trees as the oracle: many roots incl. negative cells, the default config, and a
+    merge into an existing output whose cells are spread over several waves."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys, tempfile; sys.path.insert(0, %r)\n"
+        "import numpy as np\n"
+        "from pcutil import compare_trees, load_pcb, make_points, oracle_convert, read_tree\n"
+        "rng = np.random.default_rng(29)\n"
+        "pcb = load_pcb()\n"
+        "for cfg, bs, n, ext in (((100, 8, 10.0), 1000, 60000, 70), ((5000, 96, 1000.0), 10000, 300000, 5000)):\n"
+        "    pts = make_points(rng.random((n, 3)) * [ext, ext, ext / 10] - [ext / 2, ext / 2, ext / 20])\n"
+        "    o = oracle_convert([pts], config=cfg, batch_size=bs)\n"
+        "    nodes, mj, st, _ = pcb.convert([pts], config=cfg, batch_size=bs)\n"
+        "    assert st.arrivals == o.arrivals and st.hierarchies == o.hierarchies\n"
+        "    compare_trees(o.nodes, nodes, 'oracle', 'gpu-waves')\n"
+        "    assert mj == o.meta_json and all(o.nodes[k] == nodes[k] for k in nodes)\n"
+        "A = make_points(rng.random((30000, 3)) * 60 - 30)\n"
+        "B = make_points(rng.random((20000, 3)) * 80 - 40)\n"
+        "with tempfile.TemporaryDirectory() as d_o, tempfile.TemporaryDirectory() as d_g:\n"
+        "    oracle_convert([A], out_dir=d_o, config=(100, 8, 16.0), batch_size=1000)\n"
+        "    oracle_convert([B], out_dir=d_o, batch_size=1000)\n"
+        "    pcb.convert([A], config=(100, 8, 16.0), batch_size=1000, out_dir=d_g)\n"
+        "    pcb.convert([B], batch_size=1000, out_dir=d_g)\n"
+        "    compare_trees(read_tree(d_o), read_tree(d_g), 'oracle-merge', 'gpu-merge-waves')\n"
+        "    assert open(d_o + '/metadata.json').read() == open(d_g + '/metadata.json').read()\n"
+        "print('waves ok')\n") % os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, PCB_WAVE_POINTS="7000")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "waves ok" in r.stdout, r.stdout + r.stderr
