@@ -213,6 +213,7 @@ def main():
         shard = importlib.util.module_from_spec(spec)
         spec.loader.exec_module(shard)
     route_launches = [0]
+    exchange = [""]
 
     def ingest(cv, src):
         """single GPU: the resident stream as is; N GPUs: level-0 exchange (libpcb routing kernels + NCCL
@@ -223,6 +224,7 @@ def main():
             return None
         rp, rb, info = shard.route_device(pcb, src, rank * n, 10_000, 1000.0, stream=stream)
         route_launches[0] += info["launches"]
+        exchange[0] = info.get("exchange", "")
         cv.add_points_device_batched(rp.data_ptr(), rb.data_ptr(), rp.shape[0])
         return rp, rb   # keep alive until finish
 
@@ -373,8 +375,7 @@ def main():
                           "l2": "inputs (1.6 GB/step) larger than L2, no explicit flush",
                           "levels": int(last.levels_built), "arrivals_per_point": round(last.arrivals / n, 3),
                           "nodes": int(last.nodes_written), "sharding": ("none (1 GPU)" if world == 1 else
-                                       "level-0 cell owners; exchange = libpcb routing kernels + NCCL all-to-all-v, "
-                                       "inside the timed step"), "step_ms": step_ms,
+                                       "level-0 cell owners; exchange inside the timed step = " + exchange[0]), "step_ms": step_ms,
                           **({"ranks": ranks_info} if ranks_info else {})},
                "e2e": e2e, "gpu_launches": int(launches) + route_timed, "roofline": roofline, "cpu_baseline": cpu,
                "clocks": clocks}

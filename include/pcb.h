@@ -148,7 +148,12 @@ int pcb_kernel_stat_get(const pcb_handle* h, int i, pcb_kernel_stat* out);
    2. pcb_route_histogram: points per level-0 cell (metadata.rs:100-102 at level 0) inside the dense index box
       [origin, origin + dims), x fastest; the caller all-reduces the table and plans owners.
    3. pcb_route_pack: stable partition of the slice by owner[cell] into the all-to-all send buffer, with the
-      global batch ordinal (first_index + i) / batch_size of every point; send_counts[world] on the host. */
+      global batch ordinal (first_index + i) / batch_size of every point; send_counts[world] on the host.
+   4. pcb_route_scatter (world <= 8): partition and exchange in ONE kernel - every point and its batch ordinal are
+      stored straight into the receive buffers of the owner rank: recv_pts_ptrs[o] / recv_batch_ptrs[o] are device
+      addresses valid on `device` (peer-mapped memory of rank o reached over NVLink, local memory for the own rank),
+      recv_offsets[o] = number of points the lower ranks send to o.  Replaces step 3 + the all-to-all; the caller
+      synchronises the ranks before (buffers free) and after (stores landed). */
 int pcb_route_bbox(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size, float out_min[3],
                    float out_max[3]);
 int pcb_route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size,
@@ -157,6 +162,10 @@ int pcb_route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n,
                    uint32_t batch_size, float max_cell_size, const int32_t origin[3], const uint32_t dims[3],
                    const uint8_t* d_owner, uint32_t world, pcb_point* d_send_pts, uint32_t* d_send_batch,
                    uint64_t* send_counts);
+int pcb_route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index,
+                      uint32_t batch_size, float max_cell_size, const int32_t origin[3], const uint32_t dims[3],
+                      const uint8_t* d_owner, uint32_t world, const uint64_t* recv_pts_ptrs,
+                      const uint64_t* recv_batch_ptrs, const uint64_t* recv_offsets);
 
 const char* pcb_version(void);
 int pcb_device_count(void);

@@ -29,6 +29,9 @@ int route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n
 int route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
                float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner, uint32_t world,
                pcb_point* d_send_pts, uint32_t* d_send_batch, uint64_t* send_counts);
+int route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
+                  float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner, uint32_t world,
+                  const uint64_t* recv_pts_ptrs, const uint64_t* recv_batch_ptrs, const uint64_t* recv_offsets);
 }
 
 struct pcb_handle {
@@ -229,6 +232,15 @@ int pcb_route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n,
     if (!origin || !dims || !d_owner || !send_counts || (n && (!d_pts || !d_send_pts || !d_send_batch))) return PCB_ERR_ARG;
     PCB_ROUTE_GUARD(pcb::route_pack(device, stream, d_pts, n, first_index, batch_size, max_cell_size, origin, dims,
                                     d_owner, world, d_send_pts, d_send_batch, send_counts))
+}
+
+int pcb_route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index,
+                      uint32_t batch_size, float max_cell_size, const int32_t origin[3], const uint32_t dims[3],
+                      const uint8_t* d_owner, uint32_t world, const uint64_t* recv_pts_ptrs,
+                      const uint64_t* recv_batch_ptrs, const uint64_t* recv_offsets) {
+    if (!origin || !dims || !d_owner || !recv_pts_ptrs || !recv_batch_ptrs || !recv_offsets || (n && !d_pts)) return PCB_ERR_ARG;
+    PCB_ROUTE_GUARD(pcb::route_scatter(device, stream, d_pts, n, first_index, batch_size, max_cell_size, origin, dims,
+                                       d_owner, world, recv_pts_ptrs, recv_batch_ptrs, recv_offsets))
 }
 
 int pcb_get_config(const pcb_handle* h, uint32_t* limit, uint32_t* dim, float* max_cell_size) {

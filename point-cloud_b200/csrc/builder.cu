@@ -1071,6 +1071,31 @@ int route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uin
         if (!n) return 0;
         if (n >= (1ull << 30) || world == 0 || world > 256 || batch_size == 0) throw Error{PCB_ERR_ARG, "bad routing arguments"};
         const u32 n32 = (u32)n;
+        static const bool no_split = getenv("PCB_ROUTE_SORT") != nullptr;   // test hook: force the general path
+        if (world <= 8 && !no_split) {
+            // one node: single-pass stable split (local histogram -> per-owner send offsets -> chained 8-way split)
+            const L0Box box = make_box(origin, dims);
+            const u64 vol = (u64)dims[0] * dims[1] * dims[2];
+            const u32 ntiles = div_up(n, ROUTE_SPLIT_TILE);
+            u32* tmp = nullptr;   // [vol] local histogram | [8] counts | [8] bases | descriptors
+            const u64 words = vol + 16 + 4 + (chain_temp_bytes(ntiles) + 3) / 4 + 4;
+            CUDA_TRY(cudaMallocAsync((void**)&tmp, 4 * words, st));
+            CUDA_TRY(cudaMemsetAsync(tmp, 0, 4 * words, st));
+            u32 *lhist = tmp, *counts = tmp + vol, *bases = counts + 8;
+            uint4* desc = (uint4*)(tmp + ((vol + 16 + 3) & ~3ull));
+            k_route_hist<<<148 * 8, 256, 0, st>>>((const PcbPoint*)d_pts, n32, S0, box, (u32)vol, lhist);
+            k_route_owner_counts<<<1, 256, 0, st>>>(lhist, (u32)vol, d_owner, counts, bases);
+            RouteDst dst8;
+            for (int o = 0; o < 8; o++) { dst8.pts[o] = (PcbPoint*)d_send_pts; dst8.bat[o] = d_send_batch; dst8.off[o] = 0; }
+            k_route_split<<<ntiles, ROUTE_SPLIT_THREADS, 0, st>>>((const PcbPoint*)d_pts, n32, S0, box, d_owner, bases, first_index,
+                                                                 batch_size, dst8, world, desc);
+            u32 hc[8];
+            CUDA_TRY(cudaMemcpyAsync(hc, counts, sizeof hc, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            for (u32 r = 0; r < world; r++) send_counts[r] = hc[r];
+            CUDA_TRY(cudaFreeAsync(tmp, st));
+            return 3;
+        }
         const int pb = std::max(1, bits_count(n));
         const RadixPlan plan = radix_plan(pb, std::max(1, bits_count(world)));
         u64 *kA = nullptr, *kB = nullptr;
@@ -1096,6 +1121,38 @@ int route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uin
         CUDA_TRY(cudaFreeAsync(kB, st));
         CUDA_TRY(cudaFreeAsync(ghist, st));
         return 2 + plan.npass;
+    });
+}
+
+// Partition + exchange in one kernel: every point is stored straight into the receive buffer of the rank that owns
+// its level-0 cell.  recv_*_ptrs[o] are device pointers valid on THIS device (peer-mapped memory of rank o, or local
+// memory for o == own rank); recv_offsets[o] = points that lower ranks send to o.  The caller synchronises the ranks
+// before (buffers free) and after (stores landed).
+int route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
+                  float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner, uint32_t world,
+                  const uint64_t* recv_pts_ptrs, const uint64_t* recv_batch_ptrs, const uint64_t* recv_offsets) {
+    return guarded([&] {
+        CUDA_TRY(cudaSetDevice(device));
+        cudaStream_t st = (cudaStream_t)stream;
+        if (!n) return 0;
+        if (n >= (1ull << 30) || world == 0 || world > 8 || batch_size == 0) throw Error{PCB_ERR_ARG, "bad routing arguments"};
+        RouteDst dst8;
+        for (u32 o = 0; o < 8; o++) {
+            const u32 q = o < world ? o : 0;
+            if (recv_offsets[q] >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "receive offset too large"};
+            dst8.pts[o] = (PcbPoint*)(uintptr_t)recv_pts_ptrs[q];
+            dst8.bat[o] = (u32*)(uintptr_t)recv_batch_ptrs[q];
+            dst8.off[o] = (u32)recv_offsets[q];
+        }
+        const u32 ntiles = div_up(n, ROUTE_SPLIT_TILE);
+        uint4* desc = nullptr;
+        CUDA_TRY(cudaMallocAsync((void**)&desc, chain_temp_bytes(ntiles), st));
+        CUDA_TRY(cudaMemsetAsync(desc, 0, chain_temp_bytes(ntiles), st));
+        k_route_split<<<ntiles, ROUTE_SPLIT_THREADS, 0, st>>>((const PcbPoint*)d_pts, (u32)n, S0, make_box(origin, dims), d_owner,
+                                                             nullptr, first_index, batch_size, dst8, world, desc);
+        CUDA_TRY(cudaGetLastError());
+        CUDA_TRY(cudaFreeAsync(desc, st));
+        return 1;
     });
 }
 

@@ -59,3 +59,158 @@ __global__ void k_route_gather(const PcbPoint* __restrict__ pts, const u64* __re
     *(uint4*)(send_pts + j) = __ldg((const uint4*)(pts + i));
     send_bat[j] = (u32)((first_index + i) / batch_size);
 }
+
+// ---- stable split by owner, up to 8 owners (one node) --------------------------------------------------------
+// One pass instead of key + radix pass + gather: a point is read once (16 B) and written once (16 + 4 B) at
+// send_base[owner] + (number of earlier points of this slice with the same owner).  The running per-owner counts
+// are a chained scan over tiles (decoupled look-back, scan.cuh); inside a tile the eight counters are packed
+// 4 x 16 bit like the octant scan's.
+#define ROUTE_SPLIT_THREADS 256
+#define ROUTE_SPLIT_ITEMS 8
+#define ROUTE_SPLIT_TILE (ROUTE_SPLIT_THREADS * ROUTE_SPLIT_ITEMS)
+struct RouteCountOp {
+    typedef Oct8 State;
+    __device__ static void pack(const State& s, u32 status, uint4& a, uint4& b) {   // counters < 2^30
+        a = make_uint4(s.c[0], s.c[1], s.c[2], s.c[3] | status);
+        b = make_uint4(s.c[4], s.c[5], s.c[6], s.c[7] | status);
+    }
+    __device__ static State unpack(const uint4& a, const uint4& b) {
+        State s;
+        s.c[0] = a.x; s.c[1] = a.y; s.c[2] = a.z; s.c[3] = a.w & ~PCB_DESC_MASK;
+        s.c[4] = b.x; s.c[5] = b.y; s.c[6] = b.z; s.c[7] = b.w & ~PCB_DESC_MASK;
+        s.head = 0;
+        return s;
+    }
+    __device__ State identity() const {
+        State s;
+#pragma unroll
+        for (int k = 0; k < 8; k++) s.c[k] = 0;
+        s.head = 0;
+        return s;
+    }
+    __device__ State combine(const State& a, const State& b) const {
+        State s;
+#pragma unroll
+        for (int k = 0; k < 8; k++) s.c[k] = a.c[k] + b.c[k];
+        s.head = 0;
+        return s;
+    }
+};
+
+// per-owner totals of the slice from its dense level-0 histogram, and their exclusive prefix (send offsets)
+__global__ void k_route_owner_counts(const u32* __restrict__ lhist, u32 vol, const unsigned char* __restrict__ owner,
+                                     u32* __restrict__ counts /* [8] */, u32* __restrict__ bases /* [8] */) {
+    __shared__ u32 sc[8];
+    if (threadIdx.x < 8) sc[threadIdx.x] = 0;
+    __syncthreads();
+    u32 loc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (u32 i = threadIdx.x; i < vol; i += blockDim.x) {
+        const u32 h = lhist[i];
+        if (h) {
+            const u32 o = owner[i] & 7u;
+#pragma unroll
+            for (int k = 0; k < 8; k++) loc[k] += (o == (u32)k) ? h : 0u;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+        if (loc[k]) atomicAdd(&sc[k], loc[k]);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        u32 run = 0;
+        for (int k = 0; k < 8; k++) { counts[k] = sc[k]; bases[k] = run; run += sc[k]; }
+    }
+}
+
+// Where owner o's points go: slot off[o] (+ dev_bases[o] when given) of (pts[o], bat[o]).  All eight equal = a local
+// send buffer; peer-mapped receive buffers of the other ranks = the exchange itself (stores travel over NVLink).
+struct RouteDst {
+    PcbPoint* pts[8];
+    u32* bat[8];
+    u32 off[8];
+};
+__global__ void __launch_bounds__(ROUTE_SPLIT_THREADS)
+k_route_split(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, const unsigned char* __restrict__ owner,
+              const u32* __restrict__ dev_bases, u64 first_index, u32 batch_size, RouteDst dst8, u32 world,
+              uint4* __restrict__ desc) {
+    constexpr int WARPS = ROUTE_SPLIT_THREADS / 32;
+    __shared__ u32 s_warp[WARPS][8];
+    __shared__ Oct8 s_prefix;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u32 tile = blockIdx.x;   // tile = block index, see k_chain_scan
+    // warp-striped: item k of lane l is element wbase + 32 k + l, so one load / store instruction of a warp covers
+    // 32 consecutive points and the points of one owner leave as contiguous runs (full sectors, also over NVLink)
+    const u64 wbase = (u64)tile * ROUTE_SPLIT_TILE + (u64)warp * (32 * ROUTE_SPLIT_ITEMS);
+    const u32 lt = (1u << lane) - 1u;
+    uint4 p[ROUTE_SPLIT_ITEMS];
+    u32 code[ROUTE_SPLIT_ITEMS];   // owner | rank inside the warp << 4
+    u32 wc[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // per-owner counts of this warp so far (same in every lane)
+#pragma unroll
+    for (int k = 0; k < ROUTE_SPLIT_ITEMS; k++) {
+        const u64 e = wbase + 32 * k + lane;
+        u32 o = 8u;
+        if (e < n) {
+            p[k] = __ldg((const uint4*)(pts + e));
+            PcbPoint q;
+            q.x = __uint_as_float(p[k].x); q.y = __uint_as_float(p[k].y); q.z = __uint_as_float(p[k].z); q.rgba = p[k].w;
+            o = __ldg(owner + l0_cell_id(q, S0, box)) & 7u;
+        }
+        const u32 peers = __match_any_sync(0xFFFFFFFFu, o);   // at most 9 distinct values
+        u32 before = 0;
+#pragma unroll
+        for (int q = 0; q < 8; q++) before = (o == (u32)q) ? wc[q] : before;
+        code[k] = o | ((before + (u32)__popc(peers & lt)) << 4);
+#pragma unroll
+        for (int q = 0; q < 8; q++)
+            if (q < (int)world) wc[q] += (u32)__popc(__ballot_sync(0xFFFFFFFFu, o == (u32)q));
+    }
+    if (lane < 8) {
+        u32 v = 0;
+#pragma unroll
+        for (int q = 0; q < 8; q++) v = (lane == q) ? wc[q] : v;
+        s_warp[warp][lane] = v;
+    }
+    __syncthreads();
+    RouteCountOp op;
+    if (warp == 0) {
+        Oct8 tot;
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            u32 t = 0;
+#pragma unroll
+            for (int w = 0; w < WARPS; w++) t += s_warp[w][q];
+            tot.c[q] = t;
+        }
+        tot.head = 0;
+        Oct8 prefix = chain_lookback(op, desc, tile, tot);
+        if (lane == 0) s_prefix = prefix;
+    }
+    __syncthreads();
+    u32 start[8];   // first slot of this warp's points per owner
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        u32 t = dst8.off[q] + (dev_bases ? __ldg(dev_bases + q) : 0u) + s_prefix.c[q];
+#pragma unroll
+        for (int w = 0; w < WARPS; w++) t += (w < warp) ? s_warp[w][q] : 0u;
+        start[q] = t;
+    }
+#pragma unroll
+    for (int k = 0; k < ROUTE_SPLIT_ITEMS; k++) {
+        const u32 o = code[k] & 0xFu;
+        u32 dst = 0;
+        PcbPoint* dp = nullptr;
+        u32* db = nullptr;
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const bool hit = (o == (u32)q);
+            dst = hit ? start[q] : dst;
+            dp = hit ? dst8.pts[q] : dp;
+            db = hit ? dst8.bat[q] : db;
+        }
+        if (o < 8u) {
+            dst += code[k] >> 4;
+            *(uint4*)(dp + dst) = p[k];
+            db[dst] = (u32)((first_index + wbase + 32 * k + lane) / batch_size);
+        }
+    }
+}

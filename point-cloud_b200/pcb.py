@@ -27,7 +27,7 @@ FLAG_NO_METADATA_FILE = 8
 EXPORTS = [
     "pcb_open", "pcb_set_stream", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
     "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
-    "pcb_route_bbox", "pcb_route_histogram", "pcb_route_pack",
+    "pcb_route_bbox", "pcb_route_histogram", "pcb_route_pack", "pcb_route_scatter",
     "pcb_add_points_device_batched", "pcb_write_metadata", "pcb_get_config", "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
 
@@ -88,6 +88,9 @@ def load_library():
                                       C.POINTER(C.c_uint32), vp]
     L.pcb_route_pack.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_uint64, C.c_uint32, C.c_float, C.POINTER(C.c_int32),
                                  C.POINTER(C.c_uint32), vp, C.c_uint32, vp, vp, C.POINTER(C.c_uint64)]
+    L.pcb_route_scatter.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_uint64, C.c_uint32, C.c_float, C.POINTER(C.c_int32),
+                                    C.POINTER(C.c_uint32), vp, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                    C.POINTER(C.c_uint64)]
     L.pcb_reserve.argtypes = [vp, C.c_uint64]
     L.pcb_set_stream.argtypes = [vp, vp]
     L.pcb_finish.argtypes = [vp, C.POINTER(PcbStats)]
@@ -249,6 +252,18 @@ def route_pack(device, stream, pts_ptr, n, first_index, batch_size, max_cell_siz
                                                     batch_size, max_cell_size, o, d, C.c_void_p(owner_ptr), world,
                                                     C.c_void_p(send_pts_ptr), C.c_void_p(send_bat_ptr), counts))
     return list(counts), nl
+
+
+def route_scatter(device, stream, pts_ptr, n, first_index, batch_size, max_cell_size, origin, dims, owner_ptr, world,
+                  recv_pts_ptrs, recv_bat_ptrs, recv_offsets):
+    """pcb_route_scatter: partition + exchange in one kernel over peer-mapped receive buffers (world <= 8)."""
+    o, d = (C.c_int32 * 3)(*origin), (C.c_uint32 * 3)(*dims)
+    pp = (C.c_uint64 * world)(*[int(v) for v in recv_pts_ptrs])
+    pb = (C.c_uint64 * world)(*[int(v) for v in recv_bat_ptrs])
+    po = (C.c_uint64 * world)(*[int(v) for v in recv_offsets])
+    return _route_check(load_library().pcb_route_scatter(device, C.c_void_p(stream), C.c_void_p(pts_ptr), n, first_index,
+                                                         batch_size, max_cell_size, o, d, C.c_void_p(owner_ptr), world,
+                                                         pp, pb, po))
 
 
 def write_metadata(out_dir, number_of_points, hierarchies, bbox_min, bbox_max, config):

@@ -21,6 +21,8 @@ caller initialised (NCCL over NVLink on the GPU box, gloo in the CPU tests of th
 """
 from __future__ import annotations
 
+import os
+
 from typing import List, Optional, Tuple
 
 import torch
@@ -166,8 +168,61 @@ def route_emulated(slices: List[torch.Tensor], batch_size: int, max_cell_size: f
 
 
 # ---- device path: the partition runs in the library's own kernels (route.cuh) --------------------------------
+class _P2PUnavailable(RuntimeError):
+    pass
+
+
+# Fused partition + exchange (pcb_route_scatter): receive buffers live in torch symmetric memory (one allocation per
+# rank, peer-mapped into every process of the node), grown on demand and kept for the life of the process.
+_P2P = {"enabled": os.environ.get("PCB_ROUTE_P2P", "1") != "0", "why": None, "buf": None, "hdl": None, "cap": 0}
+
+
+def _p2p_buffers(dev, group, cap):
+    """Symmetric receive buffer for `cap` points: [cap x 16 B points][cap x 4 B batch ordinals].  Collective."""
+    if _P2P["buf"] is not None and _P2P["cap"] >= cap:
+        return _P2P["buf"], _P2P["hdl"], _P2P["cap"]
+    try:
+        import torch.distributed._symmetric_memory as symm
+        cap = (int(cap * 1.1) + 4095) // 4096 * 4096
+        buf = symm.empty(cap * 20, dtype=torch.uint8, device=dev)
+        hdl = symm.rendezvous(buf, group if group is not None else dist.group.WORLD)
+        ptrs = list(hdl.buffer_ptrs)
+    except Exception as e:   # noqa: BLE001 - anything here means "no peer-mapped memory on this system"
+        raise _P2PUnavailable(f"{type(e).__name__}: {e}") from e
+    _P2P.update(buf=buf, hdl=hdl, cap=cap, ptrs=ptrs)
+    return buf, hdl, cap
+
+
+def _route_scatter_p2p(pcb, pts_u8, first_index, batch_size, max_cell_size, origin, dims, owner_dev, local_hist, group,
+                       st, mark):
+    dev = pts_u8.device
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    n = pts_u8.shape[0]
+    # who sends how much to whom: local per-owner counts from the local histogram, all-gathered (world x world)
+    cnt = torch.zeros(world, dtype=torch.int64, device=dev)
+    cnt.index_add_(0, owner_dev.to(torch.int64), local_hist.to(torch.int64))
+    allc = torch.empty(world * world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(allc, cnt, group=group)
+    cmat = allc.view(world, world).cpu()           # cmat[r][o] = points rank r sends to owner o
+    recv_tot = cmat.sum(0)
+    m = int(recv_tot[rank])
+    offs = cmat[:rank].sum(0).tolist() if rank > 0 else [0] * world
+    buf, hdl, cap = _p2p_buffers(dev, group, int(recv_tot.max()))
+    ptrs = _P2P["ptrs"]
+    mark("counts all-gather")
+    with torch.cuda.stream(st):
+        hdl.barrier(channel=0)                     # every rank is done with the previous contents
+        nl = pcb.route_scatter(dev.index, st.cuda_stream, pts_u8.data_ptr(), n, first_index, batch_size, max_cell_size,
+                               origin, dims, owner_dev.data_ptr(), world, ptrs, [p + cap * 16 for p in ptrs], offs)
+        hdl.barrier(channel=0)                     # every rank's stores have landed
+    recv_pts = buf[:m * 16].view(m, 16)
+    recv_bat = buf[cap * 16:cap * 16 + m * 4].view(torch.int32)
+    mark("scatter (partition + exchange)")
+    return recv_pts, recv_bat, nl, 20 * (n - int(cmat[rank][rank]))
+
+
 def route_device(pcb, pts_u8: torch.Tensor, first_index: int, batch_size: int, max_cell_size: float, group=None,
-                 stream=None):
+                 stream=None, trace=False):
     """Steps 1-4 on the GPU with libpcb's kernels: bounding box -> dense level-0 histogram -> all-reduce ->
     owner plan -> ONE onesweep pass (owner digit) that writes the all-to-all send buffer -> all-to-all-v.
     Returns (points, batch ordinals (int32), info dict with launch count)."""
@@ -178,12 +233,22 @@ def route_device(pcb, pts_u8: torch.Tensor, first_index: int, batch_size: int, m
     st = stream if stream is not None else torch.cuda.current_stream(dev)
     sp = st.cuda_stream
     launches = 0
+    import time as _time
+    _t = [_time.perf_counter()]
+
+    def _mark(name):   # debugging aid: per-phase wall time (synchronises!)
+        if trace:
+            torch.cuda.synchronize(dev)
+            now = _time.perf_counter()
+            print(f"[route] {name}: {1e3 * (now - _t[0]):.2f} ms", flush=True)
+            _t[0] = now
     lo, hi, nl = pcb.route_bbox(dev.index, sp, pts_u8.data_ptr(), n, max_cell_size)
     launches += nl
     box = torch.tensor(lo + [-v for v in hi], dtype=torch.float32, device=dev)   # min of (lo, -hi)
     if world > 1:
         dist.all_reduce(box, op=dist.ReduceOp.MIN, group=group)
     b = box.cpu().tolist()
+    _mark("bbox + all-reduce")
     glo, ghi = b[:3], [-v for v in b[3:]]
     if not all(math.isfinite(v) for v in glo + ghi):       # no points anywhere
         return pts_u8[:0], torch.zeros(0, dtype=torch.int32, device=dev), {"launches": launches, "cells": 0}
@@ -194,19 +259,34 @@ def route_device(pcb, pts_u8: torch.Tensor, first_index: int, batch_size: int, m
     vol = dims[0] * dims[1] * dims[2]
     hist = torch.empty(vol, dtype=torch.int32, device=dev)
     launches += pcb.route_histogram(dev.index, sp, pts_u8.data_ptr(), n, max_cell_size, origin, dims, hist.data_ptr())
+    local_hist = hist.clone() if world > 1 else hist
     if world > 1:
         dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
     h = hist.cpu()
+    _mark("histogram + all-reduce")
     cells = torch.nonzero(h).flatten()
     owners = plan_owners(cells, h[cells].to(torch.int64), world)
     owner_tab = torch.zeros(vol, dtype=torch.uint8)
     owner_tab[cells] = owners.to(torch.uint8)
     owner_dev = owner_tab.to(dev)
+    _mark("owner plan")
+    if world > 1 and world <= 8 and _P2P["enabled"]:
+        try:
+            out = _route_scatter_p2p(pcb, pts_u8, first_index, batch_size, max_cell_size, origin, dims, owner_dev,
+                                     local_hist, group, st, _mark)
+            launches += out[2]
+            return out[0], out[1], {"launches": launches, "cells": int(cells.numel()), "box": (origin, dims),
+                                    "exchange": "p2p stores (pcb_route_scatter over symmetric memory)",
+                                    "sent_bytes": out[3]}
+        except _P2PUnavailable as e:   # no peer access / symmetric memory on this system: NCCL all-to-all below
+            _P2P["enabled"] = False
+            _P2P["why"] = str(e)
     send_pts = torch.empty((n, 16), dtype=torch.uint8, device=dev)
     send_bat = torch.empty((n,), dtype=torch.int32, device=dev)
     ins, nl = pcb.route_pack(dev.index, sp, pts_u8.data_ptr(), n, first_index, batch_size, max_cell_size, origin, dims,
                              owner_dev.data_ptr(), world, send_pts.data_ptr(), send_bat.data_ptr())
     launches += nl
+    _mark("pack")
     info = {"launches": launches, "cells": int(cells.numel()), "box": (origin, dims)}
     if world == 1:
         return send_pts, send_bat, info
@@ -220,4 +300,6 @@ def route_device(pcb, pts_u8: torch.Tensor, first_index: int, batch_size: int, m
     dist.all_to_all_single(recv_pts, send_pts, outs, ins, group=group)
     dist.all_to_all_single(recv_bat, send_bat, outs, ins, group=group)
     info["sent_bytes"] = 20 * (n - ins[dist.get_rank(group)])
+    info["exchange"] = "NCCL all-to-all-v" + (f" (p2p unavailable: {_P2P['why']})" if _P2P.get("why") else "")
+    _mark("all-to-all")
     return recv_pts, recv_bat, info
