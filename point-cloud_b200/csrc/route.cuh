@@ -135,7 +135,9 @@ k_route_split(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, cons
               uint4* __restrict__ desc) {
     constexpr int WARPS = ROUTE_SPLIT_THREADS / 32;
     __shared__ u32 s_warp[WARPS][8];
-    __shared__ Oct8 s_prefix;
+    __shared__ u32 s_tbase[9], s_gstart[8];
+    __shared__ uint4 s_pts[ROUTE_SPLIT_TILE];
+    __shared__ u32 s_bat[ROUTE_SPLIT_TILE];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const u32 tile = blockIdx.x;   // tile = block index, see k_chain_scan
     // warp-striped: item k of lane l is element wbase + 32 k + l, so one load / store instruction of a warp covers
@@ -183,13 +185,25 @@ k_route_split(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, cons
         }
         tot.head = 0;
         Oct8 prefix = chain_lookback(op, desc, tile, tot);
-        if (lane == 0) s_prefix = prefix;
+        if (lane == 0) {
+            u32 run = 0;
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                s_tbase[q] = run;   // first staged slot of owner q in this tile
+                s_gstart[q] = dst8.off[q] + (dev_bases ? __ldg(dev_bases + q) : 0u) + prefix.c[q];
+                run += tot.c[q];
+            }
+            s_tbase[8] = run;
+        }
     }
     __syncthreads();
-    u32 start[8];   // first slot of this warp's points per owner
+    // stage the tile in owner order in shared memory, then write it out: one owner's points of a tile leave as ONE
+    // contiguous run (~TILE / world points), which is what the NVLink stores need at 8 owners (direct stores from
+    // the warp-striped registers were runs of 4 points there)
+    u32 start[8];
 #pragma unroll
     for (int q = 0; q < 8; q++) {
-        u32 t = dst8.off[q] + (dev_bases ? __ldg(dev_bases + q) : 0u) + s_prefix.c[q];
+        u32 t = s_tbase[q];
 #pragma unroll
         for (int w = 0; w < WARPS; w++) t += (w < warp) ? s_warp[w][q] : 0u;
         start[q] = t;
@@ -197,20 +211,32 @@ k_route_split(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, cons
 #pragma unroll
     for (int k = 0; k < ROUTE_SPLIT_ITEMS; k++) {
         const u32 o = code[k] & 0xFu;
-        u32 dst = 0;
+        if (o < 8u) {
+            u32 slot = 0;
+#pragma unroll
+            for (int q = 0; q < 8; q++) slot = (o == (u32)q) ? start[q] : slot;
+            slot += code[k] >> 4;
+            s_pts[slot] = p[k];
+            s_bat[slot] = (u32)((first_index + wbase + 32 * k + lane) / batch_size);
+        }
+    }
+    __syncthreads();
+    const u32 tile_n = s_tbase[8];
+    for (u32 j = tid; j < tile_n; j += ROUTE_SPLIT_THREADS) {
+        u32 o = 0;
+#pragma unroll
+        for (int q = 1; q < 8; q++) o += (s_tbase[q] <= j) ? 1u : 0u;   // bases are non-decreasing
+        // an owner without points in this tile shares its base with the next one: the count above then lands on
+        // the LAST owner whose base is <= j, which is the one that has points
+        const u32 g = s_gstart[o] + (j - s_tbase[o]);
         PcbPoint* dp = nullptr;
         u32* db = nullptr;
 #pragma unroll
         for (int q = 0; q < 8; q++) {
-            const bool hit = (o == (u32)q);
-            dst = hit ? start[q] : dst;
-            dp = hit ? dst8.pts[q] : dp;
-            db = hit ? dst8.bat[q] : db;
+            dp = (o == (u32)q) ? dst8.pts[q] : dp;
+            db = (o == (u32)q) ? dst8.bat[q] : db;
         }
-        if (o < 8u) {
-            dst += code[k] >> 4;
-            *(uint4*)(dp + dst) = p[k];
-            db[dst] = (u32)((first_index + wbase + 32 * k + lane) / batch_size);
-        }
+        *(uint4*)(dp + g) = s_pts[j];
+        db[g] = s_bat[j];
     }
 }
