@@ -574,42 +574,66 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     int pb0 = std::max(1, bits_count(n0));
     const bool pairs0 = g_force_pairs || cb0 + pb0 > 64;
     if (pairs0) pb0 = 0;
-    const RadixPlan plan0 = radix_plan(pb0, cb0);
-    u64 *kA = dalloc<u64>(n0), *kB = dalloc<u64>(n0);
-    u32 *vA = pairs0 ? dalloc<u32>(n0) : nullptr, *vB = pairs0 ? dalloc<u32>(n0) : nullptr;
-    RadixTemp rt;
-    const u64 rwords = RadixTemp::ghist_words() + RadixTemp::status_words(n0, plan0);
-    rt.ghist = dalloc<u32>(rwords);
-    rt.status = rt.ghist + RadixTemp::ghist_words();
-    CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
-    pb();
-    k_l0_key<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, pb0, plan0, kA, vA, rt.ghist);
-    pe("l0_key", 1, n0, 24ull * n0);
-    int cur = pairs0 ? radix_sort<true>(kA, vA, kB, vB, n0, plan0, rt, st, *this)
-                     : radix_sort<false>(kA, vA, kB, vB, n0, plan0, rt, st, *this);
-    u64* ks = cur ? kB : kA;
-    u32* vs = cur ? vB : vA;
-    trace_mark(st, "l0_sort", 0, n0);
     u32 ncell_ub = (u32)std::min<u64>(n0, vol);
     arena_prepare(3, 20ull * n0 + 16ull * ncell_ub + (1ull << 20));
     u32* cell_start = dalloc_from<u32>(3, (u64)ncell_ub + 1);
     int* cell_idx = dalloc_from<int>(3, 3ull * ncell_ub);
-    void* scan_tmp = dalloc<unsigned char>(chain_scan_temp_bytes<256, 8>(n0));
-    L0HeadOp hop{ks, n0, pb0, box, cell_start, cell_idx, &d_scr->ncell};
-    pb();
-    int nl = chain_scan<L0HeadOp, 256, 8>(hop, n0, scan_tmp, st);
-    pe("l0_heads", nl, n0, 8ull * n0);
-    BatchSeg* d_segs = dalloc<BatchSeg>(segs.size());
-    CUDA_TRY(cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(BatchSeg), cudaMemcpyHostToDevice, st));
     PcbPoint* pts = dalloc_from<PcbPoint>(3, n0);
     u32* bat = dalloc_from<u32>(3, n0);
-    pb();
-    k_l0_gather<<<div_up(n0, 256), 256, 0, st>>>(d_in, ks, vs, n0, pb0, d_segs, (u32)segs.size(), d_bat_in, pts, bat);
-    pe("l0_gather", 1, n0, 44ull * n0);
+    BatchSeg* d_segs = dalloc<BatchSeg>(segs.size());
+    CUDA_TRY(cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(BatchSeg), cudaMemcpyHostToDevice, st));
+    static const bool l0_sort_forced = getenv("PCB_L0_SORT") != nullptr;   // test hook: the general (sort) path
+    if (vol <= L0S_MAX_BINS && !pairs0 && !l0_sort_forced) {
+        // ---- few level-0 cells: dense histogram -> first slot per cell -> one stable split pass
+        const u32 nb = (u32)vol, ntiles = div_up(n0, L0S_TILE);
+        const int dbits = std::max(1, bits_count(vol));
+        const u64 words = 2ull * nb + (u64)ntiles * nb;
+        u32* tmp = dalloc<u32>(words);
+        CUDA_TRY(cudaMemsetAsync(tmp, 0, 4 * words, st));
+        u32 *lhist = tmp, *dbase = tmp + nb, *status = tmp + 2ull * nb;
+        const int smem = L0S_TILE * 22 + (L0S_WARPS + 2) * (int)nb * 4;
+        CUDA_TRY(cudaFuncSetAttribute(k_l0_split, cudaFuncAttributeMaxDynamicSharedMemorySize, L0SplitSmem::bytes));
+        CUDA_TRY(cudaFuncSetAttribute(k_l0_split, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        pb();
+        k_route_hist<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, nb, lhist);
+        k_l0_cells<<<1, L0S_MAX_BINS, 0, st>>>(lhist, nb, box, n0, dbase, cell_start, cell_idx, &d_scr->ncell);
+        pe("l0_hist", 2, n0, 16ull * n0);
+        pb();
+        k_l0_split<<<ntiles, L0S_THREADS, smem, st>>>(d_in, n0, S0, box, nb, dbits, dbase, d_segs, (u32)segs.size(), d_bat_in,
+                                                      pts, bat, status);
+        pe("l0_split", 1, n0, 36ull * n0);
+        dfree(tmp);
+    } else {
+        const RadixPlan plan0 = radix_plan(pb0, cb0);
+        u64 *kA = dalloc<u64>(n0), *kB = dalloc<u64>(n0);
+        u32 *vA = pairs0 ? dalloc<u32>(n0) : nullptr, *vB = pairs0 ? dalloc<u32>(n0) : nullptr;
+        RadixTemp rt;
+        const u64 rwords = RadixTemp::ghist_words() + RadixTemp::status_words(n0, plan0);
+        rt.ghist = dalloc<u32>(rwords);
+        rt.status = rt.ghist + RadixTemp::ghist_words();
+        CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
+        pb();
+        k_l0_key<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, pb0, plan0, kA, vA, rt.ghist);
+        pe("l0_key", 1, n0, 24ull * n0);
+        int cur = pairs0 ? radix_sort<true>(kA, vA, kB, vB, n0, plan0, rt, st, *this)
+                         : radix_sort<false>(kA, vA, kB, vB, n0, plan0, rt, st, *this);
+        u64* ks = cur ? kB : kA;
+        u32* vs = cur ? vB : vA;
+        trace_mark(st, "l0_sort", 0, n0);
+        void* scan_tmp = dalloc<unsigned char>(chain_scan_temp_bytes<256, 8>(n0));
+        L0HeadOp hop{ks, n0, pb0, box, cell_start, cell_idx, &d_scr->ncell};
+        pb();
+        int nl = chain_scan<L0HeadOp, 256, 8>(hop, n0, scan_tmp, st);
+        pe("l0_heads", nl, n0, 8ull * n0);
+        pb();
+        k_l0_gather<<<div_up(n0, 256), 256, 0, st>>>(d_in, ks, vs, n0, pb0, d_segs, (u32)segs.size(), d_bat_in, pts, bat);
+        pe("l0_gather", 1, n0, 44ull * n0);
+        dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
+    }
     fetch_scratch();
     u32 ncell = h_scr->ncell;
     trace_mark(st, "l0_gather", 0, n0);
-    dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp); dfree(d_segs);
+    dfree(d_segs);
 
     // ---- waves of level-0 cells.  Level-0 cells never interact (converter.rs:124-134: a cell only receives from
     // its parent), so the forest is built a contiguous group of level-0 cells at a time: the node images of one

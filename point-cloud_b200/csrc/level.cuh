@@ -187,6 +187,216 @@ __global__ void k_l0_gather(const PcbPoint* __restrict__ in_pts, const u64* __re
     bat[j] = s.first_batch + (i - s.start) / s.batch_size + 1u;
 }
 
+// ---- level-0 arrivals in ONE pass when the level-0 box has at most 512 cells ---------------------------------
+// (the usual case: 1000-unit cells).  k_l0_key + a radix pass + the head scan + k_l0_gather move every point
+// 16 R + 8 W, 8 R + 8 W, 8 R, 8 + 16 R + 20 W; here a dense per-cell histogram (16 R, k_route_hist) gives the first
+// slot of every cell, and k_l0_split - a onesweep pass whose "key" is the point itself and whose digit is the dense
+// cell id - reads each point once and writes it (and its batch ordinal) once at its final place: stable ranking
+// per warp, tile staged in shared memory in cell order, decoupled look-back over per-tile cell counts.
+#define L0S_THREADS 256
+#define L0S_ITEMS 8
+#define L0S_TILE (L0S_THREADS * L0S_ITEMS)
+#define L0S_WARPS (L0S_THREADS / 32)
+#define L0S_MAX_BINS 512
+
+// one block: dense histogram -> first slot of every dense cell + the CSR of the non-empty cells (sorted by dense id,
+// the order of the level-0 keys: z, y, x)
+__global__ void __launch_bounds__(L0S_MAX_BINS)
+k_l0_cells(const u32* __restrict__ hist, u32 vol, L0Box box, u32 n, u32* __restrict__ dbase, u32* __restrict__ cell_start,
+           int* __restrict__ cell_idx, u32* __restrict__ ncell_out) {
+    __shared__ u32 s_cnt[L0S_MAX_BINS], s_ne[L0S_MAX_BINS];
+    const u32 t = threadIdx.x;
+    const u32 c = t < vol ? hist[t] : 0u;
+    s_cnt[t] = c;
+    s_ne[t] = c ? 1u : 0u;
+    __syncthreads();
+    for (u32 o = 1; o < L0S_MAX_BINS; o <<= 1) {   // Hillis-Steele inclusive scans
+        u32 a = t >= o ? s_cnt[t - o] : 0u, b = t >= o ? s_ne[t - o] : 0u;
+        __syncthreads();
+        s_cnt[t] += a;
+        s_ne[t] += b;
+        __syncthreads();
+    }
+    if (t < vol) {
+        const u32 first = s_cnt[t] - c;
+        dbase[t] = first;
+        if (c) {
+            const u32 ord = s_ne[t] - 1u;
+            cell_start[ord] = first;
+            cell_idx[3 * ord + 0] = box.ox + (int)(t % box.nx);
+            cell_idx[3 * ord + 1] = box.oy + (int)((t / box.nx) % box.ny);
+            cell_idx[3 * ord + 2] = box.oz + (int)(t / (box.nx * box.ny));
+        }
+    }
+    if (t == L0S_MAX_BINS - 1) {
+        cell_start[s_ne[t]] = n;
+        *ncell_out = s_ne[t];
+    }
+}
+
+struct L0SplitSmem {
+    static constexpr int bytes = L0S_TILE * 16 + L0S_TILE * 4 + L0S_TILE * 2 + L0S_WARPS * L0S_MAX_BINS * 4 +
+                                 2 * L0S_MAX_BINS * 4;
+};
+
+__global__ void __launch_bounds__(L0S_THREADS, 3)
+k_l0_split(const PcbPoint* __restrict__ in_pts, u32 n, float S0, L0Box box, u32 nb, int bits,
+           const u32* __restrict__ dbase, const BatchSeg* __restrict__ segs, u32 nseg, const u32* __restrict__ in_bat,
+           PcbPoint* __restrict__ pts, u32* __restrict__ bat, u32* __restrict__ status /* [ntiles][nb] */) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint4* s_pts = (uint4*)smem_raw;
+    u32* s_idx = (u32*)(s_pts + L0S_TILE);
+    unsigned short* s_dig = (unsigned short*)(s_idx + L0S_TILE);
+    u32* cnt = (u32*)(s_dig + L0S_TILE);   // [WARPS][nb]
+    u32* dig_excl = cnt + L0S_WARPS * nb;
+    u32* gbase = dig_excl + nb;
+    __shared__ u32 s_warp_sums[L0S_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u32 tile = blockIdx.x;   // tile = block index, see k_chain_scan
+    const u64 tbase = (u64)tile * L0S_TILE;
+    const u32 tile_n = (u32)min((u64)L0S_TILE, (u64)n - tbase);
+    for (u32 i = tid; i < L0S_WARPS * nb; i += L0S_THREADS) cnt[i] = 0;
+    __syncthreads();
+
+    // warp-striped ownership: item k of lane l in warp w is element w * 32 * ITEMS + 32 k + l of the tile
+    uint4 p[L0S_ITEMS];
+    u32 dig[L0S_ITEMS];
+    const u32 wbase = warp * 32 * L0S_ITEMS + lane;
+    u32* wcnt = cnt + warp * nb;
+#pragma unroll
+    for (int k = 0; k < L0S_ITEMS; k++) {
+        const u32 j = wbase + 32 * k;
+        dig[k] = nb;
+        if (j < tile_n) {
+            p[k] = __ldg((const uint4*)(in_pts + tbase + j));
+            PcbPoint q;
+            q.x = __uint_as_float(p[k].x); q.y = __uint_as_float(p[k].y); q.z = __uint_as_float(p[k].z); q.rgba = p[k].w;
+            dig[k] = (u32)l0_cell_id(q, S0, box);
+            atomicAdd(&wcnt[dig[k]], 1u);   // early counts (see k_onesweep)
+        }
+    }
+    __syncthreads();
+
+    constexpr u32 DPT = L0S_MAX_BINS / L0S_THREADS;   // 2 digits per thread at most
+    const u32 d0 = tid * DPT;
+    u32 count[DPT];
+    u32 tsum = 0;
+#pragma unroll
+    for (u32 q = 0; q < DPT; q++) {
+        const u32 d = d0 + q;
+        count[q] = 0;
+        if (d < nb) {
+            u32 running = 0;
+#pragma unroll
+            for (int w = 0; w < L0S_WARPS; w++) running += cnt[w * nb + d];
+            count[q] = running;
+            *(volatile u32*)&status[(u64)tile * nb + d] = running | (tile == 0 ? RADIX_FLAG_INCL : RADIX_FLAG_AGG);
+        }
+        tsum += count[q];
+    }
+    u32 tinc = tsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        u32 a = __shfl_up_sync(0xFFFFFFFFu, tinc, o);
+        if (lane >= o) tinc += a;
+    }
+    if (lane == 31) s_warp_sums[warp] = tinc;
+    __syncthreads();
+    u32 toff = 0;
+#pragma unroll
+    for (int w = 0; w < L0S_WARPS; w++)
+        if (w < warp) toff += s_warp_sums[w];
+    u32 texcl = toff + tinc - tsum;
+#pragma unroll
+    for (u32 q = 0; q < DPT; q++) {
+        const u32 d = d0 + q;
+        if (d < nb) {
+            u32 running = texcl;
+#pragma unroll
+            for (int w = 0; w < L0S_WARPS; w++) {
+                u32 c = cnt[w * nb + d];
+                cnt[w * nb + d] = running;   // first staged slot of (warp, cell)
+                running += c;
+            }
+            dig_excl[d] = texcl;
+            texcl += count[q];
+        }
+    }
+    __syncthreads();
+
+    // stable ranking inside the warp, points go straight to their staged slot
+    const u32 lt = (1u << lane) - 1u;
+    bool votes = false;
+#pragma unroll
+    for (int k = 0; k < L0S_ITEMS; k++) {
+        const u32 j = wbase + 32 * k;
+        const bool valid = j < tile_n;
+        const u32 d = valid ? dig[k] : 0u;
+        const u32 peers = radix_peers<2>(d, valid, bits, 1u << bits, k, votes);
+        const u32 lower = __popc(peers & lt);
+        const u32 before = valid ? wcnt[d] : 0u;
+        __syncwarp();
+        if (valid && lower == 0) wcnt[d] = before + __popc(peers);
+        __syncwarp();
+        if (valid) {
+            s_pts[before + lower] = p[k];
+            s_idx[before + lower] = (u32)(tbase + j);
+            s_dig[before + lower] = (unsigned short)d;
+        }
+    }
+
+    // decoupled look-back per cell over the tiles before this one
+#pragma unroll
+    for (u32 q = 0; q < DPT; q++) {
+        const u32 d = d0 + q;
+        if (d < nb) {
+            u32 prev = 0;
+            if (tile > 0) {
+                int t = (int)tile - 1;
+                const volatile u32* sp = status + (u64)t * nb + d;
+                bool done = false;
+                while (!done) {
+                    u32 w[RADIX_WINDOW];
+#pragma unroll
+                    for (int x = 0; x < RADIX_WINDOW; x++) w[x] = (t - x >= 0) ? *(sp - (size_t)x * nb) : RADIX_FLAG_INCL;
+#pragma unroll
+                    for (int x = 0; x < RADIX_WINDOW; x++) {
+                        if (!done) {
+                            u32 sw = w[x];
+                            while ((sw & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u) sw = *(sp - (size_t)x * nb);
+                            prev += sw & RADIX_COUNT_MASK;
+                            done = (sw & RADIX_FLAG_INCL) != 0u;
+                        }
+                    }
+                    t -= RADIX_WINDOW;
+                    sp -= (size_t)RADIX_WINDOW * nb;
+                }
+                *(volatile u32*)&status[(u64)tile * nb + d] = ((prev + count[q]) & RADIX_COUNT_MASK) | RADIX_FLAG_INCL;
+            }
+            gbase[d] = __ldg(dbase + d) + prev - dig_excl[d];
+        }
+    }
+    __syncthreads();
+    for (u32 j = tid; j < tile_n; j += L0S_THREADS) {
+        const u32 g = gbase[s_dig[j]] + j;
+        const u32 i = s_idx[j];
+        *(uint4*)(pts + g) = s_pts[j];
+        u32 b;
+        if (in_bat) {
+            b = __ldg(in_bat + i) + 1u;
+        } else {
+            u32 lo = 0, hi = nseg;
+            while (hi - lo > 1) {
+                u32 mid = (lo + hi) >> 1;
+                if (segs[mid].start <= i) lo = mid; else hi = mid;
+            }
+            const BatchSeg sg = segs[lo];
+            b = sg.first_batch + (i - sg.start) / sg.batch_size + 1u;
+        }
+        bat[g] = b;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // The child octant of a loser is bit-for-bit cell_index(p, level + 1) - 2 * cell_index (converter.rs:68,
 // metadata.rs:100-102).  x -> floor(x / S_child) is monotone, so for the odd child index m = 2 * i + 1 there is

@@ -189,3 +189,30 @@ def test_waves_of_level0_cells_forced():
     env = dict(os.environ, PCB_WAVE_POINTS="7000")
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "waves ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_level0_sort_path_forced_and_wide_boxes():
+    """Level-0 arrivals are made by a single split pass when the level-0 box has at most 512 cells, else by the
+    key / radix sort / gather path.  Both must give the oracle's trees: the sort path forced on small boxes
+    (PCB_L0_SORT, fresh process), and a cloud whose box is wider than 512 cells in this process."""
+    import os
+    import subprocess
+    import sys
+    rng = np.random.default_rng(31)
+    wide = make_points(rng.random((60_000, 3)) * [40.0 * 30, 40.0 * 30, 40.0] - [600.0, 600.0, 0.0])
+    _check([wide], config=(50, 8, 40.0), bs=1000)   # 30 x 30 x 1 level-0 cells
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "import numpy as np\n"
+        "from pcutil import compare_trees, load_pcb, make_points, oracle_convert\n"
+        "rng = np.random.default_rng(37)\n"
+        "for cfg, bs, n, ext in (((100, 8, 10.0), 1000, 40000, 50), ((5000, 96, 1000.0), 10000, 200000, 2500)):\n"
+        "    pts = make_points(rng.random((n, 3)) * ext - ext / 2)\n"
+        "    o = oracle_convert([pts], config=cfg, batch_size=bs)\n"
+        "    nodes, mj, st, _ = load_pcb().convert([pts], config=cfg, batch_size=bs)\n"
+        "    compare_trees(o.nodes, nodes, 'oracle', 'gpu-l0sort')\n"
+        "    assert mj == o.meta_json and all(o.nodes[k] == nodes[k] for k in nodes)\n"
+        "print('l0 sort ok')\n") % os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, PCB_L0_SORT="1")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "l0 sort ok" in r.stdout, r.stdout + r.stderr
