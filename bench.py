@@ -362,10 +362,10 @@ def main():
                                     sorted(kstats.items(), key=lambda kv: -kv[1]["ms"])}}
         cpu = None
         if not args.no_cpu:
-            ncpu = int(DENSITY * 1000.0 * 1000.0 * args.cpu_scale)
-            v, dt = cpu_oracle_run(ncpu, (0.0, 1000.0, 0.0, 1000.0), 1)
+            ncpu = int(DENSITY * 3000.0 * 1000.0 * args.cpu_scale)
+            v, dt = cpu_oracle_run(ncpu, (0.0, 3000.0, 0.0, 1000.0), 1)
             cpu = {"value": round(v, 4), "unit": UNIT, "cores": 1, "kind": "port", "seconds": round(dt, 2),
-                   "sample": f"{ncpu} points: one level-0 cell (1 km^2) of the same terrain generator at the "
+                   "sample": f"{ncpu} points: three level-0 cells (3 km x 1 km) of the same terrain generator at the "
                              f"workload's density ({DENSITY}/m^2); sequential oracle = the reference CLI's own "
                              f"concurrency (single-threaded)"}
         out = {"metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
