@@ -752,6 +752,7 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     static_assert(OCT_TILE <= OCT_TILE_MAX && OCT_ITEMS % 8 == 0, "tile shape");
     __shared__ OctPacked s_warp[WARPS];
     __shared__ Oct8 s_prefix;
+    __shared__ u32 s_run[9][OCT_THREADS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const u32 tile = blockIdx.x;   // see k_chain_scan
     const u64 base = (u64)tile * OCT_TILE + (u64)tid * OCT_ITEMS;
@@ -830,6 +831,11 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
         run[k] = texcl.head ? a : s_prefix.c[k] + a;
         run[4 + k] = texcl.head ? b : s_prefix.c[4 + k] + b;
     }
+    // The eight running counters live in shared memory, one column per thread (row = octant, so a warp's accesses
+    // never share a bank): rank = load, bump = store, instead of eight selects and eight predicated adds per item.
+    // Row 8 takes the arrivals that emit nothing.
+#pragma unroll
+    for (int q = 0; q < 8; q++) s_run[q][tid] = run[q];
     u32 rk[OCT_ITEMS];
 #pragma unroll
     for (int k = 0; k < OCT_ITEMS; k++) {
@@ -837,14 +843,12 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
         const u32 o = code[k] & 0xFu;
         if (code[k] & 16u) {
 #pragma unroll
-            for (int q = 0; q < 8; q++) run[q] = 0;
+            for (int q = 0; q < 8; q++) s_run[q][tid] = 0;
         }
-        u32 r = 0;
-#pragma unroll
-        for (int q = 0; q < 8; q++) r = (o == (u32)q) ? run[q] : r;
+        const u32 got = s_run[o][tid];
+        s_run[o][tid] = got + 1u;
+        const u32 r = o < 8u ? got : 0u;
         rk[k] = r;
-#pragma unroll
-        for (int q = 0; q < 8; q++) run[q] += (o == (u32)q) ? 1u : 0u;
         if (i < n) {
             u32 c = PCB_NONE;
             if (o < 8u && (op.ex_state || r == 0 || r + 1 == op.L || r == op.L)) {
@@ -863,7 +867,7 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
             if (code[k] & 32u) {   // last arrival of its cell: bucket totals
                 if (c == PCB_NONE) c = find_segment(op.cell_start, op.ncell, (u32)i);
 #pragma unroll
-                for (int q = 0; q < 8; q++) op.bcnt[8 * c + q] = run[q];
+                for (int q = 0; q < 8; q++) op.bcnt[8 * c + q] = s_run[q][tid];
             }
         }
     }

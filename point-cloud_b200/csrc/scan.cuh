@@ -231,11 +231,15 @@ __device__ __forceinline__ typename Op::State chain_lookback(const Op& op, uint4
             State s = op.identity();
             if (t >= 0) {
                 uint4 a, b;
-                do {   // both words of one publication (a reader may catch the writer between its two stores)
+                for (;;) {   // both words of one publication (a reader may catch the writer between its two stores)
                     a = ld_volatile_v4(desc + 2 * (u64)t);
                     b = ld_volatile_v4(desc + 2 * (u64)t + 1);
                     f = a.w & PCB_DESC_MASK;
-                } while (f == 0u || f != (b.w & PCB_DESC_MASK));
+                    if (f != 0u && f == (b.w & PCB_DESC_MASK)) break;
+#ifdef PCB_SPIN_BACKOFF
+                    __nanosleep(PCB_SPIN_BACKOFF);
+#endif
+                }
                 s = Op::unpack(a, b);
             }
             const u32 m = __ballot_sync(0xFFFFFFFFu, f == PCB_DESC_INCL);
