@@ -55,17 +55,18 @@ static inline RadixPlan radix_plan(int lo, int nbits) {
 // ---- histogram side (called from the key-producing kernels) ----------------------------------------------
 // shared: u32 hist[npass * RADIX_MAX_BINS], zeroed by the caller
 __device__ __forceinline__ void radix_hist_add(u32* __restrict__ hist, const RadixPlan& plan, u64 key) {
-#pragma unroll
-    for (int p = 0; p < RADIX_MAX_PASSES; p++) {
-        if (p + 1 < plan.npass) {
-            atomicAdd(&hist[p * RADIX_MAX_BINS + ((u32)(key >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u))], 1u);
-        } else if (p + 1 == plan.npass) {
-            // the most significant digit is nearly uniform inside a warp (arrivals come cell by cell):
-            // aggregate in the warp instead of serialising 32 atomics on one address
-            const u32 d = (u32)(key >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u);
-            const u32 peers = __match_any_sync(__activemask(), d);
-            if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u) atomicAdd(&hist[p * RADIX_MAX_BINS + d], (u32)__popc(peers));
-        }
+    // a real loop over the lower passes (the plan sits in the constant bank: indexed loads, no unrolled
+    // compare-and-branch ladder over RADIX_MAX_PASSES), then the top pass
+    const int top = plan.npass - 1;
+#pragma unroll 1
+    for (int p = 0; p < top; p++)
+        atomicAdd(&hist[p * RADIX_MAX_BINS + ((u32)(key >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u))], 1u);
+    if (top >= 0) {
+        // the most significant digit is nearly uniform inside a warp (arrivals come cell by cell):
+        // aggregate in the warp instead of serialising 32 atomics on one address
+        const u32 d = (u32)(key >> plan.shift[top]) & ((1u << plan.bits[top]) - 1u);
+        const u32 peers = __match_any_sync(__activemask(), d);
+        if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u) atomicAdd(&hist[top * RADIX_MAX_BINS + d], (u32)__popc(peers));
     }
 }
 __device__ __forceinline__ void radix_hist_flush(const u32* __restrict__ hist, const RadixPlan& plan, u32* __restrict__ ghist) {
