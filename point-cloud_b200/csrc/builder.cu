@@ -858,11 +858,13 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     rt.ghist = dalloc<u32>(rwords);
     rt.status = rt.ghist + RadixTemp::ghist_words();
     CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
+    u32* d2a = dalloc<u32>(n);                       // contest inputs by arrival position, written by k_hexkey
+    unsigned char* octa = dalloc<unsigned char>(n);
     pb();
     k_cellgeo<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, cell_start, ncell, g, geo, &d_scr->err);
     k_hexkey<PAIRS><<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay,
-                                                                            plan, kA, vA, rt.ghist, &d_scr->err);
-    pe("hexkey", 2, n, (PAIRS ? 28ull : 24ull) * n);
+                                                                            plan, kA, vA, d2a, octa, rt.ghist, &d_scr->err);
+    pe("hexkey", 2, n, (PAIRS ? 33ull : 29ull) * n);
     trace_mark(st, "hexkey", h, n);
 
     // ---- stage 3: stable sort by (cell, Z, Y, X)
@@ -879,7 +881,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                                                       chain_scan_temp_bytes<64, 8>(n)),
                                         chain_scan_temp_bytes<256, 4>(ncell));
     void* scan_tmp = dalloc<unsigned char>(tmp_bytes);
-    ContestOp<PAIRS> cop{ks, vs, n, lay, g, pts, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
+    ContestOp<PAIRS> cop{ks, vs, n, lay, g, d2a, octa, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
     pb();
     static const int contest_minb = getenv("PCB_CONTEST_MINB") ? atoi(getenv("PCB_CONTEST_MINB")) : 3;  // tuning hook
     int nl = contest_minb == 4   ? chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, n, scan_tmp, st)
@@ -887,7 +889,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
              : contest_minb == 8 ? chain_scan<ContestOp<PAIRS>, 128, 8, 8>(cop, n, scan_tmp, st)
              : contest_minb == 12 ? chain_scan<ContestOp<PAIRS>, 64, 8, 12>(cop, n, scan_tmp, st)
                                  : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, n, scan_tmp, st);
-    pe("contest", nl, n, (PAIRS ? 36ull : 32ull) * n);
+    pe("contest", nl, n, (PAIRS ? 25ull : 21ull) * n);
     trace_mark(st, "contest", h, n);
 
     // ---- stages 5-6: segmented 8-way split of the losers (ranks inside their (cell, octant) buckets)
@@ -975,7 +977,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     levels.push_back(img);
 
     // ---- hand over to the next level
-    dfree(geo); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
+    dfree(geo); dfree(d2a); dfree(octa); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
     dfree(win_src); dfree(win_end); dfree(rank); dfree(bcnt); dfree(special); dfree(bdst);
     dfree(cell_deliver); dfree(cell_children); dfree(cell_dbase); dfree(cell_cbase); dfree(cell_bytes); dfree(node_off);
     dfree(ex_state); dfree(ex_m0); dfree(ex_pts); dfree(ex_bucket); dfree(ex_rank);

@@ -456,7 +456,8 @@ template <bool PAIRS>
 __global__ void __launch_bounds__(256)
 k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_start, u32 ncell,
          const CellGeo* __restrict__ geo, LevelGeom g, KeyLayout lay, RadixPlan plan, u64* __restrict__ keys,
-         u32* __restrict__ vals, u32* __restrict__ ghist, u32* __restrict__ err) {
+         u32* __restrict__ vals, u32* __restrict__ d2_out, unsigned char* __restrict__ oct_out,
+         u32* __restrict__ ghist, u32* __restrict__ err) {
     __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
     for (int i = threadIdx.x; i < plan.npass * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
     __syncthreads();
@@ -491,6 +492,10 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
                 key = (key << lay.pb) | i;
             }
             keys[i] = key;
+            // what the contest needs of this point, by arrival position: 5 bytes that stay L2-resident per cell,
+            // instead of a random 16-byte gather of the point itself (one DRAM sector per arrival)
+            d2_out[i] = __float_as_uint(hex_d2(k, p.x, p.y, p.z, g.R, g.half_sqrt3, g.row_pitch));
+            oct_out[i] = (unsigned char)((p.x >= cg.tx ? 4u : 0u) | (p.y >= cg.ty ? 2u : 0u) | (p.z >= cg.tz ? 1u : 0u));
             radix_hist_add(hist, plan, key);
         }
     }
@@ -526,7 +531,8 @@ struct ContestOp {
     u32 n;
     KeyLayout lay;
     LevelGeom g;
-    const PcbPoint* pts;
+    const u32* d2a;             // [n] by arrival position: d2 to the prism centre (hex.rs:55-65, cell.rs:77-78), from k_hexkey
+    const unsigned char* octa;  // [n] by arrival position: child octant (metadata.rs:100-102 one level down)
     const CellGeo* geo;
     u64* em;       // [n] by arrival position: loser's arrival position | octant << 32 | flags
     u32* win_src;  // [#groups] arrival position of each winner, sorted (cell, Z, Y, X)
@@ -566,9 +572,12 @@ struct ContestOp {
             else pos[k] = (u32)(key[k] & ((1ull << lay.pb) - 1ull));
         }
         // the gathers go first: they are the long-latency part
-        uint4 pt[ITEMS];
+        u32 d2v[ITEMS], ocv[ITEMS];
 #pragma unroll
-        for (int k = 0; k < ITEMS; k++) pt[k] = (base + k < n) ? __ldg((const uint4*)(pts + pos[k])) : make_uint4(0, 0, 0, 0);
+        for (int k = 0; k < ITEMS; k++) {
+            d2v[k] = (base + k < n) ? __ldg(d2a + pos[k]) : 0u;
+            ocv[k] = (base + k < n) ? (u32)__ldg(octa + pos[k]) : 0u;
+        }
         // neighbours across the thread boundary
         u64 prevk = __shfl_up_sync(0xFFFFFFFFu, key[ITEMS - 1], 1);
         u64 nextk = __shfl_down_sync(0xFFFFFFFFu, key[0], 1);
@@ -593,20 +602,14 @@ struct ContestOp {
                 cg = load_geo(geo, c);
                 cprev = c;
             }
-            const float px = __uint_as_float(pt[k].x), py = __uint_as_float(pt[k].y), pz = __uint_as_float(pt[k].z);
-            HexKey hk;
-            hk.x = (i32)((u32)G & ((1u << g.bx) - 1u)) + cg.hx;
-            hk.y = (i32)((u32)(G >> g.bx) & ((1u << g.by) - 1u)) + cg.hy;
-            hk.z = (i32)((u32)(G >> (g.bx + g.by)) & ((1u << g.bz) - 1u)) + cg.hz;
-            const float d2 = hex_d2(hk, px, py, pz, g.R, g.half_sqrt3, g.row_pitch);
-            u32 meta = (px >= cg.tx ? 4u : 0u) | (py >= cg.ty ? 2u : 0u) | (pz >= cg.tz ? 1u : 0u);
+            u32 meta = ocv[k];
             const bool head = (i == 0) || Gp != G;
             const bool last = (i + 1 == n);
             const bool tail = last || Gn != G;
             const bool cell_end = last || (Gn >> g.hexbits) != (G >> g.hexbits);
             meta |= (head ? 0x100u : 0u) | (tail ? 0x200u : 0u) | (cell_end ? 0x400u : 0u);
             meta |= (cg.start == pos[k] ? 0x800u : 0u) | (cg.end == pos[k] + 1u ? 0x1000u : 0u);
-            v[k] = State{((u64)__float_as_uint(d2) << 32) | pos[k], meta, tail ? 1u : 0u};
+            v[k] = State{((u64)d2v[k] << 32) | pos[k], meta, tail ? 1u : 0u};
         }
     }
     __device__ State load(u32) const { return identity(); }   // unused (kTileLoad)
