@@ -1194,3 +1194,12 @@ int device_count() {
 }
 
 }  // namespace pcb
+
+#ifdef PCB_RADIX_INSTR
+// diagnostics build only: cycles per onesweep phase summed over tiles (see RADIX_TICK), reset on read
+extern "C" int pcb_debug_radix_instr(unsigned long long* out) {
+    unsigned long long zero[16] = {0};
+    if (cudaMemcpyFromSymbol(out, g_radix_instr, sizeof(zero)) != cudaSuccess) return -1;
+    return cudaMemcpyToSymbol(g_radix_instr, zero, sizeof(zero)) == cudaSuccess ? 0 : -1;
+}
+#endif
