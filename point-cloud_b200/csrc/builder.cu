@@ -847,24 +847,57 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     lay.hexbits = g.hexbits;
     lay.pb = PAIRS ? 0 : std::max(1, bits_count(n));
     if (lay.cb + lay.hexbits + lay.pb > 64) throw Error{PCB_ERR_RANGE, "too many cells on one level"};
-    const RadixPlan plan = radix_plan(lay.pb, lay.cb + lay.hexbits);
+    // Arrivals come cell by cell, so the sort only has to order every cell's arrivals by prism: when the cell bits
+    // would cost extra passes, runs of 2^segk consecutive cells ("segments") are sorted independently inside the same
+    // launches and only segk cell bits take part (radix.cuh).  Taken when segments average >= PCB_SEG_MIN arrivals
+    // (tiles never straddle a segment: small segments mean partly filled tiles).
+    static const bool seg_off = getenv("PCB_NO_SEG") != nullptr;                                       // tuning / test hooks
+    static const u64 seg_min = getenv("PCB_SEG_MIN") ? strtoull(getenv("PCB_SEG_MIN"), nullptr, 10) : 4ull * RADIX_TILE;
+    int segk = 31;
+    u32 nseg = 1;
+    {
+        const int db = radix_digit_bits();
+        const int top = div_up(lay.hexbits + 1, db) * db;   // room left in the top digit
+        const int k = top - lay.hexbits;
+        if (!seg_off && lay.cb > k && div_up(lay.hexbits + k, db) < div_up(lay.hexbits + lay.cb, db) &&
+            (u64)n >= seg_min * div_up(ncell, 1u << k)) {
+            segk = k;
+            nseg = div_up(ncell, 1u << k);
+        }
+    }
+    const RadixPlan plan = radix_plan(lay.pb, (nseg > 1 ? segk : lay.cb) + lay.hexbits);
 
     // ---- stages 1-2: hex keys (+ the digit histograms of every pass)
     CellGeo* geo = dalloc<CellGeo>(ncell);
     u64 *kA = dalloc<u64>(n), *kB = dalloc<u64>(n);
     u32 *vA = PAIRS ? dalloc<u32>(n) : nullptr, *vB = PAIRS ? dalloc<u32>(n) : nullptr;
     RadixTemp rt;
-    const u64 rwords = RadixTemp::ghist_words() + RadixTemp::status_words(n, plan);
+    const u64 hwords = nseg > 1 ? RadixTemp::ghist_words_seg(nseg, plan) : RadixTemp::ghist_words();
+    const u64 rwords = hwords + RadixTemp::status_words(n, plan, nseg > 1 ? nseg : 0);
     rt.ghist = dalloc<u32>(rwords);
-    rt.status = rt.ghist + RadixTemp::ghist_words();
+    rt.status = rt.ghist + hwords;
     CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
+    uint4* tinfo = nullptr;
+    u32* seg_base = nullptr;
+    if (nseg > 1) {
+        rt.nseg = nseg;
+        rt.ntiles_seg = (u32)RadixTemp::seg_tiles_bound(n, nseg);
+        tinfo = dalloc<uint4>(rt.ntiles_seg);
+        seg_base = dalloc<u32>(nseg + 1);
+        rt.tinfo = tinfo;
+    }
     u32* d2a = dalloc<u32>(n);                       // contest inputs by arrival position, written by k_hexkey
     unsigned char* octa = dalloc<unsigned char>(n);
     pb();
     k_cellgeo<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, cell_start, ncell, g, geo, &d_scr->err);
+    if (nseg > 1) {
+        k_seg_plan<<<1, 1024, 0, st>>>(cell_start, ncell, segk, nseg, seg_base);
+        k_seg_tiles<<<div_up(rt.ntiles_seg, 256), 256, 0, st>>>(cell_start, ncell, segk, seg_base, nseg, rt.ntiles_seg, tinfo);
+    }
     k_hexkey<PAIRS><<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay,
-                                                                            plan, kA, vA, d2a, octa, rt.ghist, &d_scr->err);
-    pe("hexkey", 2, n, (PAIRS ? 33ull : 29ull) * n);
+                                                                            plan, kA, vA, d2a, octa, rt.ghist, segk, nseg,
+                                                                            &d_scr->err);
+    pe("hexkey", nseg > 1 ? 4 : 2, n, (PAIRS ? 33ull : 29ull) * n);
     trace_mark(st, "hexkey", h, n);
 
     // ---- stage 3: stable sort by (cell, Z, Y, X)
@@ -978,6 +1011,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
 
     // ---- hand over to the next level
     dfree(geo); dfree(d2a); dfree(octa); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
+    dfree(tinfo); dfree(seg_base);
     dfree(win_src); dfree(win_end); dfree(rank); dfree(bcnt); dfree(special); dfree(bdst);
     dfree(cell_deliver); dfree(cell_children); dfree(cell_dbase); dfree(cell_cbase); dfree(cell_bytes); dfree(node_off);
     dfree(ex_state); dfree(ex_m0); dfree(ex_pts); dfree(ex_bucket); dfree(ex_rank);

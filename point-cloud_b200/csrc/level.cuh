@@ -453,30 +453,38 @@ __device__ __forceinline__ u32 cell_of_arrival(const u32* __restrict__ cell_star
 // Stage 2: hex-prism key (cell.rs:276-278 -> hex.rs:32-34) of every arrival, window-relative, plus the digit
 // histograms of all radix passes.
 template <bool PAIRS>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 8)   // 32 registers: eight blocks per SM (37 registers ran 20 % slower)
 k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_start, u32 ncell,
          const CellGeo* __restrict__ geo, LevelGeom g, KeyLayout lay, RadixPlan plan, u64* __restrict__ keys,
          u32* __restrict__ vals, u32* __restrict__ d2_out, unsigned char* __restrict__ oct_out,
-         u32* __restrict__ ghist, u32* __restrict__ err) {
+         u32* __restrict__ ghist, int segk /* segment = cell >> segk (31: one segment) */, u32 nseg,
+         u32* __restrict__ err) {
     __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
-    for (int i = threadIdx.x; i < plan.npass * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
+    for (int i = threadIdx.x; i < RADIX_MAX_PASSES * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
     __syncthreads();
     u32 bad = 0;
     // every block owns one contiguous chunk of arrivals: the cell ordinal is searched once, then walked
     const u64 chunk = (((u64)n + gridDim.x - 1) / gridDim.x + 255ull) & ~255ull;
     const u64 lo = (u64)blockIdx.x * chunk, hi = min((u64)n, lo + chunk);
+    const u32 seg_lo = lo < hi ? find_segment(cell_start, ncell, (u32)lo) >> segk : 0u;   // first segment of the block
+    const u32 seg_words = (u32)plan.npass * RADIX_MAX_BINS, slots = (u32)radix_hist_slots(plan);
     u32 c = 0;
     CellGeo cg;
     cg.end = 0;
+    u32 slot = 0;   // segment of cell c relative to the block's first segment (changes with the cell: rarely)
     if (lo + threadIdx.x < hi) {
         c = find_segment(cell_start, ncell, (u32)(lo + threadIdx.x));
         cg = load_geo(geo, c);
+        slot = (c >> segk) - seg_lo;
     }
     for (u64 i0 = lo; i0 < hi; i0 += 256) {
         u64 i = i0 + threadIdx.x;
         if (i < hi) {
             PcbPoint p = pts[i];
-            while (cg.end <= (u32)i) cg = load_geo(geo, ++c);
+            if (cg.end <= (u32)i) {
+                do cg = load_geo(geo, ++c); while (cg.end <= (u32)i);
+                slot = (c >> segk) - seg_lo;
+            }
             HexKey k = hex_from_world(p.x, p.y, p.z, g.R);
             u32 rx = (u32)(k.x - cg.hx);
             u32 ry = (u32)(k.y - cg.hy);
@@ -496,13 +504,14 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
             // instead of a random 16-byte gather of the point itself (one DRAM sector per arrival)
             d2_out[i] = __float_as_uint(hex_d2(k, p.x, p.y, p.z, g.R, g.half_sqrt3, g.row_pitch));
             oct_out[i] = (unsigned char)((p.x >= cg.tx ? 4u : 0u) | (p.y >= cg.ty ? 2u : 0u) | (p.z >= cg.tz ? 1u : 0u));
-            radix_hist_add(hist, plan, key);
+            if (slot < slots) radix_hist_add(hist + slot * seg_words, plan, key, slot);
+            else radix_hist_add_global(ghist + (u64)(seg_lo + slot) * seg_words, plan, key);
         }
     }
     for (int o = 16; o; o >>= 1) bad |= __shfl_xor_sync(0xFFFFFFFFu, bad, o);
     if ((threadIdx.x & 31) == 0 && bad) atomicOr(err, bad);
     __syncthreads();
-    radix_hist_flush(hist, plan, ghist);
+    radix_hist_flush_seg(hist, plan, ghist, seg_lo, nseg);
 }
 
 // Stage 4: the hex-grid contest of Cell::add_point (cell.rs:70-94) for every (cell, prism) group at

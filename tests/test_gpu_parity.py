@@ -156,6 +156,34 @@ def test_payload_sort_path_forced():
     assert r.returncode == 0 and "pairs ok" in r.stdout, r.stdout + r.stderr
 
 
+def test_segmented_sort_forced():
+    """Levels whose cell bits would cost extra radix passes sort runs of consecutive cells ("segments")
+    independently (radix.cuh).  Forced on small inputs with PCB_SEG_MIN=1 (fresh process): many cells per level
+    (several segments, partly filled tiles, segments of one tile), the default grid and a coarse one, with and
+    without the payload sort."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "import numpy as np\n"
+        "from pcutil import compare_trees, load_pcb, make_points, oracle_convert\n"
+        "rng = np.random.default_rng(43)\n"
+        "for cfg, bs, n, ext in (((100, 8, 10.0), 1000, 80000, 90), ((5000, 96, 1000.0), 10000, 300000, 9000),\n"
+        "                        ((20, 96, 4.0), 5000, 120000, 60), ((300, 20, 16.0), 2000, 250000, 100)):\n"
+        "    pts = make_points(rng.random((n, 3)) * [ext, ext, ext / 4] - [ext / 2, ext / 2, ext / 8])\n"
+        "    o = oracle_convert([pts], config=cfg, batch_size=bs)\n"
+        "    nodes, mj, st, _ = load_pcb().convert([pts], config=cfg, batch_size=bs)\n"
+        "    assert st.arrivals == o.arrivals and st.hierarchies == o.hierarchies\n"
+        "    compare_trees(o.nodes, nodes, 'oracle', 'gpu-seg')\n"
+        "    assert mj == o.meta_json and all(o.nodes[k] == nodes[k] for k in nodes)\n"
+        "print('seg ok')\n") % os.path.dirname(os.path.abspath(__file__))
+    for extra in ({}, {"PCB_FORCE_PAIRS": "1"}):
+        env = dict(os.environ, PCB_SEG_MIN="1", **extra)
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0 and "seg ok" in r.stdout, r.stdout + r.stderr
+
+
 def test_waves_of_level0_cells_forced():
     """The forest is built a group of level-0 cells ("wave") at a time.  Tiny waves (PCB_WAVE_POINTS, fresh
     process) must give the same trees as the oracle: many roots incl. negative cells, the default config, and a
