@@ -465,7 +465,7 @@ class BuilderImpl {
     bool pairs_mode_for(u32 n, u32 ncell, const LevelGeom& g);
     // Level-0 arrivals per wave.  With node images going to the host a quarter of the run per wave lets the
     // downloads overlap the build; device-only runs have nothing to overlap and keep one wave (fewer, larger
-    // launches) until the per-level arrays (68 B per arrival, twice) would crowd the device.
+    // launches) until the per-level arrays (72 B per arrival, twice) would crowd the device.
     u64 wave_points(u64 n0) const {
         static const u64 forced = getenv("PCB_WAVE_POINTS") ? strtoull(getenv("PCB_WAVE_POINTS"), nullptr, 10) : 0;
         if (forced) return forced;
@@ -662,8 +662,8 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
             wave_max = std::max<u64>(wave_max, (u64)h_cs[ncell] - h_cs[c]);
         }
     }
-    arena_prepare(0, std::max<u64>(arenas->a[0].cap, 68ull * wave_max + (64ull << 20)));
-    arena_prepare(1, std::max<u64>(arenas->a[1].cap, 68ull * wave_max + (64ull << 20)));
+    arena_prepare(0, std::max<u64>(arenas->a[0].cap, 72ull * wave_max + (64ull << 20)));
+    arena_prepare(1, std::max<u64>(arenas->a[1].cap, 72ull * wave_max + (64ull << 20)));
     u32 hmax = 0, c0 = 0;
     for (u32 c1 : wave_end) {
         u32 n = h_cs[c1] - h_cs[c0], wcell = c1 - c0, h = 0;
@@ -886,8 +886,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         seg_base = dalloc<u32>(nseg + 1);
         rt.tinfo = tinfo;
     }
-    u32* d2a = dalloc<u32>(n);                       // contest inputs by arrival position, written by k_hexkey
-    unsigned char* octa = dalloc<unsigned char>(n);
+    uint2* d2oct = dalloc<uint2>(n);                 // contest inputs by arrival position, written by k_hexkey
     pb();
     k_cellgeo<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, cell_start, ncell, g, geo, &d_scr->err);
     if (nseg > 1) {
@@ -895,9 +894,9 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         k_seg_tiles<<<div_up(rt.ntiles_seg, 256), 256, 0, st>>>(cell_start, ncell, segk, seg_base, nseg, rt.ntiles_seg, tinfo);
     }
     k_hexkey<PAIRS><<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay,
-                                                                            plan, kA, vA, d2a, octa, rt.ghist, segk, nseg,
+                                                                            plan, kA, vA, d2oct, rt.ghist, segk, nseg,
                                                                             &d_scr->err);
-    pe("hexkey", nseg > 1 ? 4 : 2, n, (PAIRS ? 33ull : 29ull) * n);
+    pe("hexkey", nseg > 1 ? 4 : 2, n, (PAIRS ? 36ull : 32ull) * n);
     trace_mark(st, "hexkey", h, n);
 
     // ---- stage 3: stable sort by (cell, Z, Y, X)
@@ -914,7 +913,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                                                       chain_scan_temp_bytes<64, 8>(n)),
                                         chain_scan_temp_bytes<256, 4>(ncell));
     void* scan_tmp = dalloc<unsigned char>(tmp_bytes);
-    ContestOp<PAIRS> cop{ks, vs, n, lay, g, d2a, octa, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
+    ContestOp<PAIRS> cop{ks, vs, n, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
     pb();
     static const int contest_minb = getenv("PCB_CONTEST_MINB") ? atoi(getenv("PCB_CONTEST_MINB")) : 3;  // tuning hook
     int nl = contest_minb == 4   ? chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, n, scan_tmp, st)
@@ -922,7 +921,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
              : contest_minb == 8 ? chain_scan<ContestOp<PAIRS>, 128, 8, 8>(cop, n, scan_tmp, st)
              : contest_minb == 12 ? chain_scan<ContestOp<PAIRS>, 64, 8, 12>(cop, n, scan_tmp, st)
                                  : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, n, scan_tmp, st);
-    pe("contest", nl, n, (PAIRS ? 25ull : 21ull) * n);
+    pe("contest", nl, n, (PAIRS ? 28ull : 24ull) * n);
     trace_mark(st, "contest", h, n);
 
     // ---- stages 5-6: segmented 8-way split of the losers (ranks inside their (cell, octant) buckets)
@@ -1010,7 +1009,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     levels.push_back(img);
 
     // ---- hand over to the next level
-    dfree(geo); dfree(d2a); dfree(octa); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
+    dfree(geo); dfree(d2oct); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
     dfree(tinfo); dfree(seg_base);
     dfree(win_src); dfree(win_end); dfree(rank); dfree(bcnt); dfree(special); dfree(bdst);
     dfree(cell_deliver); dfree(cell_children); dfree(cell_dbase); dfree(cell_cbase); dfree(cell_bytes); dfree(node_off);

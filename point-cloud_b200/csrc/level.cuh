@@ -456,7 +456,7 @@ template <bool PAIRS>
 __global__ void __launch_bounds__(256, 8)   // 32 registers: eight blocks per SM (37 registers ran 20 % slower)
 k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_start, u32 ncell,
          const CellGeo* __restrict__ geo, LevelGeom g, KeyLayout lay, RadixPlan plan, u64* __restrict__ keys,
-         u32* __restrict__ vals, u32* __restrict__ d2_out, unsigned char* __restrict__ oct_out,
+         u32* __restrict__ vals, uint2* __restrict__ d2oct_out,
          u32* __restrict__ ghist, int segk /* segment = cell >> segk (31: one segment) */, u32 nseg,
          u32* __restrict__ err) {
     __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
@@ -500,10 +500,11 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
                 key = (key << lay.pb) | i;
             }
             keys[i] = key;
-            // what the contest needs of this point, by arrival position: 5 bytes that stay L2-resident per cell,
-            // instead of a random 16-byte gather of the point itself (one DRAM sector per arrival)
-            d2_out[i] = __float_as_uint(hex_d2(k, p.x, p.y, p.z, g.R, g.half_sqrt3, g.row_pitch));
-            oct_out[i] = (unsigned char)((p.x >= cg.tx ? 4u : 0u) | (p.y >= cg.ty ? 2u : 0u) | (p.z >= cg.tz ? 1u : 0u));
+            // what the contest needs of this point, by arrival position: ONE 8-byte record (d2, child octant) that
+            // stays L2-resident per cell, instead of a random 16-byte gather of the point itself (one DRAM sector per
+            // arrival).  One record = one L2 sector per gather; d2 and octant in separate arrays cost two.
+            d2oct_out[i] = make_uint2(__float_as_uint(hex_d2(k, p.x, p.y, p.z, g.R, g.half_sqrt3, g.row_pitch)),
+                                      (p.x >= cg.tx ? 4u : 0u) | (p.y >= cg.ty ? 2u : 0u) | (p.z >= cg.tz ? 1u : 0u));
             if (slot < slots) radix_hist_add(hist + slot * seg_words, plan, key, slot);
             else radix_hist_add_global(ghist + (u64)(seg_lo + slot) * seg_words, plan, key);
         }
@@ -540,8 +541,8 @@ struct ContestOp {
     u32 n;
     KeyLayout lay;
     LevelGeom g;
-    const u32* d2a;             // [n] by arrival position: d2 to the prism centre (hex.rs:55-65, cell.rs:77-78), from k_hexkey
-    const unsigned char* octa;  // [n] by arrival position: child octant (metadata.rs:100-102 one level down)
+    const uint2* d2oct;   // [n] by arrival position, from k_hexkey: .x = d2 to the prism centre (hex.rs:55-65, cell.rs:77-78),
+                          // .y = child octant (metadata.rs:100-102 one level down)
     const CellGeo* geo;
     u64* em;       // [n] by arrival position: loser's arrival position | octant << 32 | flags
     u32* win_src;  // [#groups] arrival position of each winner, sorted (cell, Z, Y, X)
@@ -584,8 +585,9 @@ struct ContestOp {
         u32 d2v[ITEMS], ocv[ITEMS];
 #pragma unroll
         for (int k = 0; k < ITEMS; k++) {
-            d2v[k] = (base + k < n) ? __ldg(d2a + pos[k]) : 0u;
-            ocv[k] = (base + k < n) ? (u32)__ldg(octa + pos[k]) : 0u;
+            const uint2 rec = (base + k < n) ? __ldg(d2oct + pos[k]) : make_uint2(0u, 0u);
+            d2v[k] = rec.x;
+            ocv[k] = rec.y;
         }
         // neighbours across the thread boundary
         u64 prevk = __shfl_up_sync(0xFFFFFFFFu, key[ITEMS - 1], 1);
