@@ -505,6 +505,11 @@ static LevelGeom make_geom(float max_cell_size, u32 dim, u32 h) {
     g.hexbits = g.bx + g.by + g.bz;
     g.half_sqrt3 = 1.73205080757f / 2.0f;          // hex.rs:60  SQRT_3 / 2.0
     g.row_pitch = (g.R * 3.0f) / 2.0f;             // hex.rs:61  cell_radius * 3.0 / 2.0
+    const volatile float dx = g.R * 1.73205080757f, dy = (-g.R) * 1.73205080757f;   // the f32 divisors of hex.rs:68-69
+    g.inv.x = 1.0 / (double)dx;
+    g.inv.y = 1.0 / (double)dy;
+    g.inv.z = 1.0 / (double)g.R;
+    g.inv.third = 1.0 / 3.0;
     return g;
 }
 

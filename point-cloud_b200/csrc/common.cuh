@@ -42,23 +42,43 @@ __device__ __forceinline__ i32 cell_index_axis(float p, float cell_size) {
     return sat_i32(floorf(__fdiv_rn(p, cell_size)));
 }
 
+// The reference divides every point by per-level constants (hex.rs:68-69, :79-80, :83; metadata.rs:101).  The IEEE
+// quotient a / b of two binary32 numbers equals  (float)((double)a * inv)  with inv = 1.0 / (double)b  computed once:
+// the double product is within 2^-52 (relative) of a / b, while a / b - unless exactly representable - stays at least
+// ~2^-49 (relative) away from every binary32 rounding boundary (a - m * b is a non-zero multiple of the last place of a
+// 49-bit product), and it never IS a midpoint (m * b would need 25 significant bits).  So one conversion, one DMUL
+// and one conversion replace the ~22-instruction __fdiv_rn sequence, bit for bit (checked exhaustively over all 2^32
+// dividends for b = 3.0 and the default grid's divisors, and on 4 * 10^8 random (a, b) pairs incl. overflow and
+// subnormal quotients: tests/test_div_identity.py).
+__device__ __forceinline__ float fdiv_inv(float a, double inv) { return __double2float_rn(__dmul_rn((double)a, inv)); }
+__device__ __forceinline__ i32 cell_index_axis_inv(float p, double inv_cell_size) {
+    return sat_i32(floorf(fdiv_inv(p, inv_cell_size)));
+}
+// reciprocals of the divisors of hex.rs:67-85 for one level
+struct HexInv {
+    double x;      // 1 / (R * SQRT_3)
+    double y;      // 1 / ((-R) * SQRT_3)
+    double z;      // 1 / R
+    double third;  // 1 / 3.0
+};
+
 struct HexKey {
     i32 x, y, z;
 };
 
 // hex.rs:67-85 followed by :45-51 (wrapping i32 arithmetic as in a Rust release build)
-__device__ __forceinline__ HexKey hex_from_world(float px, float py, float pz, float R) {
-    float x = __fdiv_rn(px, __fmul_rn(R, PCB_SQRT_3));
-    float y = __fdiv_rn(py, __fmul_rn(-R, PCB_SQRT_3));
+__device__ __forceinline__ HexKey hex_from_world(float px, float py, float pz, const HexInv& inv) {
+    float x = fdiv_inv(px, inv.x);   // px / (R * SQRT_3)
+    float y = fdiv_inv(py, inv.y);   // py / ((-R) * SQRT_3)
     float t = __fadd_rn(__fmul_rn(PCB_SQRT_3, y), 1.0f);
     float temp1 = floorf(__fadd_rn(t, x));
     float temp2 = __fsub_rn(t, x);
     float temp3 = __fadd_rn(__fmul_rn(2.0f, x), 1.0f);
-    float qf = __fdiv_rn(__fadd_rn(temp1, temp3), 3.0f);
-    float rf = __fdiv_rn(__fadd_rn(temp1, temp2), 3.0f);
+    float qf = fdiv_inv(__fadd_rn(temp1, temp3), inv.third);   // (temp1 + temp3) / 3.0
+    float rf = fdiv_inv(__fadd_rn(temp1, temp2), inv.third);
     i32 q = sat_i32(floorf(qf));
     i32 r = (i32)(0u - (u32)sat_i32(floorf(rf)));
-    i32 h = sat_i32(__fdiv_rn(pz, R));
+    i32 h = sat_i32(fdiv_inv(pz, inv.z));   // (pz / R) as i32: truncation
     i32 e = (i32)((u32)r - (u32)(r & 1));  // even => `/ 2` is exact
     HexKey k;
     k.x = (i32)((u32)q + (u32)(e / 2));

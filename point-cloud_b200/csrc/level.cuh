@@ -21,6 +21,7 @@ struct LevelGeom {
     int hexbits;    // bx + by + bz
     float half_sqrt3;  // SQRT_3 / 2.0          hex.rs:60 (loop-invariant sub-expressions, same single IEEE ops)
     float row_pitch;   // (R * 3.0) / 2.0       hex.rs:61
+    HexInv inv;        // reciprocals (double) of the level's divisors, see fdiv_inv
 };
 
 // per-cell constants of a level, one 32-byte record
@@ -50,6 +51,7 @@ __global__ void k_bbox_check(const PcbPoint* __restrict__ pts, u32 n, float S0, 
                              u32* __restrict__ err) {
     int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
     u32 bad = 0;
+    const double invS0 = 1.0 / (double)S0;
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
         PcbPoint p = pts[i];
         float v[3] = {p.x, p.y, p.z};
@@ -59,7 +61,7 @@ __global__ void k_bbox_check(const PcbPoint* __restrict__ pts, u32 n, float S0, 
             int o = f2ord(v[a]);
             mn[a] = min(mn[a], o);
             mx[a] = max(mx[a], o);
-            int ci = cell_index_axis(v[a], S0);
+            int ci = cell_index_axis_inv(v[a], invS0);
             if (ci < -(1 << 20) || ci >= (1 << 20)) bad |= PCB_DERR_L0RANGE;
         }
     }
@@ -98,10 +100,11 @@ struct L0Box {
     int ox, oy, oz;
     u32 nx, ny, nz;
 };
-__device__ __forceinline__ u64 l0_cell_id(const PcbPoint& p, float S0, const L0Box& b) {
-    u64 ix = (u64)(u32)(cell_index_axis(p.x, S0) - b.ox);
-    u64 iy = (u64)(u32)(cell_index_axis(p.y, S0) - b.oy);
-    u64 iz = (u64)(u32)(cell_index_axis(p.z, S0) - b.oz);
+// invS0 = 1.0 / (double)max_cell_size, once per thread (fdiv_inv: the reference's f32 division, bit for bit)
+__device__ __forceinline__ u64 l0_cell_id(const PcbPoint& p, double invS0, const L0Box& b) {
+    u64 ix = (u64)(u32)(cell_index_axis_inv(p.x, invS0) - b.ox);
+    u64 iy = (u64)(u32)(cell_index_axis_inv(p.y, invS0) - b.oy);
+    u64 iz = (u64)(u32)(cell_index_axis_inv(p.z, invS0) - b.oz);
     return (iz * b.ny + iy) * b.nx + ix;
 }
 __global__ void __launch_bounds__(256)
@@ -110,8 +113,9 @@ k_l0_key(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, int pb, R
     __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
     for (int i = threadIdx.x; i < plan.npass * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
     __syncthreads();
+    const double invS0 = 1.0 / (double)S0;
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
-        u64 k = l0_cell_id(pts[i], S0, box);
+        u64 k = l0_cell_id(pts[i], invS0, box);
         if (vals) vals[i] = (u32)i; else k = (k << pb) | i;
         keys[i] = k;
         radix_hist_add(hist, plan, k);
@@ -261,6 +265,7 @@ k_l0_split(const PcbPoint* __restrict__ in_pts, u32 n, float S0, L0Box box, u32 
     // warp-striped ownership: item k of lane l in warp w is element w * 32 * ITEMS + 32 k + l of the tile
     uint4 p[L0S_ITEMS];
     u32 dig[L0S_ITEMS];
+    const double invS0 = 1.0 / (double)S0;
     const u32 wbase = warp * 32 * L0S_ITEMS + lane;
     u32* wcnt = cnt + warp * nb;
 #pragma unroll
@@ -271,7 +276,7 @@ k_l0_split(const PcbPoint* __restrict__ in_pts, u32 n, float S0, L0Box box, u32 
             p[k] = __ldg((const uint4*)(in_pts + tbase + j));
             PcbPoint q;
             q.x = __uint_as_float(p[k].x); q.y = __uint_as_float(p[k].y); q.z = __uint_as_float(p[k].z); q.rgba = p[k].w;
-            dig[k] = (u32)l0_cell_id(q, S0, box);
+            dig[k] = (u32)l0_cell_id(q, invS0, box);
             atomicAdd(&wcnt[dig[k]], 1u);   // early counts (see k_onesweep)
         }
     }
@@ -424,7 +429,7 @@ __global__ void k_cellgeo(const int* __restrict__ cell_idx, const u32* __restric
     float x = __fmul_rn((float)ix, g.S);
     float y = __fmul_rn((float)iy, g.S);
     float z = __fmul_rn((float)iz, g.S);
-    HexKey k = hex_from_world(x, y, z, g.R);
+    HexKey k = hex_from_world(x, y, z, g.inv);
     CellGeo o;
     o.hx = k.x - g.mx; o.hy = k.y - g.my; o.hz = k.z - g.mz;
     o.start = cell_start[c];
@@ -485,7 +490,7 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
                 do cg = load_geo(geo, ++c); while (cg.end <= (u32)i);
                 slot = (c >> segk) - seg_lo;
             }
-            HexKey k = hex_from_world(p.x, p.y, p.z, g.R);
+            HexKey k = hex_from_world(p.x, p.y, p.z, g.inv);
             u32 rx = (u32)(k.x - cg.hx);
             u32 ry = (u32)(k.y - cg.hy);
             u32 rz = (u32)(k.z - cg.hz);

@@ -17,8 +17,9 @@ k_route_hist(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, u32 v
         for (u32 i = threadIdx.x; i < vol; i += blockDim.x) sh[i] = 0;
         __syncthreads();
     }
+    const double invS0 = 1.0 / (double)S0;
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
-        const u32 id = (u32)l0_cell_id(pts[i], S0, box);
+        const u32 id = (u32)l0_cell_id(pts[i], invS0, box);
         const u32 peers = __match_any_sync(__activemask(), id);       // random points hit few cells: aggregate
         if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u) {
             if (use_sh) atomicAdd(&sh[id], (u32)__popc(peers));
@@ -39,8 +40,9 @@ k_route_key(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, const 
     __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
     for (int i = threadIdx.x; i < plan.npass * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
     __syncthreads();
+    const double invS0 = 1.0 / (double)S0;
     for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
-        const u64 id = l0_cell_id(pts[i], S0, box);
+        const u64 id = l0_cell_id(pts[i], invS0, box);
         const u64 k = ((u64)__ldg(owner + id) << pb) | i;
         keys[i] = k;
         radix_hist_add(hist, plan, k);
@@ -145,6 +147,7 @@ k_route_split(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, cons
     const u64 wbase = (u64)tile * ROUTE_SPLIT_TILE + (u64)warp * (32 * ROUTE_SPLIT_ITEMS);
     const u32 lt = (1u << lane) - 1u;
     uint4 p[ROUTE_SPLIT_ITEMS];
+    const double invS0 = 1.0 / (double)S0;
     u32 code[ROUTE_SPLIT_ITEMS];   // owner | rank inside the warp << 4
     u32 wc[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // per-owner counts of this warp so far (same in every lane)
 #pragma unroll
@@ -155,7 +158,7 @@ k_route_split(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, cons
             p[k] = __ldg((const uint4*)(pts + e));
             PcbPoint q;
             q.x = __uint_as_float(p[k].x); q.y = __uint_as_float(p[k].y); q.z = __uint_as_float(p[k].z); q.rgba = p[k].w;
-            o = __ldg(owner + l0_cell_id(q, S0, box)) & 7u;
+            o = __ldg(owner + l0_cell_id(q, invS0, box)) & 7u;
         }
         const u32 peers = __match_any_sync(0xFFFFFFFFu, o);   // at most 9 distinct values
         u32 before = 0;
