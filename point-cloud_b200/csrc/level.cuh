@@ -540,6 +540,7 @@ template <bool PAIRS>
 struct ContestOp {
     typedef ContestState State;
     static constexpr bool kTileLoad = true;
+    static constexpr bool kOneWord = true;   // the 16-byte state and the status bits share one descriptor word
     static constexpr int ITEMS = 8;
     const u64* keys;
     const u32* vals;

@@ -197,6 +197,12 @@ __device__ __forceinline__ State ldcg_state(const State* p) {
 // memory transaction: no fence, no L1 invalidation, one volatile 16-byte load per word and poll.
 // Every Op supplies   static void pack(const State&, u32 status, uint4& a, uint4& b)   (status already
 // shifted: PCB_DESC_AGG / PCB_DESC_INCL OR-ed into a.w and b.w by pack) and   static State unpack(a, b).
+// An Op whose State fits the first word sets  static constexpr bool kOneWord = true;  the second word is then neither
+// stored nor polled.
+template <class Op, class = void>
+struct ChainOneWord { static constexpr bool value = false; };
+template <class Op>
+struct ChainOneWord<Op, decltype((void)Op::kOneWord)> { static constexpr bool value = Op::kOneWord; };
 #define PCB_DESC_AGG 0x40000000u
 #define PCB_DESC_INCL 0x80000000u
 #define PCB_DESC_MASK 0xC0000000u
@@ -220,7 +226,7 @@ __device__ __forceinline__ typename Op::State chain_lookback(const Op& op, uint4
         uint4 a, b;
         Op::pack(total, tile == 0 ? PCB_DESC_INCL : PCB_DESC_AGG, a, b);
         st_volatile_v4(desc + 2 * (u64)tile, a);
-        st_volatile_v4(desc + 2 * (u64)tile + 1, b);
+        if (!ChainOneWord<Op>::value) st_volatile_v4(desc + 2 * (u64)tile + 1, b);
     }
     State prefix = op.identity();
     if (tile > 0) {
@@ -233,7 +239,7 @@ __device__ __forceinline__ typename Op::State chain_lookback(const Op& op, uint4
                 uint4 a, b;
                 for (;;) {   // both words of one publication (a reader may catch the writer between its two stores)
                     a = ld_volatile_v4(desc + 2 * (u64)t);
-                    b = ld_volatile_v4(desc + 2 * (u64)t + 1);
+                    if (ChainOneWord<Op>::value) b = a; else b = ld_volatile_v4(desc + 2 * (u64)t + 1);
                     f = a.w & PCB_DESC_MASK;
                     if (f != 0u && f == (b.w & PCB_DESC_MASK)) break;
 #ifdef PCB_SPIN_BACKOFF
@@ -259,7 +265,7 @@ __device__ __forceinline__ typename Op::State chain_lookback(const Op& op, uint4
             uint4 a, b;
             Op::pack(op.combine(prefix, total), PCB_DESC_INCL, a, b);
             st_volatile_v4(desc + 2 * (u64)tile, a);
-            st_volatile_v4(desc + 2 * (u64)tile + 1, b);
+            if (!ChainOneWord<Op>::value) st_volatile_v4(desc + 2 * (u64)tile + 1, b);
         }
     }
     return prefix;
@@ -304,12 +310,15 @@ __global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 
     if (lane == 31) s_warp[warp] = winc;
     __syncthreads();
     State wpre = op.identity();   // warps before mine
-    State total = op.identity();  // whole tile
+    State total = op.identity();  // whole tile (only warp 0, which does the look-back, and the last thread need it)
+    if (warp == 0 || tid == THREADS - 1) {
 #pragma unroll
-    for (int w = 0; w < WARPS; w++) {
-        State sw = s_warp[w];
-        if (w < warp) wpre = op.combine(wpre, sw);
-        total = op.combine(total, sw);
+        for (int w = 0; w < WARPS; w++) total = op.combine(total, s_warp[w]);
+    }
+    if (warp > 0) {
+#pragma unroll
+        for (int w = 0; w < WARPS - 1; w++)
+            if (w < warp) wpre = op.combine(wpre, s_warp[w]);
     }
     State texcl = shfl_up_state(winc, 1);
     if (lane == 0) texcl = op.identity();
