@@ -977,7 +977,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                                                     tot.ncell_next);
     pe("cell_emit", 1, ncell, 300ull * ncell);
     pb();
-    k_loser_emit<<<div_up(n, 256), 256, 0, st>>>(em, rank, bat, n, cell_start, ncell, pts, bdst, next_pts, next_bat,
+    k_loser_emit<<<div_up(n, 256 * LOSER_ITEMS), 256, 0, st>>>(em, rank, bat, n, cell_start, ncell, pts, bdst, next_pts, next_bat,
                                                  img.d_image);
     pe("loser_emit", 1, n, 12ull * n + 40ull * (n - nwin));
     pb();

@@ -1119,27 +1119,50 @@ __global__ void k_cell_emit(const int* __restrict__ cell_idx, u32 ncell, u32 hie
 // Stage 8b: move every loser, in arrival (= emission) order: delivered to its child cell (next level's
 // arrivals, in (child, tau') order, with batch max(b_e, b_flush) — SURVEY N3) or kept in the parent's
 // overflow list (image).
+#define LOSER_ITEMS 4   // arrivals per thread: independent load chains (em -> bucket record -> point) in flight together
 __global__ void __launch_bounds__(256)
 k_loser_emit(const u64* __restrict__ em, const u32* __restrict__ rank, const u32* __restrict__ bat, u32 n,
              const u32* __restrict__ cell_start, u32 ncell, const PcbPoint* __restrict__ pts,
              const BucketDst* __restrict__ bdst, PcbPoint* __restrict__ next_pts, u32* __restrict__ next_bat,
              unsigned char* __restrict__ image) {
-    const u64 t0 = (u64)blockIdx.x * blockDim.x;
-    const u64 t = t0 + threadIdx.x;
-    if (t >= n) return;
-    const u64 e = em[t];
-    const u32 o = (u32)(e >> 32) & 0xFu;
-    if (o >= 8) return;
-    const u32 c = cell_of_arrival(cell_start, ncell, (u32)t, (u32)(t0 + (threadIdx.x & ~31u)));
-    const BucketDst d = bdst[8 * c + o];
-    const u32 r = (d.m0fl >> 2) + rank[t];
-    const uint4 p = *(const uint4*)(pts + (u32)e);
-    if (d.m0fl & PCB_BF_FLUSH) {
-        const u64 dst = d.base + r;
-        *(uint4*)(next_pts + dst) = p;
-        next_bat[dst] = max(bat[t], d.bfl);
-    } else {
-        store16_at1(image + d.base + 16ull * r, p);
+    const u64 b0 = (u64)blockIdx.x * (256 * LOSER_ITEMS);
+    u64 e[LOSER_ITEMS];
+    u32 rk[LOSER_ITEMS], bt[LOSER_ITEMS];
+#pragma unroll
+    for (int k = 0; k < LOSER_ITEMS; k++) {
+        const u64 t = b0 + 256 * k + threadIdx.x;
+        e[k] = (t < n) ? em[t] : ((u64)PCB_EM_NONE_OCT << 32);
+        rk[k] = (t < n) ? rank[t] : 0u;
+        bt[k] = (t < n) ? bat[t] : 0u;
+    }
+    BucketDst d[LOSER_ITEMS];
+    uint4 p[LOSER_ITEMS];
+    // cell of the arrival: one binary search per warp (its first arrival), then a walk (arrivals ascend with k)
+    u32 c = (b0 + (threadIdx.x & ~31u) < n) ? find_segment(cell_start, ncell, (u32)(b0 + (threadIdx.x & ~31u))) : 0u;
+#pragma unroll
+    for (int k = 0; k < LOSER_ITEMS; k++) {
+        const u64 t = b0 + 256 * k + threadIdx.x;
+        const u32 o = (u32)(e[k] >> 32) & 0xFu;
+        if (t < n)
+            while (__ldg(cell_start + c + 1) <= (u32)t) c++;
+        if (o < 8) {
+            d[k] = bdst[8 * c + o];
+            p[k] = *(const uint4*)(pts + (u32)e[k]);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < LOSER_ITEMS; k++) {
+        const u32 o = (u32)(e[k] >> 32) & 0xFu;
+        if (o < 8) {
+            const u32 r = (d[k].m0fl >> 2) + rk[k];
+            if (d[k].m0fl & PCB_BF_FLUSH) {
+                const u64 dst = d[k].base + r;
+                *(uint4*)(next_pts + dst) = p[k];
+                next_bat[dst] = max(bt[k], d[k].bfl);
+            } else {
+                store16_at1(image + d[k].base + 16ull * r, p[k]);
+            }
+        }
     }
 }
 
