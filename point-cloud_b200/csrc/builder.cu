@@ -981,7 +981,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                                                  img.d_image);
     pe("loser_emit", 1, n, 12ull * n + 40ull * (n - nwin));
     pb();
-    k_winner_emit<<<div_up(nwin, 256), 256, 0, st>>>(win_src, nwin, win_end, ncell, pts, node_off, img.d_image);
+    k_winner_emit<<<div_up(nwin, 256 * WINNER_ITEMS), 256, 0, st>>>(win_src, nwin, win_end, ncell, pts, node_off, img.d_image);
     pe("winner_emit", 1, nwin, 36ull * nwin);
     if (nex) {
         pb();

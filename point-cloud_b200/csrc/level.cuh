@@ -1167,20 +1167,41 @@ k_loser_emit(const u64* __restrict__ em, const u32* __restrict__ rank, const u32
 }
 
 // Stage 8c: grid section of every node: the winners, already in (cell, Z, Y, X) order.
-__global__ void k_winner_emit(const u32* __restrict__ win_src, u32 nwin, const u32* __restrict__ win_end, u32 ncell,
-                              const PcbPoint* __restrict__ pts, const u64* __restrict__ node_off,
-                              unsigned char* __restrict__ image) {
-    u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= nwin) return;
-    // cell = first c with win_end[c] > w
-    u32 lo = 0, hi = ncell;
-    while (lo < hi) {
-        u32 mid = (lo + hi) >> 1;
-        if (__ldg(win_end + mid) > (u32)w) hi = mid; else lo = mid + 1;
+#define WINNER_ITEMS 4
+__global__ void __launch_bounds__(256)
+k_winner_emit(const u32* __restrict__ win_src, u32 nwin, const u32* __restrict__ win_end, u32 ncell,
+              const PcbPoint* __restrict__ pts, const u64* __restrict__ node_off, unsigned char* __restrict__ image) {
+    const u64 b0 = (u64)blockIdx.x * (256 * WINNER_ITEMS);
+    u32 src[WINNER_ITEMS];
+#pragma unroll
+    for (int k = 0; k < WINNER_ITEMS; k++) {
+        const u64 w = b0 + 256 * k + threadIdx.x;
+        src[k] = (w < nwin) ? win_src[w] : 0u;
     }
-    const u32 c = lo;
-    const u32 wbeg = c ? __ldg(win_end + c - 1) : 0u;
-    *(uint4*)(image + node_off[c] + 48ull + 16ull * ((u32)w - wbeg)) = *(const uint4*)(pts + win_src[w]);
+    uint4 p[WINNER_ITEMS];
+#pragma unroll
+    for (int k = 0; k < WINNER_ITEMS; k++)
+        if (b0 + 256 * k + threadIdx.x < nwin) p[k] = *(const uint4*)(pts + src[k]);
+    // cell = first c with win_end[c] > w: one binary search per warp (its first winner), then a walk (w ascends with k)
+    const u64 wf = b0 + (threadIdx.x & ~31u);
+    u32 c = 0;
+    if (wf < nwin) {
+        u32 lo = 0, hi = ncell;
+        while (lo < hi) {
+            u32 mid = (lo + hi) >> 1;
+            if (__ldg(win_end + mid) > (u32)wf) hi = mid; else lo = mid + 1;
+        }
+        c = lo;
+    }
+#pragma unroll
+    for (int k = 0; k < WINNER_ITEMS; k++) {
+        const u64 w = b0 + 256 * k + threadIdx.x;
+        if (w < nwin) {
+            while (__ldg(win_end + c) <= (u32)w) c++;
+            const u32 wbeg = c ? __ldg(win_end + c - 1) : 0u;
+            *(uint4*)(image + node_off[c] + 48ull + 16ull * ((u32)w - wbeg)) = p[k];
+        }
+    }
 }
 
 // merge mode: the overflow lists that were already in the node files (front of each bucket)
