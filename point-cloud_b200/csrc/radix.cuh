@@ -35,7 +35,7 @@
 #define RADIX_FLAG_INCL 0x80000000u
 #define RADIX_COUNT_MASK 0x3FFFFFFFu
 #ifndef RADIX_WINDOW
-#define RADIX_WINDOW 8   // predecessors polled per look-back step (independent loads)
+#define RADIX_WINDOW 4   // predecessors polled per look-back step (independent loads); 8 and 16 measured slower with 256 bins
 #endif
 #ifdef PCB_RADIX_INSTR   // diagnostics: cycles per phase of a tile, summed over tiles (thread 0 of every block)
 __device__ unsigned long long g_radix_instr[16];
