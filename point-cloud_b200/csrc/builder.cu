@@ -171,7 +171,7 @@ struct Scratch {  // small device-resident results, mirrored in pinned host memo
     u32 err;
     u32 ncell;
     u32 nwin;
-    u32 pad;
+    u32 aux;   // record filter: number of early arrivals, then length of the round-2 key list
     int bbox[6];
     LevelTotals totals;
 };
@@ -252,6 +252,7 @@ class BuilderImpl {
     }
 
     ArenaSet* arenas = nullptr;
+    double last_mult = 0;   // arrivals per occupied prism on the level just built (same wave)
     int cur_arena = 0;
     void arena_prepare(int which, u64 bytes) {   // (re)size an arena; only while nothing of it is in use
         Arena& a = arenas->a[which];
@@ -852,82 +853,188 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     lay.hexbits = g.hexbits;
     lay.pb = PAIRS ? 0 : std::max(1, bits_count(n));
     if (lay.cb + lay.hexbits + lay.pb > 64) throw Error{PCB_ERR_RANGE, "too many cells on one level"};
-    // Arrivals come cell by cell, so the sort only has to order every cell's arrivals by prism: when the cell bits
-    // would cost extra passes, runs of 2^segk consecutive cells ("segments") are sorted independently inside the same
-    // launches and only segk cell bits take part (radix.cuh).  Taken when segments average >= PCB_SEG_MIN arrivals
-    // (tiles never straddle a segment: small segments mean partly filled tiles).
+    // ---- record filter (level.cuh): worth it when a prism sees many arrivals.  Level 0 of a big wave: assumed;
+    // deeper: predicted from the level above (the prisms shrink 4x in area, 8x in volume per level).
+    static const bool filter_off = getenv("PCB_NO_FILTER") != nullptr;                         // tuning / test hooks
+    static const int filter_force = getenv("PCB_FILTER_SHIFT") ? atoi(getenv("PCB_FILTER_SHIFT")) : -1;
+    u32 fshift = 0;   // early share of a cell = its first len >> fshift arrivals; 0 = no filter on this level
+    if (!PAIRS && !existing && !filter_off) {
+        const double m_pred = h == 0 ? 1e9 : last_mult / 4.0;
+        if (filter_force > 0) fshift = (u32)filter_force;
+        else if (n >= (1u << 21) && m_pred >= 16.0) fshift = m_pred >= 256.0 ? 4 : m_pred >= 64.0 ? 3 : 2;
+    }
+
+    CellGeo* geo = dalloc<CellGeo>(ncell);
+    uint2* d2oct = dalloc<uint2>(n);                 // contest inputs by arrival position, written by k_hexkey
+    u32* win_src = dalloc<u32>(n);
+    u32* win_end = dalloc<u32>(ncell);
+    const u64 tmp_bytes = std::max<u64>(chain_scan_temp_bytes<64, 8>(n), chain_scan_temp_bytes<256, 4>(ncell));
+    void* scan_tmp = dalloc<unsigned char>(tmp_bytes);
+    u64 *kA = nullptr, *kB = nullptr, *em = nullptr;
+    u32 *vA = nullptr, *vB = nullptr;
+    u32* rt_mem = nullptr;
+    uint4* tinfo = nullptr;
+    u32* seg_base = nullptr;
+    static const int contest_minb = getenv("PCB_CONTEST_MINB") ? atoi(getenv("PCB_CONTEST_MINB")) : 3;  // tuning hook
+    auto run_contest = [&](const ContestOp<PAIRS>& cop, u32 cnt) {
+        pb();
+        int nl = contest_minb == 4   ? chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, cnt, scan_tmp, st)
+                 : contest_minb == 6 ? chain_scan<ContestOp<PAIRS>, 128, 8, 6>(cop, cnt, scan_tmp, st)
+                 : contest_minb == 8 ? chain_scan<ContestOp<PAIRS>, 128, 8, 8>(cop, cnt, scan_tmp, st)
+                 : contest_minb == 12 ? chain_scan<ContestOp<PAIRS>, 64, 8, 12>(cop, cnt, scan_tmp, st)
+                                     : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, cnt, scan_tmp, st);
+        pe("contest", nl, cnt, (PAIRS ? 28ull : 24ull) * cnt);
+    };
+    // sort plan of `cnt` keys spread over the level's cells: segmented when the cell bits would cost extra passes
+    // (radix.cuh): runs of 2^segk consecutive cells are sorted independently inside the same launches.  Taken when
+    // segments average >= PCB_SEG_MIN keys (tiles never straddle a segment: small segments mean partly filled tiles).
     static const bool seg_off = getenv("PCB_NO_SEG") != nullptr;                                       // tuning / test hooks
     static const u64 seg_min = getenv("PCB_SEG_MIN") ? strtoull(getenv("PCB_SEG_MIN"), nullptr, 10) : 4ull * RADIX_TILE;
     int segk = 31;
     u32 nseg = 1;
-    {
+    auto plan_for = [&](u32 cnt) {
+        segk = 31;
+        nseg = 1;
         const int db = radix_digit_bits();
         const int top = div_up(lay.hexbits + 1, db) * db;   // room left in the top digit
         const int k = top - lay.hexbits;
         if (!seg_off && lay.cb > k && div_up(lay.hexbits + k, db) < div_up(lay.hexbits + lay.cb, db) &&
-            (u64)n >= seg_min * div_up(ncell, 1u << k)) {
+            (u64)cnt >= seg_min * div_up(ncell, 1u << k)) {
             segk = k;
             nseg = div_up(ncell, 1u << k);
         }
-    }
-    const RadixPlan plan = radix_plan(lay.pb, (nseg > 1 ? segk : lay.cb) + lay.hexbits);
-
-    // ---- stages 1-2: hex keys (+ the digit histograms of every pass)
-    CellGeo* geo = dalloc<CellGeo>(ncell);
-    u64 *kA = dalloc<u64>(n), *kB = dalloc<u64>(n);
-    u32 *vA = PAIRS ? dalloc<u32>(n) : nullptr, *vB = PAIRS ? dalloc<u32>(n) : nullptr;
-    RadixTemp rt;
-    const u64 hwords = nseg > 1 ? RadixTemp::ghist_words_seg(nseg, plan) : RadixTemp::ghist_words();
-    const u64 rwords = hwords + RadixTemp::status_words(n, plan, nseg > 1 ? nseg : 0);
-    rt.ghist = dalloc<u32>(rwords);
-    rt.status = rt.ghist + hwords;
-    CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
-    uint4* tinfo = nullptr;
-    u32* seg_base = nullptr;
-    if (nseg > 1) {
-        rt.nseg = nseg;
-        rt.ntiles_seg = (u32)RadixTemp::seg_tiles_bound(n, nseg);
-        tinfo = dalloc<uint4>(rt.ntiles_seg);
-        seg_base = dalloc<u32>(nseg + 1);
-        rt.tinfo = tinfo;
-    }
-    uint2* d2oct = dalloc<uint2>(n);                 // contest inputs by arrival position, written by k_hexkey
+        return radix_plan(lay.pb, (nseg > 1 ? segk : lay.cb) + lay.hexbits);
+    };
+    // radix scratch (histograms + look-back status) and, for a segmented sort, the tile table over `starts`
+    auto radix_setup = [&](RadixTemp& rt, const RadixPlan& plan, u32 cnt, const u32* starts) {
+        const u64 hwords = nseg > 1 ? RadixTemp::ghist_words_seg(nseg, plan) : RadixTemp::ghist_words();
+        const u64 rwords = hwords + RadixTemp::status_words(cnt, plan, nseg > 1 ? nseg : 0);
+        rt_mem = dalloc<u32>(rwords);
+        rt.ghist = rt_mem;
+        rt.status = rt.ghist + hwords;
+        CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
+        if (nseg > 1) {
+            rt.nseg = nseg;
+            rt.ntiles_seg = (u32)RadixTemp::seg_tiles_bound(cnt, nseg);
+            tinfo = dalloc<uint4>(rt.ntiles_seg);
+            seg_base = dalloc<u32>(nseg + 1);
+            rt.tinfo = tinfo;
+            k_seg_plan<<<1, 1024, 0, st>>>(starts, ncell, segk, nseg, seg_base);
+            k_seg_tiles<<<div_up(rt.ntiles_seg, 256), 256, 0, st>>>(starts, ncell, segk, seg_base, nseg, rt.ntiles_seg, tinfo);
+        }
+    };
+    const u32 hexgrid = std::min<u32>(148 * 8, div_up(n, 256));
     pb();
     k_cellgeo<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, cell_start, ncell, g, geo, &d_scr->err);
-    if (nseg > 1) {
-        k_seg_plan<<<1, 1024, 0, st>>>(cell_start, ncell, segk, nseg, seg_base);
-        k_seg_tiles<<<div_up(rt.ntiles_seg, 256), 256, 0, st>>>(cell_start, ncell, segk, seg_base, nseg, rt.ntiles_seg, tinfo);
+    pe("hexkey", 1, ncell, 60ull * ncell);
+
+    bool filtered = false;
+    if (fshift) {
+        // ---- round 1: the early arrivals of every cell
+        u32* estart = dalloc<u32>((u64)ncell + 1);
+        k_early_starts<<<1, 1024, 0, st>>>(cell_start, ncell, fshift, estart, &d_scr->aux);
+        fetch_scratch();
+        const u32 nE = h_scr->aux;
+        const RadixPlan plan = plan_for(nE);
+        kA = dalloc<u64>(n);   // keys by arrival position, later em
+        // candidate lists: one per warp of k_filter, each can hold every arrival that warp looks at
+        const u64 fchunk = (((u64)n + hexgrid - 1) / hexgrid + 255ull) & ~255ull;
+        const u32 nlists = hexgrid * 8, list_cap = (u32)(fchunk / 8);
+        kB = dalloc<u64>((u64)nlists * list_cap);
+        u64 *eA = dalloc<u64>(nE), *eB = dalloc<u64>(nE);
+        uint4* tails = dalloc<uint4>(nE);
+        RadixTemp rt;
+        pb();
+        radix_setup(rt, plan, nE, estart);
+        k_hexkey<PAIRS><<<hexgrid, 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay, plan, kA, vA, d2oct, rt.ghist, segk, nseg,
+                                                 estart, eA, &d_scr->err);
+        pe("hexkey", nseg > 1 ? 3 : 1, n, 32ull * n);
+        trace_mark(st, "hexkey", h, n);
+        int cur = radix_sort<PAIRS>(eA, nullptr, eB, nullptr, nE, plan, rt, st, *this);
+        em = kA;
+        run_contest(ContestOp<PAIRS>{cur ? eB : eA, nullptr, nE, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin,
+                                     &d_scr->err, tails, nullptr}, nE);
+        fetch_scratch();
+        check_err();
+        const u32 nwinE = h_scr->nwin;
+        trace_mark(st, "round1", h, nE);
+        // predicted round-2 list: early winners + one candidate per (early arrivals per prism + 1) later arrivals
+        const double s2_pred = nwinE + (double)(n - nE) / ((double)nE / std::max<u32>(nwinE, 1) + 1.0);
+        if (filter_force > 0 || s2_pred < 0.4 * n) {
+            // ---- filter: later arrivals against the early winners
+            FilterTable T;
+            u32 cap = 1024;
+            while (cap < 2ull * nwinE) cap <<= 1;
+            T.mask = cap - 1;
+            T.slots = dalloc<uint4>(cap);
+            CUDA_TRY(cudaMemsetAsync(T.slots, 0, 16ull * cap, st));
+            u32* ncand = dalloc<u32>(2ull * nlists);
+            u32* loff = ncand + nlists;
+            u64* wkeys = dalloc<u64>(std::max<u32>(nwinE, 1));
+            pb();
+            k_filter_table<<<std::min<u32>(148 * 8, div_up(std::max<u32>(nwinE, 1), 256)), 256, 0, st>>>(tails, &d_scr->nwin, T, lay.pb,
+                                                                                                wkeys);
+            k_filter<<<hexgrid, 256, 0, st>>>(kA, d2oct, n, cell_start, ncell, geo, estart, lay.pb, T, kB, ncand, em);
+            k_filter_offsets<<<1, 1024, 0, st>>>(ncand, nlists, loff, &d_scr->aux);
+            pe("filter", 3, n, 24ull * n);
+            fetch_scratch();
+            const u32 nS2 = nwinE + h_scr->aux;
+            trace_mark(st, "filter", h, nS2);
+            // ---- round 2: early winners + candidates, sorted on all key bits (the list is unordered)
+            dfree(rt_mem); dfree(tinfo); dfree(seg_base);
+            rt_mem = nullptr; tinfo = nullptr; seg_base = nullptr;
+            segk = 31;
+            nseg = 1;
+            const RadixPlan plan2 = radix_plan(0, lay.pb + lay.hexbits + lay.cb);
+            RadixTemp rt2;
+            u64 *s2A = dalloc<u64>(nS2), *s2B = dalloc<u64>(nS2);
+            pb();
+            radix_setup(rt2, plan2, nS2, nullptr);
+            CUDA_TRY(cudaMemcpyAsync(s2A, wkeys, 8ull * nwinE, cudaMemcpyDeviceToDevice, st));
+            k_filter_gather<<<nlists, 256, 0, st>>>(kB, list_cap, ncand, loff, &d_scr->nwin, s2A);
+            k_keys_hist<<<std::min<u32>(148 * 4, div_up(nS2, 256)), 256, 0, st>>>(s2A, nS2, plan2, rt2.ghist);
+            pe("filter", 3, nS2, 24ull * nS2);
+            cur = radix_sort<PAIRS>(s2A, nullptr, s2B, nullptr, nS2, plan2, rt2, st, *this);
+            run_contest(ContestOp<PAIRS>{cur ? s2B : s2A, nullptr, nS2, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin,
+                                         &d_scr->err, nullptr, estart}, nS2);
+            trace_mark(st, "round2", h, nS2);
+            dfree(s2A); dfree(s2B); dfree(T.slots); dfree(ncand); dfree(wkeys);
+            filtered = true;
+        } else {
+            dfree(kA); dfree(kB);
+            dfree(rt_mem); dfree(tinfo); dfree(seg_base);
+            kA = kB = nullptr; rt_mem = nullptr; tinfo = nullptr; seg_base = nullptr;
+        }
+        dfree(estart); dfree(eA); dfree(eB); dfree(tails);
     }
-    k_hexkey<PAIRS><<<std::min<u32>(148 * 8, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay,
-                                                                            plan, kA, vA, d2oct, rt.ghist, segk, nseg,
-                                                                            &d_scr->err);
-    pe("hexkey", nseg > 1 ? 4 : 2, n, (PAIRS ? 36ull : 32ull) * n);
-    trace_mark(st, "hexkey", h, n);
+    if (!filtered) {
+        // ---- stages 1-2: hex keys (+ the digit histograms of every pass)
+        const RadixPlan plan = plan_for(n);
+        kA = dalloc<u64>(n);
+        kB = dalloc<u64>(n);
+        vA = PAIRS ? dalloc<u32>(n) : nullptr;
+        vB = PAIRS ? dalloc<u32>(n) : nullptr;
+        RadixTemp rt;
+        pb();
+        radix_setup(rt, plan, n, cell_start);
+        k_hexkey<PAIRS><<<hexgrid, 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay, plan, kA, vA, d2oct, rt.ghist, segk, nseg,
+                                                 nullptr, nullptr, &d_scr->err);
+        pe("hexkey", nseg > 1 ? 3 : 1, n, (PAIRS ? 36ull : 32ull) * n);
+        trace_mark(st, "hexkey", h, n);
 
-    // ---- stage 3: stable sort by (cell, Z, Y, X)
-    int cur = radix_sort<PAIRS>(kA, vA, kB, vB, n, plan, rt, st, *this);
-    u64* ks = cur ? kB : kA;
-    u32* vs = cur ? vB : vA;
-    u64* em = cur ? kA : kB;   // the other key buffer is free now
-    trace_mark(st, "sort", h, n);
+        // ---- stage 3: stable sort by (cell, Z, Y, X)
+        int cur = radix_sort<PAIRS>(kA, vA, kB, vB, n, plan, rt, st, *this);
+        u64* ks = cur ? kB : kA;
+        u32* vs = cur ? vB : vA;
+        em = cur ? kA : kB;   // the other key buffer is free now
+        trace_mark(st, "sort", h, n);
 
-    // ---- stage 4: contest
-    u32* win_src = dalloc<u32>(n);
-    u32* win_end = dalloc<u32>(ncell);
-    const u64 tmp_bytes = std::max<u64>(std::max<u64>(chain_scan_temp_bytes<64, 8>(n),
-                                                      chain_scan_temp_bytes<64, 8>(n)),
-                                        chain_scan_temp_bytes<256, 4>(ncell));
-    void* scan_tmp = dalloc<unsigned char>(tmp_bytes);
-    ContestOp<PAIRS> cop{ks, vs, n, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err};
-    pb();
-    static const int contest_minb = getenv("PCB_CONTEST_MINB") ? atoi(getenv("PCB_CONTEST_MINB")) : 3;  // tuning hook
-    int nl = contest_minb == 4   ? chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, n, scan_tmp, st)
-             : contest_minb == 6 ? chain_scan<ContestOp<PAIRS>, 128, 8, 6>(cop, n, scan_tmp, st)
-             : contest_minb == 8 ? chain_scan<ContestOp<PAIRS>, 128, 8, 8>(cop, n, scan_tmp, st)
-             : contest_minb == 12 ? chain_scan<ContestOp<PAIRS>, 64, 8, 12>(cop, n, scan_tmp, st)
-                                 : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, n, scan_tmp, st);
-    pe("contest", nl, n, (PAIRS ? 28ull : 24ull) * n);
-    trace_mark(st, "contest", h, n);
+        // ---- stage 4: contest
+        run_contest(ContestOp<PAIRS>{ks, vs, n, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err, nullptr,
+                                     nullptr}, n);
+        trace_mark(st, "contest", h, n);
+    }
+    int nl = 0;
 
     // ---- stages 5-6: segmented 8-way split of the losers (ranks inside their (cell, octant) buckets)
     u32* rank = dalloc<u32>(n);
@@ -960,6 +1067,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     check_err();
     const LevelTotals tot = h_scr->totals;
     const u32 nwin = h_scr->nwin;
+    last_mult = (double)n / std::max<u32>(nwin, 1);   // arrivals per prism: predicts the next level's (record filter)
     trace_mark(st, "decide", h, ncell);
 
     // ---- stage 8: node images + next level's arrivals
@@ -1014,7 +1122,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     levels.push_back(img);
 
     // ---- hand over to the next level
-    dfree(geo); dfree(d2oct); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt.ghist); dfree(scan_tmp);
+    dfree(geo); dfree(d2oct); dfree(kA); dfree(kB); dfree(vA); dfree(vB); dfree(rt_mem); dfree(scan_tmp);
     dfree(tinfo); dfree(seg_base);
     dfree(win_src); dfree(win_end); dfree(rank); dfree(bcnt); dfree(special); dfree(bdst);
     dfree(cell_deliver); dfree(cell_children); dfree(cell_dbase); dfree(cell_cbase); dfree(cell_bytes); dfree(node_off);

@@ -463,7 +463,8 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
          const CellGeo* __restrict__ geo, LevelGeom g, KeyLayout lay, RadixPlan plan, u64* __restrict__ keys,
          u32* __restrict__ vals, uint2* __restrict__ d2oct_out,
          u32* __restrict__ ghist, int segk /* segment = cell >> segk (31: one segment) */, u32 nseg,
-         u32* __restrict__ err) {
+         const u32* __restrict__ estart /* record filter: first early arrival of every cell in keys_e, else null */,
+         u64* __restrict__ keys_e, u32* __restrict__ err) {
     __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
     for (int i = threadIdx.x; i < RADIX_MAX_PASSES * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
     __syncthreads();
@@ -477,10 +478,12 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
     CellGeo cg;
     cg.end = 0;
     u32 slot = 0;   // segment of cell c relative to the block's first segment (changes with the cell: rarely)
+    u32 ebase = 0, elen = 0xFFFFFFFFu;   // record filter: the cell's early arrivals go to keys_e[ebase ...), elen of them
     if (lo + threadIdx.x < hi) {
         c = find_segment(cell_start, ncell, (u32)(lo + threadIdx.x));
         cg = load_geo(geo, c);
         slot = (c >> segk) - seg_lo;
+        if (estart) { ebase = __ldg(estart + c); elen = __ldg(estart + c + 1) - ebase; }
     }
     for (u64 i0 = lo; i0 < hi; i0 += 256) {
         u64 i = i0 + threadIdx.x;
@@ -489,6 +492,7 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
             if (cg.end <= (u32)i) {
                 do cg = load_geo(geo, ++c); while (cg.end <= (u32)i);
                 slot = (c >> segk) - seg_lo;
+                if (estart) { ebase = __ldg(estart + c); elen = __ldg(estart + c + 1) - ebase; }
             }
             HexKey k = hex_from_world(p.x, p.y, p.z, g.inv);
             u32 rx = (u32)(k.x - cg.hx);
@@ -510,8 +514,12 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
             // arrival).  One record = one L2 sector per gather; d2 and octant in separate arrays cost two.
             d2oct_out[i] = make_uint2(__float_as_uint(hex_d2(k, p.x, p.y, p.z, g.R, g.half_sqrt3, g.row_pitch)),
                                       (p.x >= cg.tx ? 4u : 0u) | (p.y >= cg.ty ? 2u : 0u) | (p.z >= cg.tz ? 1u : 0u));
-            if (slot < slots) radix_hist_add(hist + slot * seg_words, plan, key, slot);
-            else radix_hist_add_global(ghist + (u64)(seg_lo + slot) * seg_words, plan, key);
+            const u32 rel = (u32)i - cg.start;
+            if (rel < elen) {   // every arrival without the record filter, else the early ones: these get sorted
+                if (estart) keys_e[ebase + rel] = key;
+                if (slot < slots) radix_hist_add(hist + slot * seg_words, plan, key, slot);
+                else radix_hist_add_global(ghist + (u64)(seg_lo + slot) * seg_words, plan, key);
+            }
         }
     }
     for (int o = 16; o; o >>= 1) bad |= __shfl_xor_sync(0xFFFFFFFFu, bad, o);
@@ -555,6 +563,11 @@ struct ContestOp {
     u32* win_end;  // [ncell] end of the cell's winners in win_src
     u32* nwin_out;
     u32* err;
+    // record filter (both null otherwise).  Round 1 (early arrivals): tails[w] = {group id, d2 bits, position} of
+    // winner w.  Round 2 (early winners + candidates): estart != null, elements that are early arrivals are the
+    // incumbents of their groups - their own emission was decided in round 1 and is not touched.
+    uint4* tails;
+    const u32* estart;
     __device__ static void pack(const State& s, u32 status, uint4& a, uint4& b) {
         a = make_uint4((u32)s.mn, (u32)(s.mn >> 32), s.meta, s.ntail | status);   // ntail < 2^30
         b = make_uint4(0u, 0u, 0u, status);
@@ -648,14 +661,197 @@ struct ContestOp {
         } else {
             e = ((u64)(self.meta & 0xFu) << 32) | pos;
         }
-        if (self.meta & 0x200u) win_src[excl.ntail] = (u32)incl.mn;
+        if (self.meta & 0x200u) {
+            win_src[excl.ntail] = (u32)incl.mn;
+            if (tails) {
+                const u64 G = gid(keys[j]);
+                tails[excl.ntail] = make_uint4((u32)G, (u32)(G >> 32), (u32)(incl.mn >> 32), (u32)incl.mn);
+            }
+        }
         if (self.meta & 0x400u) win_end[(u32)(gid(keys[j]) >> g.hexbits)] = excl.ntail + 1;
         if (self.meta & 0x800u) e |= PCB_EM_CELL_FIRST;
         if (self.meta & 0x1000u) e |= PCB_EM_CELL_LAST;
+        if (estart) {
+            const u32 c = (u32)(gid(keys[j]) >> g.hexbits);
+            if (pos - __ldg(&geo[c].start) < __ldg(estart + c + 1) - __ldg(estart + c)) return;   // incumbent
+        }
         em[pos] = e;
     }
     __device__ void finish(const State& total) const { *nwin_out = total.ntail; }
 };
+
+// ---- record filter ---------------------------------------------------------------------------------------------------
+// On the upper levels a prism receives hundreds of arrivals and all but a handful of them lose to an incumbent
+// that arrived long before (cell.rs:80: only an arrival with a strictly smaller d2 than everything before it - a
+// RECORD - changes the grid).  An arrival that is not a record emits itself, and that needs no sort.  So a level is
+// built in two rounds:
+//   round 1: the EARLY arrivals of every cell (its first share, in arrival order) go through sort + contest as
+//            usual; the winners so far (prism, d2) are put into a hash table;
+//   filter : every later arrival looks its prism up: d2 >= the table's d2 means an earlier arrival is at least as
+//            close, so it is no record and emits itself (coalesced store, done).  The others - CANDIDATES, a few
+//            per cent - may be records;
+//   round 2: early winners + candidates go through sort + contest.  Every true record is an early arrival or a
+//            candidate, the incumbent seen by a candidate is always a record, so the running minima over this subset
+//            are the true ones: emissions and final winners are exactly those of the full contest.
+struct FilterTable {
+    uint4* slots;   // {group id + 1 (lo, hi), d2 bits, -}; id 0 = empty; linear probing
+    u32 mask;       // capacity - 1 (power of two)
+};
+__device__ __forceinline__ u32 filter_hash(u64 gid, u32 mask) {
+    return (u32)((gid * 0x9E3779B97F4A7C15ull) >> 32) & mask;
+}
+// winners of round 1 -> table + their keys (dense list, one per winner)
+__global__ void k_filter_table(const uint4* __restrict__ tails, const u32* __restrict__ nwin_ptr, FilterTable T, int pb,
+                               u64* __restrict__ wkeys) {
+    const u32 nwin = *nwin_ptr;
+    for (u32 w = blockIdx.x * blockDim.x + threadIdx.x; w < nwin; w += gridDim.x * blockDim.x) {
+        const uint4 t = tails[w];
+        const u64 gid = ((u64)t.y << 32) | t.x;
+        u32 h = filter_hash(gid, T.mask);
+        for (;;) {
+            unsigned long long* idp = (unsigned long long*)(T.slots + h);
+            const unsigned long long old = atomicCAS(idp, 0ull, gid + 1ull);
+            if (old == 0ull) {
+                ((u32*)(T.slots + h))[2] = t.z;
+                break;
+            }
+            h = (h + 1u) & T.mask;   // group ids are distinct: never an update
+        }
+        wkeys[w] = (gid << pb) | t.w;
+    }
+}
+// Candidates are appended to one private list per WARP of k_filter (capacity = the arrivals that warp looks at, so
+// the lists tile one buffer of ~n keys): no atomics at all.  One shared counter, even 128 of them, serialised
+// millions of atomics on a few L2 lines and cost 1.5-2 ms per level.
+// every arrival behind the early share of its cell: no record -> emits itself; else candidate for round 2
+__global__ void __launch_bounds__(256)
+k_filter(const u64* keys /* by arrival position; aliases em */, const uint2* __restrict__ d2oct, u32 n,
+         const u32* __restrict__ cell_start, u32 ncell, const CellGeo* __restrict__ geo, const u32* __restrict__ estart,
+         int pb, FilterTable T, u64* __restrict__ cand_lists /* [gridDim.x * 8] lists of chunk / 8 keys */,
+         u32* __restrict__ ncand /* [gridDim.x * 8] */, u64* em) {
+    const u64 chunk = (((u64)n + gridDim.x - 1) / gridDim.x + 255ull) & ~255ull;
+    const u64 lo = (u64)blockIdx.x * chunk, hi = min((u64)n, lo + chunk);
+    const u32 list_id = blockIdx.x * 8u + (threadIdx.x >> 5);
+    u64* const list = cand_lists + (u64)list_id * (chunk / 8);
+    u32 filled = 0;   // keys in this warp's list (same in every lane)
+    u32 c = 0, elen = 0;
+    CellGeo cg;
+    cg.start = cg.end = 0;
+    if (lo + threadIdx.x < hi) {
+        c = find_segment(cell_start, ncell, (u32)(lo + threadIdx.x));
+        cg = load_geo(geo, c);
+        elen = __ldg(estart + c + 1) - __ldg(estart + c);
+    }
+    const int lane = threadIdx.x & 31;
+    for (u64 i0 = lo; i0 < hi; i0 += 256) {
+        const u64 i = i0 + threadIdx.x;
+        bool cand = false;
+        u64 key = 0;
+        if (i < hi) {
+            if (cg.end <= (u32)i) {
+                do cg = load_geo(geo, ++c); while (cg.end <= (u32)i);
+                elen = __ldg(estart + c + 1) - __ldg(estart + c);
+            }
+            if ((u32)i - cg.start >= elen) {
+                key = keys[i];
+                const uint2 rec = d2oct[i];
+                const u64 gid = key >> pb;
+                u32 h = filter_hash(gid, T.mask);
+                cand = true;
+                for (;;) {
+                    const uint4 s = __ldg(T.slots + h);
+                    const u64 id = ((u64)s.y << 32) | s.x;
+                    if (id == 0ull) break;                       // prism not seen among the early arrivals
+                    if (id == gid + 1ull) {
+                        cand = rec.x < s.z;                       // cell.rs:80 strict <; an equal d2 keeps the earlier arrival
+                        break;
+                    }
+                    h = (h + 1u) & T.mask;
+                }
+                if (!cand)
+                    em[i] = ((u64)rec.y << 32) | (u32)i | (cg.end == (u32)i + 1u ? PCB_EM_CELL_LAST : 0ull);
+            }
+        }
+        const u32 m = __ballot_sync(0xFFFFFFFFu, cand);
+        if (cand) list[filled + __popc(m & ((1u << lane) - 1u))] = key;
+        filled += (u32)__popc(m);
+    }
+    if (lane == 0) ncand[list_id] = filled;
+}
+// exclusive prefix of the candidate-list lengths (one block); *total = number of candidates
+__global__ void __launch_bounds__(1024) k_filter_offsets(const u32* __restrict__ ncand, u32 nlists, u32* __restrict__ loff,
+                                                         u32* __restrict__ total) {
+    __shared__ u32 sh[1024];
+    const u32 per = (nlists + 1023u) / 1024u;
+    const u32 lo = min(nlists, threadIdx.x * per), hi = min(nlists, lo + per);
+    u32 acc = 0;
+    for (u32 c = lo; c < hi; c++) acc += ncand[c];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        u32 v = threadIdx.x >= (u32)d ? sh[threadIdx.x - d] : 0u;
+        __syncthreads();
+        sh[threadIdx.x] += v;
+        __syncthreads();
+    }
+    u32 run = sh[threadIdx.x] - acc;
+    for (u32 c = lo; c < hi; c++) {
+        loff[c] = run;
+        run += ncand[c];
+    }
+    if (threadIdx.x == 1023) *total = sh[1023];
+}
+// round-2 key list = early winners, then the candidate lists back to back (one block per list)
+__global__ void __launch_bounds__(256)
+k_filter_gather(const u64* __restrict__ cand_lists, u32 list_cap, const u32* __restrict__ ncand, const u32* __restrict__ loff,
+                const u32* __restrict__ nwin_ptr, u64* __restrict__ out) {
+    const u64* in = cand_lists + (u64)blockIdx.x * list_cap;
+    const u32 cnt = ncand[blockIdx.x];
+    u64* dst = out + *nwin_ptr + loff[blockIdx.x];
+    for (u32 i = threadIdx.x; i < cnt; i += blockDim.x) dst[i] = in[i];
+}
+// digit histograms of all passes for a key list that no kernel of ours produced in order
+__global__ void __launch_bounds__(256)
+k_keys_hist(const u64* __restrict__ keys, u32 n, RadixPlan plan, u32* __restrict__ ghist) {
+    __shared__ u32 hist[RADIX_MAX_PASSES * RADIX_MAX_BINS];
+    for (int i = threadIdx.x; i < RADIX_MAX_PASSES * RADIX_MAX_BINS; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
+        const u64 key = keys[i];
+#pragma unroll 1
+        for (int p = 0; p < plan.npass; p++)
+            atomicAdd(&hist[p * RADIX_MAX_BINS + ((u32)(key >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u))], 1u);
+    }
+    __syncthreads();
+    radix_hist_flush(hist, plan, ghist);
+}
+// early share of every cell (its first max(1, len >> shift) arrivals): estart[c] = first slot of cell c in the early
+// key list, estart[ncell] = *total = number of early arrivals.  One block.
+__global__ void __launch_bounds__(1024) k_early_starts(const u32* __restrict__ cell_start, u32 ncell, u32 shift,
+                                                       u32* __restrict__ estart, u32* __restrict__ total) {
+    __shared__ u32 sh[1024];
+    const u32 per = (ncell + 1023u) / 1024u;
+    const u32 lo = min(ncell, threadIdx.x * per), hi = min(ncell, lo + per);
+    u32 acc = 0;
+    for (u32 c = lo; c < hi; c++) acc += max(1u, (cell_start[c + 1] - cell_start[c]) >> shift);
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        u32 v = threadIdx.x >= (u32)d ? sh[threadIdx.x - d] : 0u;
+        __syncthreads();
+        sh[threadIdx.x] += v;
+        __syncthreads();
+    }
+    u32 run = sh[threadIdx.x] - acc;
+    for (u32 c = lo; c < hi; c++) {
+        estart[c] = run;
+        run += max(1u, (cell_start[c + 1] - cell_start[c]) >> shift);
+    }
+    if (threadIdx.x == 1023) {
+        estart[ncell] = sh[1023];
+        *total = sh[1023];
+    }
+}
 
 // Stage 6: segmented stable 8-way split of the losers by child octant.  One scan over arrival positions,
 // restarting at every cell, with eight running counters gives every loser its rank inside its

@@ -184,6 +184,38 @@ def test_segmented_sort_forced():
         assert r.returncode == 0 and "seg ok" in r.stdout, r.stdout + r.stderr
 
 
+def test_record_filter_forced():
+    """Record filter (level.cuh): a level is built from the early arrivals of every cell, a hash-table filter over
+    the later ones and a second contest over early winners + candidates.  Forced on every level of small inputs
+    (PCB_FILTER_SHIFT = early share 1/2, 1/4, 1/16; fresh processes): duplicate- and tie-heavy clouds, many cells,
+    tiny cells (early share of one arrival), multi-file runs, with and without forced segmentation."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "import numpy as np\n"
+        "from pcutil import compare_trees, load_pcb, make_points, oracle_convert\n"
+        "rng = np.random.default_rng(47)\n"
+        "clouds = []\n"
+        "for cfg, bs, n, ext in (((100, 8, 10.0), 1000, 80000, 30), ((5000, 96, 1000.0), 10000, 300000, 3000),\n"
+        "                        ((20, 96, 4.0), 5000, 120000, 20), ((300, 20, 16.0), 2000, 250000, 100)):\n"
+        "    clouds.append((cfg, bs, [make_points(rng.random((n, 3)) * [ext, ext, ext / 4] - [ext / 2, ext / 2, ext / 8])]))\n"
+        "dup = np.round(rng.random((20000, 3)) * 12, 0) / 2\n"   # few distinct positions: ties and exact duplicates
+        "clouds.append(((50, 8, 8.0), 700, [make_points(dup), make_points(dup[::-1].copy()), make_points(rng.random((5000, 3)) * 6)]))\n"
+        "for cfg, bs, files in clouds:\n"
+        "    o = oracle_convert(files, config=cfg, batch_size=bs)\n"
+        "    nodes, mj, st, _ = load_pcb().convert(files, config=cfg, batch_size=bs)\n"
+        "    assert st.arrivals == o.arrivals and st.hierarchies == o.hierarchies\n"
+        "    compare_trees(o.nodes, nodes, 'oracle', 'gpu-filter')\n"
+        "    assert mj == o.meta_json and all(o.nodes[k] == nodes[k] for k in nodes)\n"
+        "print('filter ok')\n") % os.path.dirname(os.path.abspath(__file__))
+    for extra in ({"PCB_FILTER_SHIFT": "1"}, {"PCB_FILTER_SHIFT": "2", "PCB_SEG_MIN": "1"}, {"PCB_FILTER_SHIFT": "4"}):
+        env = dict(os.environ, **extra)
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0 and "filter ok" in r.stdout, str(extra) + r.stdout[-2000:] + r.stderr[-3000:]
+
+
 def test_waves_of_level0_cells_forced():
     """The forest is built a group of level-0 cells ("wave") at a time.  Tiny waves (PCB_WAVE_POINTS, fresh
     process) must give the same trees as the oracle: many roots incl. negative cells, the default config, and a
