@@ -858,10 +858,11 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     static const bool filter_off = getenv("PCB_NO_FILTER") != nullptr;                         // tuning / test hooks
     static const int filter_force = getenv("PCB_FILTER_SHIFT") ? atoi(getenv("PCB_FILTER_SHIFT")) : -1;
     u32 fshift = 0;   // early share of a cell = its first len >> fshift arrivals; 0 = no filter on this level
-    if (!PAIRS && !existing && !filter_off) {
+    static const double filter_min = getenv("PCB_FILTER_MIN") ? atof(getenv("PCB_FILTER_MIN")) : 64.0;
+    if (!PAIRS && !existing && !filter_off && lay.cb + lay.hexbits < FILTER_GID_BITS) {
         const double m_pred = h == 0 ? 1e9 : last_mult / 4.0;
         if (filter_force > 0) fshift = (u32)filter_force;
-        else if (n >= (1u << 21) && m_pred >= 16.0) fshift = m_pred >= 256.0 ? 4 : m_pred >= 64.0 ? 3 : 2;
+        else if (n >= (1u << 21) && m_pred >= filter_min) fshift = m_pred >= 256.0 ? 4 : m_pred >= 64.0 ? 3 : 2;
     }
 
     CellGeo* geo = dalloc<CellGeo>(ncell);
@@ -964,10 +965,12 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
             // ---- filter: later arrivals against the early winners
             FilterTable T;
             u32 cap = 1024;
-            while (cap < 2ull * nwinE) cap <<= 1;
+            int capbits = 10;
+            while (cap < 3ull * nwinE) { cap <<= 1; capbits++; }   // load factor 1/6 .. 1/3
             T.mask = cap - 1;
-            T.slots = dalloc<uint4>(cap);
-            CUDA_TRY(cudaMemsetAsync(T.slots, 0, 16ull * cap, st));
+            T.shift = 64 - capbits;
+            T.slots = dalloc<unsigned long long>(cap);
+            CUDA_TRY(cudaMemsetAsync(T.slots, 0, 8ull * cap, st));
             u32* ncand = dalloc<u32>(2ull * nlists);
             u32* loff = ncand + nlists;
             u64* wkeys = dalloc<u64>(std::max<u32>(nwinE, 1));

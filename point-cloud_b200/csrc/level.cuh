@@ -693,12 +693,17 @@ struct ContestOp {
 //   round 2: early winners + candidates go through sort + contest.  Every true record is an early arrival or a
 //            candidate, the incumbent seen by a candidate is always a record, so the running minima over this subset
 //            are the true ones: emissions and final winners are exactly those of the full contest.
+// One 8-byte slot per early winner: (group id + 1) << 24 | ceil(d2 bits / 256); 0 = empty; linear probing.  The 24-bit
+// bound is rounded UP, so "arrival's d2 bits >> 8 >= bound" still proves d2 >= the early winner's d2 (a few more
+// candidates, never a missed record).  Group ids need 40 bits (cell + prism bits; the filter is off beyond that).
+#define FILTER_GID_BITS 40
 struct FilterTable {
-    uint4* slots;   // {group id + 1 (lo, hi), d2 bits, -}; id 0 = empty; linear probing
-    u32 mask;       // capacity - 1 (power of two)
+    unsigned long long* slots;
+    u32 mask;    // capacity - 1 (power of two)
+    int shift;   // 64 - log2(capacity): Fibonacci hashing takes the top bits of the product
 };
-__device__ __forceinline__ u32 filter_hash(u64 gid, u32 mask) {
-    return (u32)((gid * 0x9E3779B97F4A7C15ull) >> 32) & mask;
+__device__ __forceinline__ u32 filter_hash(u64 gid, const FilterTable& T) {
+    return (u32)((gid * 0x9E3779B97F4A7C15ull) >> T.shift);
 }
 // winners of round 1 -> table + their keys (dense list, one per winner)
 __global__ void k_filter_table(const uint4* __restrict__ tails, const u32* __restrict__ nwin_ptr, FilterTable T, int pb,
@@ -707,16 +712,9 @@ __global__ void k_filter_table(const uint4* __restrict__ tails, const u32* __res
     for (u32 w = blockIdx.x * blockDim.x + threadIdx.x; w < nwin; w += gridDim.x * blockDim.x) {
         const uint4 t = tails[w];
         const u64 gid = ((u64)t.y << 32) | t.x;
-        u32 h = filter_hash(gid, T.mask);
-        for (;;) {
-            unsigned long long* idp = (unsigned long long*)(T.slots + h);
-            const unsigned long long old = atomicCAS(idp, 0ull, gid + 1ull);
-            if (old == 0ull) {
-                ((u32*)(T.slots + h))[2] = t.z;
-                break;
-            }
-            h = (h + 1u) & T.mask;   // group ids are distinct: never an update
-        }
+        const unsigned long long entry = ((gid + 1ull) << 24) | (unsigned long long)((t.z + 0xFFu) >> 8);
+        u32 h = filter_hash(gid, T);
+        while (atomicCAS(T.slots + h, 0ull, entry) != 0ull) h = (h + 1u) & T.mask;   // group ids are distinct: never an update
         wkeys[w] = (gid << pb) | t.w;
     }
 }
@@ -756,14 +754,14 @@ k_filter(const u64* keys /* by arrival position; aliases em */, const uint2* __r
                 key = keys[i];
                 const uint2 rec = d2oct[i];
                 const u64 gid = key >> pb;
-                u32 h = filter_hash(gid, T.mask);
+                u32 h = filter_hash(gid, T);
                 cand = true;
                 for (;;) {
-                    const uint4 s = __ldg(T.slots + h);
-                    const u64 id = ((u64)s.y << 32) | s.x;
-                    if (id == 0ull) break;                       // prism not seen among the early arrivals
-                    if (id == gid + 1ull) {
-                        cand = rec.x < s.z;                       // cell.rs:80 strict <; an equal d2 keeps the earlier arrival
+                    const unsigned long long s = __ldg(T.slots + h);
+                    if (s == 0ull) break;                        // prism not seen among the early arrivals
+                    if ((s >> 24) == gid + 1ull) {
+                        // cell.rs:80: only a strictly smaller d2 displaces; d2 >= the (rounded-up) early minimum: no record
+                        cand = (rec.x >> 8) < (u32)(s & 0xFFFFFFull);
                         break;
                     }
                     h = (h + 1u) & T.mask;
