@@ -983,12 +983,12 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
             fetch_scratch();
             const u32 nS2 = nwinE + h_scr->aux;
             trace_mark(st, "filter", h, nS2);
-            // ---- round 2: early winners + candidates, sorted on all key bits (the list is unordered)
+            // ---- round 2: early winners, then the candidates in arrival order: stable sort on the cell + prism bits
             dfree(rt_mem); dfree(tinfo); dfree(seg_base);
             rt_mem = nullptr; tinfo = nullptr; seg_base = nullptr;
             segk = 31;
             nseg = 1;
-            const RadixPlan plan2 = radix_plan(0, lay.pb + lay.hexbits + lay.cb);
+            const RadixPlan plan2 = radix_plan(lay.pb, lay.hexbits + lay.cb);
             RadixTemp rt2;
             u64 *s2A = dalloc<u64>(nS2), *s2B = dalloc<u64>(nS2);
             pb();

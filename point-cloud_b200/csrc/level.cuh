@@ -720,7 +720,9 @@ __global__ void k_filter_table(const uint4* __restrict__ tails, const u32* __res
 }
 // Candidates are appended to one private list per WARP of k_filter (capacity = the arrivals that warp looks at, so
 // the lists tile one buffer of ~n keys): no atomics at all.  One shared counter, even 128 of them, serialised
-// millions of atomics on a few L2 lines and cost 1.5-2 ms per level.
+// millions of atomics on a few L2 lines and cost 1.5-2 ms per level.  Every warp owns a CONTIGUOUS range of arrivals,
+// so the lists back to back hold the candidates in arrival order: the round-2 list (early winners first, then the
+// candidates) only needs a stable sort on the cell and prism bits, like any level.
 // every arrival behind the early share of its cell: no record -> emits itself; else candidate for round 2
 __global__ void __launch_bounds__(256)
 k_filter(const u64* keys /* by arrival position; aliases em */, const uint2* __restrict__ d2oct, u32 n,
@@ -732,20 +734,21 @@ k_filter(const u64* keys /* by arrival position; aliases em */, const uint2* __r
     const u32 list_id = blockIdx.x * 8u + (threadIdx.x >> 5);
     u64* const list = cand_lists + (u64)list_id * (chunk / 8);
     u32 filled = 0;   // keys in this warp's list (same in every lane)
+    const int lane = threadIdx.x & 31;
+    const u64 wlo = lo + (u64)(threadIdx.x >> 5) * (chunk / 8), whi = min(hi, wlo + chunk / 8);   // this warp's arrivals
     u32 c = 0, elen = 0;
     CellGeo cg;
     cg.start = cg.end = 0;
-    if (lo + threadIdx.x < hi) {
-        c = find_segment(cell_start, ncell, (u32)(lo + threadIdx.x));
+    if (wlo + lane < whi) {
+        c = find_segment(cell_start, ncell, (u32)(wlo + lane));
         cg = load_geo(geo, c);
         elen = __ldg(estart + c + 1) - __ldg(estart + c);
     }
-    const int lane = threadIdx.x & 31;
-    for (u64 i0 = lo; i0 < hi; i0 += 256) {
-        const u64 i = i0 + threadIdx.x;
+    for (u64 i0 = wlo; i0 < whi; i0 += 32) {
+        const u64 i = i0 + lane;
         bool cand = false;
         u64 key = 0;
-        if (i < hi) {
+        if (i < whi) {
             if (cg.end <= (u32)i) {
                 do cg = load_geo(geo, ++c); while (cg.end <= (u32)i);
                 elen = __ldg(estart + c + 1) - __ldg(estart + c);
