@@ -210,7 +210,9 @@ def test_record_filter_forced():
         "    compare_trees(o.nodes, nodes, 'oracle', 'gpu-filter')\n"
         "    assert mj == o.meta_json and all(o.nodes[k] == nodes[k] for k in nodes)\n"
         "print('filter ok')\n") % os.path.dirname(os.path.abspath(__file__))
-    for extra in ({"PCB_FILTER_SHIFT": "1"}, {"PCB_FILTER_SHIFT": "2", "PCB_SEG_MIN": "1"}, {"PCB_FILTER_SHIFT": "4"}):
+    # the last one gives the filter up after round 1 (too many predicted candidates) and falls back to the full sort
+    for extra in ({"PCB_FILTER_SHIFT": "1"}, {"PCB_FILTER_SHIFT": "2", "PCB_SEG_MIN": "1"}, {"PCB_FILTER_SHIFT": "4"},
+                  {"PCB_FILTER_SHIFT": "3", "PCB_FILTER_BAIL": "1"}):
         env = dict(os.environ, **extra)
         r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and "filter ok" in r.stdout, str(extra) + r.stdout[-2000:] + r.stderr[-3000:]
