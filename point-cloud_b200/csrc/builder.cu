@@ -877,13 +877,14 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     uint4* tinfo = nullptr;
     u32* seg_base = nullptr;
     static const int contest_minb = getenv("PCB_CONTEST_MINB") ? atoi(getenv("PCB_CONTEST_MINB")) : 3;  // tuning hook
-    auto run_contest = [&](const ContestOp<PAIRS>& cop, u32 cnt) {
+    auto run_contest = [&](const ContestOp<PAIRS>& cop, u32 cnt) {   // cnt: upper bound when cop.n_dev is set
         pb();
-        int nl = contest_minb == 4   ? chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, cnt, scan_tmp, st)
-                 : contest_minb == 6 ? chain_scan<ContestOp<PAIRS>, 128, 8, 6>(cop, cnt, scan_tmp, st)
-                 : contest_minb == 8 ? chain_scan<ContestOp<PAIRS>, 128, 8, 8>(cop, cnt, scan_tmp, st)
-                 : contest_minb == 12 ? chain_scan<ContestOp<PAIRS>, 64, 8, 12>(cop, cnt, scan_tmp, st)
-                                     : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, cnt, scan_tmp, st);
+        const u32* nd = cop.n_dev;
+        int nl = contest_minb == 4   ? chain_scan<ContestOp<PAIRS>, 256, 8, 4>(cop, cnt, scan_tmp, st, nd)
+                 : contest_minb == 6 ? chain_scan<ContestOp<PAIRS>, 128, 8, 6>(cop, cnt, scan_tmp, st, nd)
+                 : contest_minb == 8 ? chain_scan<ContestOp<PAIRS>, 128, 8, 8>(cop, cnt, scan_tmp, st, nd)
+                 : contest_minb == 12 ? chain_scan<ContestOp<PAIRS>, 64, 8, 12>(cop, cnt, scan_tmp, st, nd)
+                                     : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, cnt, scan_tmp, st, nd);
         pe("contest", nl, cnt, (PAIRS ? 28ull : 24ull) * cnt);
     };
     // sort plan of `cnt` keys spread over the level's cells: segmented when the cell bits would cost extra passes
@@ -907,14 +908,17 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         return radix_plan(lay.pb, (nseg > 1 ? segk : lay.cb) + lay.hexbits);
     };
     // radix scratch (histograms + look-back status) and, for a segmented sort, the tile table over `starts`
-    auto radix_setup = [&](RadixTemp& rt, const RadixPlan& plan, u32 cnt, const u32* starts) {
-        const u64 hwords = nseg > 1 ? RadixTemp::ghist_words_seg(nseg, plan) : RadixTemp::ghist_words();
-        const u64 rwords = hwords + RadixTemp::status_words(cnt, plan, nseg > 1 ? nseg : 0);
+    // (`table`: use the tile table even for a single segment - the keys' count is then only known on the device and
+    // `cnt` is an upper bound; the table gives every tile its real extent)
+    auto radix_setup = [&](RadixTemp& rt, const RadixPlan& plan, u32 cnt, const u32* starts, bool table = false) {
+        table = table || nseg > 1;
+        const u64 hwords = table ? RadixTemp::ghist_words_seg(nseg, plan) : RadixTemp::ghist_words();
+        const u64 rwords = hwords + RadixTemp::status_words(cnt, plan, table ? nseg : 0);
         rt_mem = dalloc<u32>(rwords);
         rt.ghist = rt_mem;
         rt.status = rt.ghist + hwords;
         CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
-        if (nseg > 1) {
+        if (table) {
             rt.nseg = nseg;
             rt.ntiles_seg = (u32)RadixTemp::seg_tiles_bound(cnt, nseg);
             tinfo = dalloc<uint4>(rt.ntiles_seg);
@@ -934,30 +938,31 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         // ---- round 1: the early arrivals of every cell
         u32* estart = dalloc<u32>((u64)ncell + 1);
         k_early_starts<<<1, 1024, 0, st>>>(cell_start, ncell, fshift, estart, &d_scr->aux);
-        fetch_scratch();
-        const u32 nE = h_scr->aux;
-        const RadixPlan plan = plan_for(nE);
+        // the number of early arrivals stays on the device until round 1 is over (one host synchronisation less):
+        // buffers, grids and the tile table are sized by its upper bound
+        const u32 nE_ub = (u32)std::min<u64>(n, ((u64)n >> fshift) + ncell);
+        const RadixPlan plan = plan_for(nE_ub);
         kA = dalloc<u64>(n);   // keys by arrival position, later em
         // candidate lists: one per warp of k_filter, each can hold every arrival that warp looks at
         const u64 fchunk = (((u64)n + hexgrid - 1) / hexgrid + 255ull) & ~255ull;
         const u32 nlists = hexgrid * 8, list_cap = (u32)(fchunk / 8);
         kB = dalloc<u64>((u64)nlists * list_cap);
-        u64 *eA = dalloc<u64>(nE), *eB = dalloc<u64>(nE);
-        uint4* tails = dalloc<uint4>(nE);
+        u64 *eA = dalloc<u64>(nE_ub), *eB = dalloc<u64>(nE_ub);
+        uint4* tails = dalloc<uint4>(nE_ub);
         RadixTemp rt;
         pb();
-        radix_setup(rt, plan, nE, estart);
+        radix_setup(rt, plan, nE_ub, estart, true);
         k_hexkey<PAIRS><<<hexgrid, 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay, plan, kA, vA, d2oct, rt.ghist, segk, nseg,
                                                  estart, eA, &d_scr->err);
-        pe("hexkey", nseg > 1 ? 3 : 1, n, 32ull * n);
+        pe("hexkey", 3, n, 32ull * n);
         trace_mark(st, "hexkey", h, n);
-        int cur = radix_sort<PAIRS>(eA, nullptr, eB, nullptr, nE, plan, rt, st, *this);
+        int cur = radix_sort<PAIRS>(eA, nullptr, eB, nullptr, nE_ub, plan, rt, st, *this);
         em = kA;
-        run_contest(ContestOp<PAIRS>{cur ? eB : eA, nullptr, nE, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin,
-                                     &d_scr->err, tails, nullptr}, nE);
+        run_contest(ContestOp<PAIRS>{cur ? eB : eA, nullptr, nE_ub, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin,
+                                     &d_scr->err, tails, nullptr, &d_scr->aux}, nE_ub);
         fetch_scratch();
         check_err();
-        const u32 nwinE = h_scr->nwin;
+        const u32 nwinE = h_scr->nwin, nE = h_scr->aux;
         trace_mark(st, "round1", h, nE);
         // predicted round-2 list: early winners + one candidate per (early arrivals per prism + 1) later arrivals
         const double s2_pred = nwinE + (double)(n - nE) / ((double)nE / std::max<u32>(nwinE, 1) + 1.0);
@@ -1000,7 +1005,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
             pe("filter", 3, nS2, 24ull * nS2);
             cur = radix_sort<PAIRS>(s2A, nullptr, s2B, nullptr, nS2, plan2, rt2, st, *this);
             run_contest(ContestOp<PAIRS>{cur ? s2B : s2A, nullptr, nS2, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin,
-                                         &d_scr->err, nullptr, estart}, nS2);
+                                         &d_scr->err, nullptr, estart, nullptr}, nS2);
             trace_mark(st, "round2", h, nS2);
             dfree(s2A); dfree(s2B); dfree(T.slots); dfree(ncand); dfree(wkeys);
             filtered = true;
@@ -1035,7 +1040,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
 
         // ---- stage 4: contest
         run_contest(ContestOp<PAIRS>{ks, vs, n, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err, nullptr,
-                                     nullptr}, n);
+                                     nullptr, nullptr}, n);
         trace_mark(st, "contest", h, n);
     }
     int nl = 0;

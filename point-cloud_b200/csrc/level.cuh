@@ -568,6 +568,7 @@ struct ContestOp {
     // incumbents of their groups - their own emission was decided in round 1 and is not touched.
     uint4* tails;
     const u32* estart;
+    const u32* n_dev;   // element count on the device (then `n` is an upper bound, see k_chain_scan), else null
     __device__ static void pack(const State& s, u32 status, uint4& a, uint4& b) {
         a = make_uint4((u32)s.mn, (u32)(s.mn >> 32), s.meta, s.ntail | status);   // ntail < 2^30
         b = make_uint4(0u, 0u, 0u, status);
@@ -581,6 +582,7 @@ struct ContestOp {
     // order, 11 first arrival of its cell, 12 last arrival of its cell
     __device__ void load_items(u64 base, State (&v)[ITEMS]) const {
         const int lane = threadIdx.x & 31;
+        const u32 n = n_dev ? __ldg(n_dev) : this->n;
         u64 key[ITEMS];
         u32 pos[ITEMS];
         if (base + ITEMS <= n) {

@@ -271,9 +271,14 @@ __device__ __forceinline__ typename Op::State chain_lookback(const Op& op, uint4
     return prefix;
 }
 
+// n_dev (optional): the element count lives on the device; `n` is then only an upper bound that sized the grid (tiles
+// behind the real end fold identities through the chain, the last tile of the grid still reports the total).  The Op
+// must bound its own loads the same way.
 template <class Op, int THREADS, int ITEMS, int MINB>
-__global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
+__global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 ntiles, uint4* __restrict__ desc,
+                                                              const u32* __restrict__ n_dev) {
     typedef typename Op::State State;
+    if (n_dev) n = __ldg(n_dev);
     constexpr int WARPS = THREADS / 32;
     __shared__ State s_warp[WARPS];
     __shared__ State s_prefix;
@@ -344,11 +349,11 @@ __global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 
 
 // Host launcher: `temp` must hold chain_temp_bytes(ntiles) bytes.  Returns launches (memset excluded).
 template <class Op, int THREADS, int ITEMS, int MINB = 1>
-static inline int chain_scan(const Op& op, u32 n, void* temp, cudaStream_t st) {
+static inline int chain_scan(const Op& op, u32 n, void* temp, cudaStream_t st, const u32* n_dev = nullptr) {
     const u32 ntiles = div_up(n, THREADS * ITEMS);
     if (!ntiles) return 0;
     cudaMemsetAsync(temp, 0, chain_temp_bytes(ntiles), st);
-    k_chain_scan<Op, THREADS, ITEMS, MINB><<<ntiles, THREADS, 0, st>>>(op, n, ntiles, (uint4*)temp);
+    k_chain_scan<Op, THREADS, ITEMS, MINB><<<ntiles, THREADS, 0, st>>>(op, n, ntiles, (uint4*)temp, n_dev);
     return 1;
 }
 template <int THREADS, int ITEMS>
