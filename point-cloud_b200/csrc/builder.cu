@@ -967,7 +967,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         // predicted round-2 list: early winners + one candidate per (early arrivals per prism + 1) later arrivals
         const double s2_pred = nwinE + (double)(n - nE) / ((double)nE / std::max<u32>(nwinE, 1) + 1.0);
         static const bool filter_bail = getenv("PCB_FILTER_BAIL") != nullptr;   // test hook: give up after round 1
-        if (!filter_bail && (filter_force > 0 || s2_pred < 0.4 * n)) {
+        if (!filter_bail && nwinE < (1u << 29) && (filter_force > 0 || s2_pred < 0.4 * n)) {   // (table capacity is 32 bits)
             // ---- filter: later arrivals against the early winners
             FilterTable T;
             u32 cap = 1024;
