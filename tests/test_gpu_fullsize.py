@@ -97,3 +97,39 @@ def test_merge_equals_continued_stream_at_size(tmp_path):
     assert merged.keys() == both.keys()
     for k in both:
         assert _signature(merged[k]) == _signature(both[k]), k
+
+
+@pytest.mark.timeout(900)
+def test_sort_paths_agree_at_size():
+    """The segmented sort and the record filter only engage on big levels, where the CPU oracle is out of reach.  At
+    50 M terrain points and 50 M uniform-cube points (ten chain levels with ~10^7 arrivals per prism) the tree built
+    with both switched off (PCB_NO_SEG, PCB_NO_FILTER: the plain sort + contest that the small-size parity tests pin
+    against the oracle) must equal the default build byte for byte; fresh processes, one digest per node file."""
+    import hashlib
+    import json
+    import os
+    import subprocess
+    code = (
+        "import sys, hashlib, json; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import synth\n"
+        "from pcutil import load_pcb\n"
+        "pcb = load_pcb()\n"
+        "out = {}\n"
+        "for name, pts in (('terrain', synth.terrain(50_000_000, 2, 'cuda').cpu().numpy()),\n"
+        "                  ('cube', synth.uniform_cube(50_000_000, 1, 'cuda').cpu().numpy())):\n"
+        "    nodes, mj, st, _ = pcb.convert([pts])\n"
+        "    h = hashlib.sha256()\n"
+        "    for k in sorted(nodes):\n"
+        "        h.update(k.encode()); h.update(bytes(nodes[k]))\n"
+        "    out[name] = [h.hexdigest(), len(nodes), int(st.arrivals), mj]\n"
+        "    del nodes, pts\n"
+        "print('RESULT ' + json.dumps(out))\n") % (str(ROOT / "tests"), str(ROOT / "point-cloud_b200"))
+    results = []
+    for extra in ({}, {"PCB_NO_SEG": "1", "PCB_NO_FILTER": "1"}):
+        env = dict(os.environ, **extra)
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=800)
+        line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
+        assert r.returncode == 0 and line, r.stdout[-2000:] + r.stderr[-3000:]
+        results.append(json.loads(line[0][7:]))
+    assert results[0] == results[1]
+    assert results[0]["terrain"][1] > 1000 and results[0]["cube"][2] > 10 * 50_000_000
