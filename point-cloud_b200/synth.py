@@ -81,3 +81,36 @@ def gaussian_blobs(n: int, seed: int = 4, device="cpu", blobs: int = 64, chunk=1
         xyz = centres[k] + torch.randn((m, 3), device=device, generator=gen) * sigma[k, None]
         out[s:s + m] = _pack(xyz.to(torch.float32), gen)
     return out
+
+
+def city(n: int, seed: int = 5, device="cpu", extent: float = 10_000.0, boxes: int = 20_000, chunk=1 << 24) -> torch.Tensor:
+    """C5: city-scale scan: `extent` x `extent` metres (10 km: ~100 level-0 cells), 60 % of the points on
+    the ground (value noise +-2 m), 40 % on the faces of `boxes` axis-aligned boxes (footprint 10-60 m, height 5-120 m),
+    sigma = 2 cm sensor noise."""
+    gen = torch.Generator(device=device)
+    gen.manual_seed(seed)
+    bx = torch.rand((boxes, 2), device=device, generator=gen) * extent          # box corner (x, y)
+    bs = 10.0 + 50.0 * torch.rand((boxes, 2), device=device, generator=gen)     # footprint
+    bh = 5.0 + 115.0 * torch.rand(boxes, device=device, generator=gen) ** 3     # mostly low, a few towers
+    out = torch.empty((n, 16), dtype=torch.uint8, device=device)
+    for s in range(0, n, chunk):
+        m = min(chunk, n - s)
+        u = torch.rand((m, 3), device=device, generator=gen)
+        kind = torch.rand(m, device=device, generator=gen)
+        # ground
+        gx, gy = u[:, 0] * extent, u[:, 1] * extent
+        gz = (_value_noise(gx, gy, 200.0, seed) - 0.5) * 4.0
+        # box faces: roof (30 %) or one of the four walls
+        k = torch.randint(0, boxes, (m,), device=device, generator=gen)
+        face = torch.randint(0, 5, (m,), device=device, generator=gen)
+        fx = bx[k, 0] + u[:, 0] * bs[k, 0]
+        fy = bx[k, 1] + u[:, 1] * bs[k, 1]
+        fz = u[:, 2] * bh[k]
+        fx = torch.where(face == 1, bx[k, 0], torch.where(face == 2, bx[k, 0] + bs[k, 0], fx))
+        fy = torch.where(face == 3, bx[k, 1], torch.where(face == 4, bx[k, 1] + bs[k, 1], fy))
+        fz = torch.where(face == 0, bh[k], fz)
+        on_box = kind < 0.4
+        xyz = torch.stack([torch.where(on_box, fx, gx), torch.where(on_box, fy, gy), torch.where(on_box, fz, gz)], dim=1)
+        xyz = xyz + torch.randn((m, 3), device=device, generator=gen) * 0.02
+        out[s:s + m] = _pack(xyz.to(torch.float32), gen)
+    return out

@@ -29,7 +29,8 @@ def device_build(pts, reps=3):
 
 for name, gen in (("C1-shaped uniform cube", lambda: synth.uniform_cube(n, 1, "cuda")),
                   ("C4-shaped gaussian blobs", lambda: synth.gaussian_blobs(n, 4, "cuda")),
-                  ("C2 terrain", lambda: synth.terrain(n, 2, "cuda"))):
+                  ("C2 terrain", lambda: synth.terrain(n, 2, "cuda")),
+                  ("C5-shaped city scan (10 km x 10 km)", lambda: synth.city(n, 5, "cuda"))):
     pts = gen()
     torch.cuda.synchronize()
     dt, st = device_build(pts)

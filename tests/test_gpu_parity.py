@@ -133,6 +133,16 @@ def test_terrain_like_default_config():
     _check([make_points(np.column_stack([xy, z]))])
 
 
+def test_city_scan_in_miniature():
+    """BASELINE.json configs[4] in miniature (synth.city: ground + box faces + sensor noise): a 300 m block with a coarse
+    config, and 800 m of city with the default grid and a limit of 500."""
+    import sys
+    sys.path.insert(0, str(__import__("pathlib").Path(__file__).resolve().parent.parent / "point-cloud_b200"))
+    import synth
+    _check([synth.city(300_000, 5, "cpu", extent=300.0, boxes=40).numpy()], config=(50, 16, 64.0), bs=5000)
+    _check([synth.city(600_000, 6, "cpu", extent=800.0, boxes=150).numpy()], config=(500, 96, 1000.0))
+
+
 def test_payload_sort_path_forced():
     """The (key, position) pairs fallback of the level sort (taken when cell + hex + position bits exceed 64)
     must give the same trees; forced through PCB_FORCE_PAIRS in a fresh process."""
