@@ -18,12 +18,31 @@ k_route_hist(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, u32 v
         __syncthreads();
     }
     const double invS0 = 1.0 / (double)S0;
-    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) {
-        const u32 id = (u32)l0_cell_id(pts[i], invS0, box);
-        const u32 peers = __match_any_sync(__activemask(), id);       // random points hit few cells: aggregate
-        if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u) {
-            if (use_sh) atomicAdd(&sh[id], (u32)__popc(peers));
-            else atomicAdd(&hist[id], (u32)__popc(peers));
+    // four points per thread and step (independent loads in flight).  A warp whose 32 points share a cell (scans are
+    // spatially coherent) adds once; otherwise plain atomics: a few-way conflict is cheaper than MATCH.ANY, whose cost
+    // grows with the number of distinct cells in the warp.
+    constexpr int HI = 4;
+    const u64 stride = (u64)gridDim.x * blockDim.x;
+    for (u64 i0 = (u64)blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * HI) {
+        uint4 p[HI];
+#pragma unroll
+        for (int k = 0; k < HI; k++)
+            if (i0 + k * stride < n) p[k] = *(const uint4*)(pts + i0 + k * stride);
+#pragma unroll
+        for (int k = 0; k < HI; k++) {
+            if (i0 + k * stride < n) {
+                PcbPoint q;
+                q.x = __uint_as_float(p[k].x); q.y = __uint_as_float(p[k].y); q.z = __uint_as_float(p[k].z); q.rgba = p[k].w;
+                const u32 id = (u32)l0_cell_id(q, invS0, box);
+                const u32 act = __activemask();
+                const u32 id0 = __shfl_sync(act, id, __ffs(act) - 1);
+                u32* const dst = use_sh ? &sh[id] : &hist[id];
+                if (__all_sync(act, id == id0)) {
+                    if ((threadIdx.x & 31) == (u32)(__ffs(act) - 1)) atomicAdd(dst, (u32)__popc(act));
+                } else {
+                    atomicAdd(dst, 1u);
+                }
+            }
         }
     }
     if (use_sh) {
