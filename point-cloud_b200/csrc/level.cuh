@@ -243,7 +243,7 @@ struct L0SplitSmem {
                                  2 * L0S_MAX_BINS * 4;
 };
 
-__global__ void __launch_bounds__(L0S_THREADS, 3)
+__global__ void __launch_bounds__(L0S_THREADS, 4)   // 64 registers, four blocks per SM (three: 1.63 ms, four: 1.37 ms per 100 M points)
 k_l0_split(const PcbPoint* __restrict__ in_pts, u32 n, float S0, L0Box box, u32 nb, int bits,
            const u32* __restrict__ dbase, const BatchSeg* __restrict__ segs, u32 nseg, const u32* __restrict__ in_bat,
            PcbPoint* __restrict__ pts, u32* __restrict__ bat, u32* __restrict__ status /* [ntiles][nb] */) {
@@ -964,7 +964,7 @@ __device__ __forceinline__ OctPacked oct_combine(const OctPacked& a, const OctPa
     return r;
 }
 template <int OCT_THREADS, int OCT_ITEMS>
-__global__ void __launch_bounds__(OCT_THREADS)
+__global__ void __launch_bounds__(OCT_THREADS, 5)   // 48 registers: 5 blocks per SM (4: 3.07 ms, 5: 3.00, 6: 3.05 per C2 step)
 k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     constexpr int WARPS = OCT_THREADS / 32;
     constexpr int OCT_TILE = OCT_THREADS * OCT_ITEMS;
