@@ -130,7 +130,10 @@ class ClockSampler:
                 "samples": len(inside), "source": self.mode, "reasons": sorted(reasons)}
 
 
-def workload_name(n):
+def workload_name(n, kind="terrain"):
+    if kind == "city":
+        return (f"C5 city scan, {n} points per GPU, one 10 km x 10 km city (ground + 20000 boxes, 2 cm noise) shared by all "
+                f"ranks, default config (5000/96/1000.0), batch 10000")
     return (f"C2 terrain, {n} points per GPU, 2.5-D heightfield + noise, default config (5000/96/1000.0), "
             f"batch 10000")
 
@@ -170,6 +173,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--points", type=int, default=100_000_000, help="points per GPU (C2 = 1e8)")
+    ap.add_argument("--workload", default="terrain", choices=["terrain", "city"],
+                    help="terrain = C2 (the bench line); city = C5-shaped scan of a fixed 10 km x 10 km city (extra runs)")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-scale", type=float, default=1.0, help="scales the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true")
@@ -203,7 +208,10 @@ def main():
     # WHOLE extent, so (world-1)/world of them must cross NVLink to reach the owner of their level-0 cell.
     side_x = (n / DENSITY) ** 0.5 * world
     side_y = (n / DENSITY) ** 0.5
-    pts = synth.terrain(n, 2 + rank, dev, (-side_x / 2, side_x / 2, -side_y / 2, side_y / 2), surface_seed=2)
+    if args.workload == "city":   # C5: every rank holds random samples of the WHOLE city
+        pts = synth.city(n, 5, dev, sample_seed=50 + rank)
+    else:
+        pts = synth.terrain(n, 2 + rank, dev, (-side_x / 2, side_x / 2, -side_y / 2, side_y / 2), surface_seed=2)
     torch.cuda.synchronize()
     stream = torch.cuda.current_stream()
     shard = None
@@ -371,7 +379,7 @@ def main():
         out = {"metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                "warmup": args.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True,
                "scaling": "weak", "vs_baseline": None, "dtype": "f32+u64", "data": "synthetic",
-               "config": {"workload": workload_name(n), "points_per_gpu": n,
+               "config": {"workload": workload_name(n, args.workload), "points_per_gpu": n,
                           "l2": "inputs (1.6 GB/step) larger than L2, no explicit flush",
                           "levels": int(last.levels_built), "arrivals_per_point": round(last.arrivals / n, 3),
                           "nodes": int(last.nodes_written), "sharding": ("none (1 GPU)" if world == 1 else

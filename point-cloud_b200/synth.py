@@ -83,15 +83,19 @@ def gaussian_blobs(n: int, seed: int = 4, device="cpu", blobs: int = 64, chunk=1
     return out
 
 
-def city(n: int, seed: int = 5, device="cpu", extent: float = 10_000.0, boxes: int = 20_000, chunk=1 << 24) -> torch.Tensor:
+def city(n: int, seed: int = 5, device="cpu", extent: float = 10_000.0, boxes: int = 20_000, chunk=1 << 24,
+         sample_seed: int | None = None) -> torch.Tensor:
     """C5: city-scale scan: `extent` x `extent` metres (10 km: ~100 level-0 cells), 60 % of the points on
     the ground (value noise +-2 m), 40 % on the faces of `boxes` axis-aligned boxes (footprint 10-60 m, height 5-120 m),
-    sigma = 2 cm sensor noise."""
+    sigma = 2 cm sensor noise.  `seed` fixes the city (boxes, ground), `sample_seed` (default: seed) the sample
+    positions: slices of one big scan share the city and differ in the samples."""
     gen = torch.Generator(device=device)
     gen.manual_seed(seed)
     bx = torch.rand((boxes, 2), device=device, generator=gen) * extent          # box corner (x, y)
     bs = 10.0 + 50.0 * torch.rand((boxes, 2), device=device, generator=gen)     # footprint
     bh = 5.0 + 115.0 * torch.rand(boxes, device=device, generator=gen) ** 3     # mostly low, a few towers
+    if sample_seed is not None:
+        gen.manual_seed(sample_seed)
     out = torch.empty((n, 16), dtype=torch.uint8, device=device)
     for s in range(0, n, chunk):
         m = min(chunk, n - s)
