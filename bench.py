@@ -131,6 +131,9 @@ class ClockSampler:
 
 
 def workload_name(n, kind="terrain"):
+    if kind == "blobs":
+        return (f"C4 Gaussian blobs, {n} points per GPU, 64 Zipf-weighted blobs (sigma 1-100 m) shared by all ranks, "
+                f"default config (5000/96/1000.0), batch 10000")
     if kind == "city":
         return (f"C5 city scan, {n} points per GPU, one 10 km x 10 km city (ground + 20000 boxes, 2 cm noise) shared by all "
                 f"ranks, default config (5000/96/1000.0), batch 10000")
@@ -173,8 +176,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--points", type=int, default=100_000_000, help="points per GPU (C2 = 1e8)")
-    ap.add_argument("--workload", default="terrain", choices=["terrain", "city"],
-                    help="terrain = C2 (the bench line); city = C5-shaped scan of a fixed 10 km x 10 km city (extra runs)")
+    ap.add_argument("--workload", default="terrain", choices=["terrain", "city", "blobs"],
+                    help="terrain = C2 (the bench line); city = C5 scan of a fixed 10 km x 10 km city, blobs = C4 (extra runs)")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-scale", type=float, default=1.0, help="scales the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true")
@@ -210,6 +213,8 @@ def main():
     side_y = (n / DENSITY) ** 0.5
     if args.workload == "city":   # C5: every rank holds random samples of the WHOLE city
         pts = synth.city(n, 5, dev, sample_seed=50 + rank)
+    elif args.workload == "blobs":   # C4: every rank holds random samples of the same 64 blobs
+        pts = synth.gaussian_blobs(n, 4, dev, sample_seed=40 + rank)
     else:
         pts = synth.terrain(n, 2 + rank, dev, (-side_x / 2, side_x / 2, -side_y / 2, side_y / 2), surface_seed=2)
     torch.cuda.synchronize()

@@ -66,14 +66,18 @@ def uniform_cube(n: int, seed: int = 1, device="cpu") -> torch.Tensor:
     return _pack(torch.rand((n, 3), device=device, generator=gen), gen)
 
 
-def gaussian_blobs(n: int, seed: int = 4, device="cpu", blobs: int = 64, chunk=1 << 24) -> torch.Tensor:
-    """C4: Zipf-weighted isotropic Gaussian blobs, sigma log-uniform 1..100 m, centres in +-4 km."""
+def gaussian_blobs(n: int, seed: int = 4, device="cpu", blobs: int = 64, chunk=1 << 24,
+                   sample_seed: int | None = None) -> torch.Tensor:
+    """C4: Zipf-weighted isotropic Gaussian blobs, sigma log-uniform 1..100 m, centres in +-4 km.  `seed` fixes the
+    blobs, `sample_seed` (default: continue the same stream) the samples."""
     gen = torch.Generator(device=device)
     gen.manual_seed(seed)
     centres = torch.rand((blobs, 3), device=device, generator=gen) * torch.tensor([8000.0, 8000.0, 500.0], device=device) \
         - torch.tensor([4000.0, 4000.0, 0.0], device=device)
     sigma = 100.0 ** torch.rand(blobs, device=device, generator=gen)
     w = 1.0 / torch.arange(1, blobs + 1, device=device, dtype=torch.float32)
+    if sample_seed is not None:
+        gen.manual_seed(sample_seed)
     out = torch.empty((n, 16), dtype=torch.uint8, device=device)
     for s in range(0, n, chunk):
         m = min(chunk, n - s)
