@@ -10,6 +10,7 @@
 #include <memory>
 #include <vector>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -132,12 +133,14 @@ int pcb_open(const char* out_dir, const pcb_options* opt, pcb_handle** out) {
         }
     }
     if (!h->merge) {  // Metadata::default() (metadata.rs:30-41), optionally with a test-supplied config
-        if (h->opt.cell_point_overflow_limit || h->opt.sub_grid_dimension || h->opt.max_cell_size != 0.0f) {
-            h->meta.cell_point_overflow_limit = h->opt.cell_point_overflow_limit;
-            h->meta.sub_grid_dimension = h->opt.sub_grid_dimension;
-            h->meta.max_cell_size = h->opt.max_cell_size;
-        }
+        // every field by itself: a zero field keeps its reference default (5000 / 96 / 1000.0, metadata.rs:80-88)
+        if (h->opt.cell_point_overflow_limit) h->meta.cell_point_overflow_limit = h->opt.cell_point_overflow_limit;
+        if (h->opt.sub_grid_dimension) h->meta.sub_grid_dimension = h->opt.sub_grid_dimension;
+        if (h->opt.max_cell_size != 0.0f) h->meta.max_cell_size = h->opt.max_cell_size;
     }
+    // the config is validated here, not when the build starts
+    if (h->meta.sub_grid_dimension == 0 || !(h->meta.max_cell_size > 0.0f) || !std::isfinite(h->meta.max_cell_size))
+        return fail(nullptr, PCB_ERR_ARG, "bad config (sub_grid_dimension / max_cell_size)");
     try {
         h->builder.reset(new Builder(h->opt.device, h->opt.flags));
     } catch (const Error& e) {

@@ -29,7 +29,7 @@ static double now_s() {
 }
 
 // PCB_TRACE=1: host-side timeline of the build on stderr (synchronises at every mark; debugging only)
-static bool g_trace = getenv("PCB_TRACE") != nullptr;
+static bool g_trace = pcb_tuning_env("PCB_TRACE") != nullptr;
 static double g_trace_t0 = 0, g_trace_last = 0;
 static void trace_mark(cudaStream_t st, const char* what, unsigned level = 0, unsigned long long n = 0) {
     if (!g_trace) return;
@@ -468,7 +468,7 @@ class BuilderImpl {
     // downloads overlap the build; device-only runs have nothing to overlap and keep one wave (fewer, larger
     // launches) until the per-level arrays (72 B per arrival, twice) would crowd the device.
     u64 wave_points(u64 n0) const {
-        static const u64 forced = getenv("PCB_WAVE_POINTS") ? strtoull(getenv("PCB_WAVE_POINTS"), nullptr, 10) : 0;
+        static const u64 forced = pcb_tuning_env("PCB_WAVE_POINTS") ? strtoull(pcb_tuning_env("PCB_WAVE_POINTS"), nullptr, 10) : 0;
         if (forced) return forced;
         if (flags & PCB_FLAG_DEVICE_ONLY) return 400ull << 20;
         return std::min<u64>(std::max<u64>(n0 / 4, 16ull << 20), 400ull << 20);
@@ -514,7 +514,7 @@ static LevelGeom make_geom(float max_cell_size, u32 dim, u32 h) {
     return g;
 }
 
-static const bool g_force_pairs = getenv("PCB_FORCE_PAIRS") != nullptr;  // test hook: exercise the payload sort
+static const bool g_force_pairs = pcb_tuning_env("PCB_FORCE_PAIRS") != nullptr;  // test hook: exercise the payload sort
 
 void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     CUDA_TRY(cudaSetDevice(device));
@@ -588,7 +588,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     u32* bat = dalloc_from<u32>(3, n0);
     BatchSeg* d_segs = dalloc<BatchSeg>(segs.size());
     CUDA_TRY(cudaMemcpyAsync(d_segs, segs.data(), segs.size() * sizeof(BatchSeg), cudaMemcpyHostToDevice, st));
-    static const bool l0_sort_forced = getenv("PCB_L0_SORT") != nullptr;   // test hook: the general (sort) path
+    static const bool l0_sort_forced = pcb_tuning_env("PCB_L0_SORT") != nullptr;   // test hook: the general (sort) path
     if (vol <= L0S_MAX_BINS && !pairs0 && !l0_sort_forced) {
         // ---- few level-0 cells: dense histogram -> first slot per cell -> one stable split pass
         const u32 nb = (u32)vol, ntiles = div_up(n0, L0S_TILE);
@@ -855,10 +855,10 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     if (lay.cb + lay.hexbits + lay.pb > 64) throw Error{PCB_ERR_RANGE, "too many cells on one level"};
     // ---- record filter (level.cuh): worth it when a prism sees many arrivals.  Level 0 of a big wave: assumed;
     // deeper: predicted from the level above (the prisms shrink 4x in area, 8x in volume per level).
-    static const bool filter_off = getenv("PCB_NO_FILTER") != nullptr;                         // tuning / test hooks
-    static const int filter_force = getenv("PCB_FILTER_SHIFT") ? atoi(getenv("PCB_FILTER_SHIFT")) : -1;
+    static const bool filter_off = pcb_tuning_env("PCB_NO_FILTER") != nullptr;                         // tuning / test hooks
+    static const int filter_force = pcb_tuning_env("PCB_FILTER_SHIFT") ? atoi(pcb_tuning_env("PCB_FILTER_SHIFT")) : -1;
     u32 fshift = 0;   // early share of a cell = its first len >> fshift arrivals; 0 = no filter on this level
-    static const double filter_min = getenv("PCB_FILTER_MIN") ? atof(getenv("PCB_FILTER_MIN")) : 64.0;
+    static const double filter_min = pcb_tuning_env("PCB_FILTER_MIN") ? atof(pcb_tuning_env("PCB_FILTER_MIN")) : 64.0;
     if (!PAIRS && !existing && !filter_off && lay.cb + lay.hexbits < FILTER_GID_BITS) {
         const double m_pred = h == 0 ? 1e9 : last_mult / 4.0;
         if (filter_force > 0) fshift = (u32)filter_force;
@@ -876,7 +876,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     u32* rt_mem = nullptr;
     uint4* tinfo = nullptr;
     u32* seg_base = nullptr;
-    static const int contest_minb = getenv("PCB_CONTEST_MINB") ? atoi(getenv("PCB_CONTEST_MINB")) : 3;  // tuning hook
+    static const int contest_minb = pcb_tuning_env("PCB_CONTEST_MINB") ? atoi(pcb_tuning_env("PCB_CONTEST_MINB")) : 3;  // tuning hook
     auto run_contest = [&](const ContestOp<PAIRS>& cop, u32 cnt) {   // cnt: upper bound when cop.n_dev is set
         pb();
         const u32* nd = cop.n_dev;
@@ -890,8 +890,8 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     // sort plan of `cnt` keys spread over the level's cells: segmented when the cell bits would cost extra passes
     // (radix.cuh): runs of 2^segk consecutive cells are sorted independently inside the same launches.  Taken when
     // segments average >= PCB_SEG_MIN keys (tiles never straddle a segment: small segments mean partly filled tiles).
-    static const bool seg_off = getenv("PCB_NO_SEG") != nullptr;                                       // tuning / test hooks
-    static const u64 seg_min = getenv("PCB_SEG_MIN") ? strtoull(getenv("PCB_SEG_MIN"), nullptr, 10) : 4ull * RADIX_TILE;
+    static const bool seg_off = pcb_tuning_env("PCB_NO_SEG") != nullptr;                                       // tuning / test hooks
+    static const u64 seg_min = pcb_tuning_env("PCB_SEG_MIN") ? strtoull(pcb_tuning_env("PCB_SEG_MIN"), nullptr, 10) : 4ull * RADIX_TILE;
     int segk = 31;
     u32 nseg = 1;
     auto plan_for = [&](u32 cnt) {
@@ -966,7 +966,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         trace_mark(st, "round1", h, nE);
         // predicted round-2 list: early winners + one candidate per (early arrivals per prism + 1) later arrivals
         const double s2_pred = nwinE + (double)(n - nE) / ((double)nE / std::max<u32>(nwinE, 1) + 1.0);
-        static const bool filter_bail = getenv("PCB_FILTER_BAIL") != nullptr;   // test hook: give up after round 1
+        static const bool filter_bail = pcb_tuning_env("PCB_FILTER_BAIL") != nullptr;   // test hook: give up after round 1
         if (!filter_bail && nwinE < (1u << 29) && (filter_force > 0 || s2_pred < 0.4 * n)) {   // (table capacity is 32 bits)
             // ---- filter: later arrivals against the early winners
             FilterTable T;
@@ -1210,15 +1210,21 @@ int route_bbox(int device, void* stream, const pcb_point* d_pts, uint64_t n, flo
     return guarded([&] {
         CUDA_TRY(cudaSetDevice(device));
         cudaStream_t st = (cudaStream_t)stream;
+        if (n >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "more than 2^30-1 points on one device"};
         int init[8] = {INT_MAX, INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MIN, 0, 0};
-        int* d = nullptr;
-        CUDA_TRY(cudaMallocAsync((void**)&d, sizeof init, st));
+        struct Scratch8 {   // freed on every path out of this function
+            int* p = nullptr;
+            cudaStream_t st;
+            ~Scratch8() { if (p) cudaFreeAsync(p, st); }
+        } scr;
+        scr.st = st;
+        CUDA_TRY(cudaMallocAsync((void**)&scr.p, sizeof init, st));
+        int* d = scr.p;
         CUDA_TRY(cudaMemcpyAsync(d, init, sizeof init, cudaMemcpyHostToDevice, st));
         if (n) k_bbox_check<<<148 * 8, 256, 0, st>>>((const PcbPoint*)d_pts, (u32)n, S0, d, (u32*)(d + 6));
         int res[8];
         CUDA_TRY(cudaMemcpyAsync(res, d, sizeof res, cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
-        CUDA_TRY(cudaFreeAsync(d, st));
         if (res[6] & PCB_DERR_NONFINITE) throw Error{PCB_ERR_RANGE, "non-finite coordinate in input"};
         if (res[6] & PCB_DERR_L0RANGE) throw Error{PCB_ERR_RANGE, "level-0 cell index outside +-2^20"};
         for (int a = 0; a < 3; a++) {
@@ -1235,6 +1241,7 @@ int route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n
         CUDA_TRY(cudaSetDevice(device));
         cudaStream_t st = (cudaStream_t)stream;
         const u64 vol = (u64)dims[0] * dims[1] * dims[2];
+        if (n >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "more than 2^30-1 points on one device"};
         if (vol == 0 || vol > (1ull << 26)) throw Error{PCB_ERR_RANGE, "level-0 index box too large for the dense routing table"};
         CUDA_TRY(cudaMemsetAsync(d_hist, 0, vol * 4, st));
         if (n) k_route_hist<<<148 * 4, 256, 0, st>>>((const PcbPoint*)d_pts, (u32)n, S0, make_box(origin, dims), (u32)vol, d_hist);
@@ -1252,7 +1259,7 @@ int route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uin
         if (!n) return 0;
         if (n >= (1ull << 30) || world == 0 || world > 256 || batch_size == 0) throw Error{PCB_ERR_ARG, "bad routing arguments"};
         const u32 n32 = (u32)n;
-        static const bool no_split = getenv("PCB_ROUTE_SORT") != nullptr;   // test hook: force the general path
+        static const bool no_split = pcb_tuning_env("PCB_ROUTE_SORT") != nullptr;   // test hook: force the general path
         if (world <= 8 && !no_split) {
             // one node: single-pass stable split (local histogram -> per-owner send offsets -> chained 8-way split)
             const L0Box box = make_box(origin, dims);

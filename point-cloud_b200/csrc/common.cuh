@@ -15,6 +15,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 typedef uint32_t u32;
 typedef uint64_t u64;
@@ -127,3 +128,14 @@ struct PcbCudaError {
 };
 
 static inline u32 div_up(u64 a, u64 b) { return (u32)((a + b - 1) / b); }
+
+// Tuning and test hooks (PCB_FORCE_PAIRS, PCB_SEG_MIN, PCB_WAVE_POINTS, PCB_TRACE ...) are read from the environment
+// ONLY when PCB_ENABLE_TUNING=1 is set as well: a stray PCB_* variable in a user's environment must not change the
+// code path of a production conversion.  The parity tests that force a path set both.
+static inline const char* pcb_tuning_env(const char* name) {
+    static const bool on = [] {
+        const char* e = getenv("PCB_ENABLE_TUNING");
+        return e && e[0] == '1' && e[1] == 0;
+    }();
+    return on ? getenv(name) : nullptr;
+}

@@ -1109,7 +1109,7 @@ static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStr
     return 1;
 }
 static inline int octscan(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
-    static const int variant = getenv("PCB_OCT_VARIANT") ? atoi(getenv("PCB_OCT_VARIANT")) : 0;   // tuning hook
+    static const int variant = pcb_tuning_env("PCB_OCT_VARIANT") ? atoi(pcb_tuning_env("PCB_OCT_VARIANT")) : 0;   // tuning hook
     switch (variant) {
         case 1: return octscan_launch<256, 8>(op, n, temp, st);
         case 2: return octscan_launch<128, 16>(op, n, temp, st);

@@ -58,7 +58,7 @@ struct RadixPlan {
 // with three 9-bit passes, 10.7 ms with four 7-bit passes).
 #define RADIX_DEFAULT_BITS 8
 static inline int radix_digit_bits() {
-    static const int b = getenv("PCB_RADIX_BITS") ? std::min(RADIX_MAX_BITS, std::max(4, atoi(getenv("PCB_RADIX_BITS")))) : RADIX_DEFAULT_BITS;
+    static const int b = pcb_tuning_env("PCB_RADIX_BITS") ? std::min(RADIX_MAX_BITS, std::max(4, atoi(pcb_tuning_env("PCB_RADIX_BITS")))) : RADIX_DEFAULT_BITS;
     return b;
 }
 // Sort bits [lo, lo + nbits) in ceil(nbits / digit width) passes of (almost) equal width.
@@ -449,7 +449,7 @@ static inline int radix_sort_shape(u64* k0, u32* v0, u64* k1, u32* v1, u32 n, co
         kern<<<ntiles, THREADS, smem, st>>>(ki, ko, vi, vo, n, plan.shift[p], plan.bits[p],
                                             tmp.ghist + p * RADIX_MAX_BINS, status, status + words, tmp.tinfo,
                                             hist_stride);
-        static const bool by_pass = getenv("PCB_PROF_PASSES") != nullptr;   // diagnostics: one stats row per pass index
+        static const bool by_pass = pcb_tuning_env("PCB_PROF_PASSES") != nullptr;   // diagnostics: one stats row per pass index
         static const char* const pass_name[RADIX_MAX_PASSES] = {"radix_p0", "radix_p1", "radix_p2", "radix_p3",
                                                                 "radix_p4", "radix_p5", "radix_p6", "radix_p7"};
         prof.pe(by_pass ? pass_name[p] : "radix_onesweep", 1, n, (PAIRS ? 24ull : 16ull) * n);
@@ -461,8 +461,8 @@ static inline int radix_sort_shape(u64* k0, u32* v0, u64* k1, u32* v1, u32 n, co
 template <bool PAIRS, class Prof>
 static inline int radix_sort(u64* k0, u32* v0, u64* k1, u32* v1, u32 n, const RadixPlan& plan, RadixTemp& tmp,
                              cudaStream_t st, Prof& prof) {
-    static const int threads = getenv("PCB_RADIX_THREADS") ? atoi(getenv("PCB_RADIX_THREADS")) : 256;   // tuning hooks
-    static const int mode = getenv("PCB_RADIX_MODE") ? atoi(getenv("PCB_RADIX_MODE")) : 2;
+    static const int threads = pcb_tuning_env("PCB_RADIX_THREADS") ? atoi(pcb_tuning_env("PCB_RADIX_THREADS")) : 256;   // tuning hooks
+    static const int mode = pcb_tuning_env("PCB_RADIX_MODE") ? atoi(pcb_tuning_env("PCB_RADIX_MODE")) : 2;
     const int v = ((!PAIRS && threads == 512 && n > 4 * RADIX_TILE && !tmp.tinfo) ? 3 : 0) + (mode % 3);
 #define PCB_RS(T, M) radix_sort_shape<PAIRS, T, M, Prof>(k0, v0, k1, v1, n, plan, tmp, st, prof)
     switch (v) {

@@ -126,10 +126,37 @@ def test_sort_paths_agree_at_size():
         "print('RESULT ' + json.dumps(out))\n") % (str(ROOT / "tests"), str(ROOT / "point-cloud_b200"))
     results = []
     for extra in ({}, {"PCB_NO_SEG": "1", "PCB_NO_FILTER": "1"}):
-        env = dict(os.environ, **extra)
+        env = dict(os.environ, PCB_ENABLE_TUNING="1", **extra)
         r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=800)
         line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
         assert r.returncode == 0 and line, r.stdout[-2000:] + r.stderr[-3000:]
         results.append(json.loads(line[0][7:]))
     assert results[0] == results[1]
     assert results[0]["terrain"][1] > 1000 and results[0]["cube"][2] > 10 * 50_000_000
+
+
+@pytest.mark.timeout(1500)
+def test_oracle_at_size():
+    """Oracle vs GPU at a size where the fast paths engage BY THEMSELVES (default environment, nothing forced): the
+    record filter needs >= 2^21 arrivals on a level and >= 64 arrivals per prism, the segmented sort >= 4 x 4096 keys
+    per segment.  (a) 25 M terrain points at the bench workload's density over 2 x 2 level-0 cells - the cloud the
+    reference arm of bench.py builds - against the oracle with one thread per level-0 cell; (b) a 10 M-point uniform
+    unit cube (ten chain levels of a single cell that sees every point, record filter on each of them).  Every node
+    image is compared in canonical form (cell.rs:70-153 contest + overflow machine, converter.rs:106-139 recursion)."""
+    import os
+    import synth
+    from pcutil import compare_trees, oracle_convert
+    assert not any(k.startswith("PCB_") for k in os.environ), "the at-size parity test runs in the default environment"
+    pcb = load_pcb()
+    density, side = 6.25, 2000.0
+    n = int(density * side * side)
+    for name, pts, threads in (
+            ("terrain", synth.terrain(n, 2, "cuda", (-1000.0, -1000.0 + side, -1000.0, -1000.0 + side)).cpu().numpy(), 4),
+            ("cube", synth.uniform_cube(10_000_000, 1, "cuda").cpu().numpy(), 1)):
+        nodes, mj, st, _ = pcb.convert([pts])
+        assert st.gpu_launches > 0
+        o = oracle_convert([pts], threads=threads)
+        assert st.arrivals == o.arrivals and st.hierarchies == o.hierarchies, name
+        assert mj == o.meta_json, name
+        compare_trees(o.nodes, nodes, f"oracle-{name}", f"gpu-{name}")
+        del nodes, o, pts

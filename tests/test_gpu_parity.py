@@ -161,7 +161,7 @@ def test_payload_sort_path_forced():
         "    compare_trees(o.nodes, nodes, 'oracle', 'gpu-pairs')\n"
         "    assert mj == o.meta_json and all(o.nodes[k] == nodes[k] for k in nodes)\n"
         "print('pairs ok')\n") % os.path.dirname(os.path.abspath(__file__))
-    env = dict(os.environ, PCB_FORCE_PAIRS="1")
+    env = dict(os.environ, PCB_ENABLE_TUNING="1", PCB_FORCE_PAIRS="1")
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "pairs ok" in r.stdout, r.stdout + r.stderr
 
@@ -189,7 +189,7 @@ def test_segmented_sort_forced():
         "    assert mj == o.meta_json and all(o.nodes[k] == nodes[k] for k in nodes)\n"
         "print('seg ok')\n") % os.path.dirname(os.path.abspath(__file__))
     for extra in ({}, {"PCB_FORCE_PAIRS": "1"}):
-        env = dict(os.environ, PCB_SEG_MIN="1", **extra)
+        env = dict(os.environ, PCB_ENABLE_TUNING="1", PCB_SEG_MIN="1", **extra)
         r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and "seg ok" in r.stdout, r.stdout + r.stderr
 
@@ -223,7 +223,7 @@ def test_record_filter_forced():
     # the last one gives the filter up after round 1 (too many predicted candidates) and falls back to the full sort
     for extra in ({"PCB_FILTER_SHIFT": "1"}, {"PCB_FILTER_SHIFT": "2", "PCB_SEG_MIN": "1"}, {"PCB_FILTER_SHIFT": "4"},
                   {"PCB_FILTER_SHIFT": "3", "PCB_FILTER_BAIL": "1"}):
-        env = dict(os.environ, **extra)
+        env = dict(os.environ, PCB_ENABLE_TUNING="1", **extra)
         r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and "filter ok" in r.stdout, str(extra) + r.stdout[-2000:] + r.stderr[-3000:]
 
@@ -258,7 +258,7 @@ def test_waves_of_level0_cells_forced():
         "    compare_trees(read_tree(d_o), read_tree(d_g), 'oracle-merge', 'gpu-merge-waves')\n"
         "    assert open(d_o + '/metadata.json').read() == open(d_g + '/metadata.json').read()\n"
         "print('waves ok')\n") % os.path.dirname(os.path.abspath(__file__))
-    env = dict(os.environ, PCB_WAVE_POINTS="7000")
+    env = dict(os.environ, PCB_ENABLE_TUNING="1", PCB_WAVE_POINTS="7000")
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "waves ok" in r.stdout, r.stdout + r.stderr
 
@@ -285,6 +285,6 @@ def test_level0_sort_path_forced_and_wide_boxes():
         "    compare_trees(o.nodes, nodes, 'oracle', 'gpu-l0sort')\n"
         "    assert mj == o.meta_json and all(o.nodes[k] == nodes[k] for k in nodes)\n"
         "print('l0 sort ok')\n") % os.path.dirname(os.path.abspath(__file__))
-    env = dict(os.environ, PCB_L0_SORT="1")
+    env = dict(os.environ, PCB_ENABLE_TUNING="1", PCB_L0_SORT="1")
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "l0 sort ok" in r.stdout, r.stdout + r.stderr
