@@ -2,21 +2,29 @@
 """bench.py — octree/LOD build throughput (BASELINE.json metric) on B200.
 
 A step = ONE full conversion (all levels) of the synthetic cloud of the workload.
-  value  : Mpoints/s with the input resident in HBM and the node images left in HBM (device build)
-  e2e    : Mpoints/s through the C ABI with HOST buffers: pinned host points -> H2D -> build -> node
-           images D2H into host memory (no file system), wall clock
+  value   : Mpoints/s with the input resident in HBM and the node images left in HBM (device build)
+  e2e     : Mpoints/s through the C ABI with HOST buffers: pinned host points -> H2D -> (N > 1: level-0 exchange) ->
+            build -> node images D2H into host memory, wall clock, with a per-phase split
+  e2e_files: (N = 1) the same down to node files + metadata.json on tmpfs: warm (this process) and cold (a fresh
+            `point_converter` process reading a PLY from tmpfs - what a CLI user pays)
   roofline: dominant kernel class, algorithmic bytes / CUDA-event time vs MEASURED_PEAKS.json hbm_gbs
-  cpu_baseline: the CPU oracle (sequential port of the reference's algorithm; the reference CLI itself
-           is single-threaded and Rust cannot be built here) on a bounded, same-density sample
-`--impl reference` times that CPU oracle alone (all the threads the algorithm can use: it is parallel
-only across level-0 cells).
+  cpu_baseline: the CPU oracle (sequential port of the reference's algorithm; the reference CLI itself is
+            single-threaded and Rust cannot be built here) on ONE core over the FULL workload (same bytes as the GPU)
+  check   : (N > 1) one verified step outside the timed region: the order-independent digest of every stored record
+            over all ranks equals the digest of the inputs, every stored point lies in its node's cell, and the fused
+            NVLink exchange delivers the same buffers as the NCCL all-to-all path
+Workloads (--workload): terrain = C2 (the bench line), cube = C1-shaped, merge = C3, blobs = C4, city = C5.
+`--impl reference` times the CPU oracle alone on the same workload with one thread per level-0 cell (the only
+parallelism the reference's algorithm has).
 """
 import argparse
 import json
 import os
+import shutil
 import statistics
 import subprocess
 import sys
+import tempfile
 import time
 from pathlib import Path
 
@@ -36,15 +44,49 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_oracle_run(n_points, extent, threads, seed=2):
-    """Times the CPU oracle on a terrain tile of the workload's density.  Returns (Mpts/s, seconds)."""
+def terrain_extent(n, world=1):
+    side_x = (n / DENSITY) ** 0.5 * world
+    side_y = (n / DENSITY) ** 0.5
+    return (-side_x / 2, side_x / 2, -side_y / 2, side_y / 2)
+
+
+def make_cloud(kind, n, rank, world, dev):
+    """The rank's slice of the undivided stream (uint8 (n, 16) tensor on `dev`).  Weak scaling: world * n points;
+    rank r holds the index range [r*n, (r+1)*n): random points of the WHOLE extent, so (world-1)/world of them must
+    cross NVLink to reach the owner of their level-0 cell."""
     import synth
+    if kind == "city":    # C5: every rank holds random samples of the WHOLE city
+        return synth.city(n, 5, dev, sample_seed=50 + rank)
+    if kind == "blobs":   # C4: every rank holds random samples of the same 64 blobs
+        return synth.gaussian_blobs(n, 4, dev, sample_seed=40 + rank)
+    if kind == "cube":    # C1: the unit cube (one level-0 cell)
+        return synth.uniform_cube(n, 1 + rank, dev)
+    # terrain (C2) and the merged stream of C3: same density, extent grows with the world size
+    return synth.terrain(n, 2 + rank, dev, terrain_extent(n, world), surface_seed=2)
+
+
+def workload_name(n, kind="terrain"):
+    tail = "default config (5000/96/1000.0), batch 10000"
+    if kind == "blobs":
+        return f"C4 Gaussian blobs, {n} points per GPU, 64 Zipf-weighted blobs (sigma 1-100 m) shared by all ranks, {tail}"
+    if kind == "city":
+        return (f"C5 city scan, {n} points per GPU, one 10 km x 10 km city (ground + 20000 boxes, 2 cm noise) shared by all "
+                f"ranks, {tail}")
+    if kind == "cube":
+        return f"C1-shaped uniform unit cube, {n} points per GPU (one level-0 cell: every chain level sees every point), {tail}"
+    if kind == "merge":
+        return (f"C3 merge: {n} new terrain points (sample seed 3) merged into the existing output of {n} points (sample "
+                f"seed 2, same surface) on tmpfs, {tail}")
+    return f"C2 terrain, {n} points per GPU, 2.5-D heightfield + noise, {tail}"
+
+
+def cpu_oracle_run(pts_np, threads, out_dir=None, lru=0):
+    """Times the CPU oracle (test infrastructure, here as the reported CPU baseline) on the given records."""
     from pcutil import oracle_convert
-    pts = synth.terrain(n_points, seed, "cpu", extent).numpy()
     t0 = time.perf_counter()
-    oracle_convert([pts], dump=False, threads=threads)
+    oracle_convert([pts_np], dump=False, threads=threads, out_dir=out_dir, lru=lru)
     dt = time.perf_counter() - t0
-    return n_points / dt / 1e6, dt
+    return len(pts_np) / dt / 1e6, dt
 
 
 class ClockSampler:
@@ -75,7 +117,7 @@ class ClockSampler:
                 self.samples.append((time.time(), float(sm), float(mx), int(rs)))
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.02)
 
     def _smi_loop(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -130,43 +172,74 @@ class ClockSampler:
                 "samples": len(inside), "source": self.mode, "reasons": sorted(reasons)}
 
 
-def workload_name(n, kind="terrain"):
-    if kind == "blobs":
-        return (f"C4 Gaussian blobs, {n} points per GPU, 64 Zipf-weighted blobs (sigma 1-100 m) shared by all ranks, "
-                f"default config (5000/96/1000.0), batch 10000")
+def cpu_cloud(kind, n):
+    """The workload's cloud generated on the host cores (the reference arm must not need a GPU)."""
+    import synth
     if kind == "city":
-        return (f"C5 city scan, {n} points per GPU, one 10 km x 10 km city (ground + 20000 boxes, 2 cm noise) shared by all "
-                f"ranks, default config (5000/96/1000.0), batch 10000")
-    return (f"C2 terrain, {n} points per GPU, 2.5-D heightfield + noise, default config (5000/96/1000.0), "
-            f"batch 10000")
+        return synth.city(n, 5, "cpu", sample_seed=50).numpy()
+    if kind == "blobs":
+        return synth.gaussian_blobs(n, 4, "cpu", sample_seed=40).numpy()
+    if kind == "cube":
+        return synth.uniform_cube(n, 1, "cpu").numpy()
+    return synth.terrain(n, 2, "cpu", terrain_extent(n), surface_seed=2).numpy()
 
 
 def run_reference(args, rank, world):
-    """CPU arm: the oracle port on the host cores.  Rank 0 only."""
+    """CPU arm: the oracle port on the host cores, FULL single-GPU workload (`--cpu-scale` shrinks it).  Rank 0 only."""
     if rank != 0:
         return
+    import numpy as np
     cores = os.cpu_count() or 1
-    # 2 x 2 level-0 cells at full density: the only parallelism the algorithm has is across level-0 cells
-    threads = min(4, cores)
-    side = 2000.0
-    n = int(DENSITY * side * side * args.cpu_scale)
+    n = max(10_000, int(args.points * args.cpu_scale))
+    kind = "terrain" if args.workload == "merge" else args.workload
+    pts = cpu_cloud(kind, n)
+    ncell0 = len(np.unique(np.floor(pts.view(np.uint8).reshape(-1, 16)[:, :12].copy().view(np.float32).reshape(-1, 3) /
+                                    np.float32(1000.0)).astype(np.int64), axis=0))
+    threads = max(1, min(cores, ncell0, 32))
+    out_dir = None
+    tmp = None
+    if args.workload == "merge":   # C3: the existing tree is built first, outside the timed part
+        tmp = tempfile.mkdtemp(prefix="pcb_ref_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+        out_dir = tmp
+        cpu_oracle_run(pts, 1, out_dir=out_dir)
+        import synth
+        pts = synth.terrain(n, 3, "cpu", terrain_extent(n), surface_seed=2).numpy()
+        threads = 1   # the merge run re-reads node files: the oracle's worker split is for fresh runs
     vals = []
-    for _ in range(max(1, min(args.steps, 2))):
-        v, dt = cpu_oracle_run(n, (-1000.0, -1000.0 + side, -1000.0, -1000.0 + side), threads)
+    for _ in range(max(1, min(args.steps, 1 if n > 20_000_000 else 2))):
+        v, dt = cpu_oracle_run(pts, threads, out_dir=out_dir)
         vals.append((v, dt))
+        if out_dir:
+            break
+    if tmp:
+        shutil.rmtree(tmp, ignore_errors=True)
     v = statistics.median([x[0] for x in vals])
     dt = statistics.median([x[1] for x in vals])
-    sample = (f"{n} points of the same terrain generator at the workload's density ({DENSITY}/m^2) over 2x2 "
-              f"level-0 cells, {threads} threads (one per level-0 cell)")
+    sample = (f"{n} points = {'the full' if n == args.points else 'a sample of the'} single-GPU workload, same generator on the "
+              f"host ({ncell0} level-0 cells), {threads} thread(s): one per level-0 cell, the only parallelism the "
+              f"reference's algorithm has (its CLI is single-threaded)")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": round(v, 4), "unit": UNIT, "n_gpus": args.gpus,
         "steps": len(vals), "warmup": 0, "ms_per_step": round(dt * 1e3, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32+u64", "data": "synthetic",
-        "config": {"workload": workload_name(args.points), "points_per_gpu": args.points,
+        "config": {"workload": workload_name(args.points, args.workload), "points_per_gpu": args.points,
                    "sample_points": n, "sample": sample},
         "cpu_baseline": {"value": round(v, 4), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": round(v, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
+
+
+def write_ply(path, pts_np):
+    """binary little-endian PLY (float x, y, z; uchar red, green, blue) of (n, 16) uint8 records"""
+    import numpy as np
+    n = len(pts_np)
+    hdr = ("ply\nformat binary_little_endian 1.0\nelement vertex %d\nproperty float x\nproperty float y\n"
+           "property float z\nproperty uchar red\nproperty uchar green\nproperty uchar blue\nend_header\n" % n)
+    with open(path, "wb") as f:
+        f.write(hdr.encode())
+        step = 1 << 24
+        for s in range(0, n, step):
+            f.write(np.ascontiguousarray(pts_np[s:s + step, :15]).tobytes())
 
 
 def main():
@@ -176,13 +249,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--points", type=int, default=100_000_000, help="points per GPU (C2 = 1e8)")
-    ap.add_argument("--workload", default="terrain", choices=["terrain", "city", "blobs"],
-                    help="terrain = C2 (the bench line); city = C5 scan of a fixed 10 km x 10 km city, blobs = C4 (extra runs)")
-    ap.add_argument("--e2e-steps", type=int, default=2)
-    ap.add_argument("--cpu-scale", type=float, default=1.0, help="scales the bounded CPU sample")
+    ap.add_argument("--workload", default="terrain", choices=["terrain", "city", "blobs", "cube", "merge"],
+                    help="terrain = C2 (the bench line); cube = C1-shaped; merge = C3 (N = 1); blobs = C4; city = C5")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-scale", type=float, default=1.0, help="scales the CPU legs (1.0 = the full workload)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-files", action="store_true", help="skip the e2e_files legs (tmpfs node files, cold CLI process)")
+    ap.add_argument("--no-check", action="store_true", help="skip the verified step at N > 1")
+    ap.add_argument("--check", action="store_true", help="run the verified step at N = 1 as well")
     ap.add_argument("--no-profile", action="store_true", help="debug: no per-kernel CUDA events in the timed steps")
-    ap.add_argument("--no-clocks", action="store_true", help="debug: do not run the nvidia-smi sampler")
+    ap.add_argument("--no-clocks", action="store_true", help="debug: do not run the clock sampler")
     ap.add_argument("--host-log", action="store_true", help="debug: per-step host times (open, finish, close) on stderr")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -193,32 +269,41 @@ def main():
         run_reference(args, rank, world)
         return
 
+    import numpy as np
     import torch
     import torch.distributed as dist
     import synth
-    from pcutil import load_pcb
+    from pcutil import load_pcb, records_digest, combine_digests, check_tree_cells
     pcb = load_pcb()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    if args.workload == "merge" and world > 1:
+        raise SystemExit("--workload merge is the single-GPU config C3")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
     n = args.points
-    # Weak scaling: the undivided stream is world * n points of the same terrain over an extent that grows with
-    # the world size (same density); rank r holds the index range [r*n, (r+1)*n) of it, i.e. random points of the
-    # WHOLE extent, so (world-1)/world of them must cross NVLink to reach the owner of their level-0 cell.
-    side_x = (n / DENSITY) ** 0.5 * world
-    side_y = (n / DENSITY) ** 0.5
-    if args.workload == "city":   # C5: every rank holds random samples of the WHOLE city
-        pts = synth.city(n, 5, dev, sample_seed=50 + rank)
-    elif args.workload == "blobs":   # C4: every rank holds random samples of the same 64 blobs
-        pts = synth.gaussian_blobs(n, 4, dev, sample_seed=40 + rank)
-    else:
-        pts = synth.terrain(n, 2 + rank, dev, (-side_x / 2, side_x / 2, -side_y / 2, side_y / 2), surface_seed=2)
+    pts = make_cloud(args.workload, n, rank, world, dev)
     torch.cuda.synchronize()
     stream = torch.cuda.current_stream()
+    shm = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    scratch_dir = tempfile.mkdtemp(prefix=f"pcb_bench_r{rank}_", dir=shm)
+    merge_dir = None
+    if args.workload == "merge":
+        # C3: the existing output (seed-2 samples of the surface) is built to tmpfs OUTSIDE the timed region; the
+        # timed step merges `pts` (seed-3 samples) into it.  PCB_FLAG_NO_FILES / DEVICE_ONLY leave the directory
+        # untouched, so every step merges into the same existing tree.
+        merge_dir = os.path.join(scratch_dir, "existing")
+        base = synth.terrain(n, 2, dev, terrain_extent(n), surface_seed=2)
+        pts = synth.terrain(n, 3, dev, terrain_extent(n), surface_seed=2)
+        with pcb.Converter(merge_dir, device=local_rank) as cv:
+            cv.begin_file()
+            cv.add_points(base.cpu().numpy())
+            cv.finish()
+        del base
+        torch.cuda.empty_cache()
     shard = None
     if world > 1:
         import importlib.util
@@ -229,8 +314,8 @@ def main():
     exchange = [""]
 
     def ingest(cv, src):
-        """single GPU: the resident stream as is; N GPUs: level-0 exchange (libpcb routing kernels + NCCL
-        all-to-all-v), then the routed points with their global batch ordinals."""
+        """single GPU: the resident stream as is; N GPUs: level-0 exchange (libpcb routing kernels, stores over NVLink
+        or NCCL all-to-all-v), then the routed points with their global batch ordinals."""
         if world == 1:
             cv.begin_file()
             cv.add_points_device(src.data_ptr(), n)
@@ -246,7 +331,7 @@ def main():
     def step(profile=not args.no_profile):
         flags = pcb.FLAG_DEVICE_ONLY | (pcb.FLAG_PROFILE if profile else 0)
         t0 = time.perf_counter()
-        cv = pcb.Converter(None, device=local_rank, flags=flags)
+        cv = pcb.Converter(merge_dir, device=local_rank, flags=flags)
         try:
             cv.set_stream(stream.cuda_stream)
             keep = ingest(cv, pts)
@@ -312,39 +397,54 @@ def main():
         print("host_log (open, finish, close) ms:", host_log[-args.steps:], file=sys.stderr)
     value = n * world / (ms_per_step * 1e-3) / 1e6
 
-    # ---- e2e: host buffers through the C ABI (H2D + build + D2H of every node image)
+    # ---- e2e: host buffers through the C ABI (H2D + [exchange] + build + D2H of every node image)
     e2e = None
+    host = None
     if args.e2e_steps > 0:
         host = torch.empty((n, 16), dtype=torch.uint8, pin_memory=True)
         host.copy_(pts)
         torch.cuda.synchronize()
         hnp = host.numpy()
         stage = torch.empty_like(pts) if world > 1 else None
-        times, d2h = [], 0
+        times, d2h, phases = [], 0, []
 
         def e2e_step():
-            cv = pcb.Converter(None, device=local_rank, flags=pcb.FLAG_NO_FILES)
+            cv = pcb.Converter(merge_dir, device=local_rank, flags=pcb.FLAG_NO_FILES)
             try:
+                ph = {}
+                t0 = time.perf_counter()
                 if world == 1:
                     cv.reserve(n)
                     cv.begin_file()
                     cv.add_points(hnp)
+                    st = cv.finish()
+                    ph = {"h2d": st.h2d_seconds * 1e3, "build": st.build_seconds * 1e3, "d2h_tail": st.d2h_seconds * 1e3}
                 else:   # host slice -> device, exchange, build
                     cv.set_stream(stream.cuda_stream)
+                    ea, eb, ec = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+                    ea.record(stream)
                     stage.copy_(host, non_blocking=True)
+                    eb.record(stream)
                     keep = ingest(cv, stage)
-                st = cv.finish()
-                return st
+                    ec.record(stream)
+                    t1 = time.perf_counter()
+                    st = cv.finish()
+                    torch.cuda.synchronize()
+                    ph = {"h2d": ea.elapsed_time(eb), "route": eb.elapsed_time(ec), "route_host_wall": (t1 - t0) * 1e3,
+                          "build": st.build_seconds * 1e3, "d2h_tail": st.d2h_seconds * 1e3}
+                return st, ph
             finally:
                 cv.close()
 
-        e2e_step()  # warm-up (pinned staging cache, memory pool)
+        e2e_step()  # warm-up (pinned staging cache, arenas)
         barrier()
         for _ in range(args.e2e_steps):
+            barrier()
             t0 = time.perf_counter()
-            st = e2e_step()
+            st, ph = e2e_step()
             torch.cuda.synchronize()
             times.append(time.perf_counter() - t0)
+            phases.append(ph)
             d2h = int(st.node_bytes)
         t = statistics.median(times)
         if world > 1:
@@ -352,8 +452,105 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             t = float(tt.item())
         e2e = {"value": round(n * world / t / 1e6, 3), "unit": UNIT, "h2d_bytes_per_step": 16 * n,
-               "d2h_bytes_per_step": d2h, "ms_per_step": round(t * 1e3, 2)}
-        del host
+               "d2h_bytes_per_step": d2h, "ms_per_step": round(t * 1e3, 2),
+               "phases_ms": {k: round(statistics.median(p[k] for p in phases), 2) for k in phases[0]},
+               "phases_note": "rank 0; h2d / route = device time, build = host wall of the level loop (waves overlap the "
+                              "image download), d2h_tail = wait for the last images after the build"}
+
+    # ---- check (N > 1, or --check): one verified step outside the timed region
+    check = None
+    if (world > 1 and not args.no_check) or args.check:
+        s64 = lambda v: v - (1 << 64) if v >= (1 << 63) else v   # noqa: E731 - u64 digests travel as int64
+        mine, src, err = (0, 0, 0), (0, 0, 0), ""
+        cv = pcb.Converter(None, device=local_rank, flags=pcb.FLAG_NO_FILES)
+        try:
+            cv.set_stream(stream.cuda_stream)
+            keep = ingest(cv, pts)       # collective at N > 1: outside the try block below
+            st = cv.finish()
+            try:
+                nodes = cv.nodes()
+                mine = check_tree_cells(nodes)   # raises if a stored point lies outside its node's cell, bad headers ...
+                del nodes
+                src = records_digest(pts.cpu().numpy())
+            except Exception as e:   # noqa: BLE001 - reported in the line, fails the run
+                err = f"{type(e).__name__}: {e}"
+        finally:
+            cv.close()
+        vec = torch.tensor([mine[0], s64(mine[1]), s64(mine[2]), src[0], s64(src[1]), s64(src[2]), 1 if err else 0],
+                           dtype=torch.int64, device=dev)
+        allv = [torch.zeros_like(vec) for _ in range(world)]
+        if world > 1:
+            dist.all_gather(allv, vec)
+        else:
+            allv = [vec]
+        stored, inputs, nerr = (0, 0, 0), (0, 0, 0), 0
+        for v in allv:
+            x = [int(q) & 0xFFFFFFFFFFFFFFFF for q in v.tolist()]
+            stored = combine_digests(stored, (x[0], x[1], x[2]))
+            inputs = combine_digests(inputs, (x[3], x[4], x[5]))
+            nerr += x[6]
+        ok = nerr == 0 and stored == inputs and stored[0] == n * world
+        detail = {"records": stored[0], "digest_equal": stored == inputs, "ranks_with_errors": nerr,
+                  "what": "count / sum / xor of a 64-bit mix of every stored 16-byte record over all ranks == the same "
+                          "over all input records; every stored point inside its node's cell; header totals add up; no "
+                          "overflow list beyond the limit"}
+        if err:
+            detail["error"] = err
+        if world > 1 and world <= 8:
+            # fused NVLink exchange against the NCCL all-to-all-v path on every rank's first 1 M points
+            m = min(n, 1_000_000)
+            sl = pts[:m].contiguous()
+            was = shard._P2P["enabled"]
+            p1, b1, i1 = shard.route_device(pcb, sl, rank * m, 10_000, 1000.0, stream=stream)
+            p1, b1 = p1.clone(), b1.clone()
+            shard._P2P["enabled"] = False
+            p2, b2, i2 = shard.route_device(pcb, sl, rank * m, 10_000, 1000.0, stream=stream)
+            shard._P2P["enabled"] = was
+            same = bool(p1.shape == p2.shape and torch.equal(p1, p2) and torch.equal(b1, b2))
+            flag = torch.tensor([1 if same else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            detail["exchange_paths_equal"] = bool(flag.item())
+            detail["exchange_paths"] = [i1.get("exchange", ""), i2.get("exchange", "")]
+            ok = ok and bool(flag.item())
+        check = {"result": "ok" if ok else "FAILED", **detail}
+
+    # ---- e2e_files (N = 1): host buffer -> node files + metadata.json on tmpfs, warm and cold process
+    e2e_files = None
+    if world == 1 and not args.no_files and host is not None and args.workload != "merge":
+        try:
+            warm = []
+            for i in range(3):
+                d = os.path.join(scratch_dir, f"warm{i}")
+                t0 = time.perf_counter()
+                with pcb.Converter(d, device=local_rank) as cv:
+                    cv.reserve(n)
+                    cv.begin_file()
+                    cv.add_points(hnp)
+                    stf = cv.finish()
+                warm.append(time.perf_counter() - t0)
+                shutil.rmtree(d, ignore_errors=True)
+            tw = statistics.median(warm[1:])
+            ply = os.path.join(scratch_dir, "cloud.ply")
+            write_ply(ply, hnp)
+            cli = ROOT / "point-cloud_b200" / "point_converter"
+            cold = None
+            if cli.exists():
+                d = os.path.join(scratch_dir, "cold")
+                t0 = time.perf_counter()
+                r = subprocess.run([str(cli), "-o", d, "-f", ply, "--device", str(local_rank)], capture_output=True, text=True)
+                cold = time.perf_counter() - t0
+                if r.returncode != 0:
+                    cold = None
+                shutil.rmtree(d, ignore_errors=True)
+            os.remove(ply)
+            e2e_files = {"unit": UNIT, "fs": "tmpfs" if shm else "tmp", "warm_value": round(n / tw / 1e6, 2),
+                         "warm_ms": round(tw * 1e3, 1), "write_ms": round(stf.write_seconds * 1e3, 1),
+                         "cold_cli_value": round(n / cold / 1e6, 2) if cold else None,
+                         "cold_cli_ms": round(cold * 1e3, 1) if cold else None,
+                         "cold_cli": "fresh point_converter process: PLY on tmpfs -> read -> H2D -> build -> node files + "
+                                     "metadata.json on tmpfs (CUDA context, arenas and pinned staging created inside)"}
+        except Exception as e:   # noqa: BLE001
+            e2e_files = {"error": f"{type(e).__name__}: {e}"}
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -366,21 +563,27 @@ def main():
             tp = ROOT / "profiles" / "traffic.json"
             if tp.exists():
                 traffic = json.loads(tp.read_text()).get(name)
+            kernel_ms = sum(v["ms"] for v in kstats.values())
+            kernel_bytes = sum(v["bytes"] for v in kstats.values())
             roofline = {"bound": "hbm", "kernel": name, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                         "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                         "launches": d["launches"], "avg_ms": round(d["ms"] / max(1, d["launches"]), 4),
                         "step_share": round(d["ms"] / ms, 4),
+                        "kernel_sum": {"GBps": round(kernel_bytes / max(kernel_ms, 1e-9) / 1e6, 1),
+                                       "frac": round(kernel_bytes / max(kernel_ms, 1e-9) / 1e6 / peak, 4),
+                                       "bytes_per_arrival": round(kernel_bytes / args.steps / max(1, last.arrivals), 1)},
+                        "whole_path_32B_per_point": {"GBps": round(32.0 * n / (ms_per_step * 1e-3) / 1e9, 1),
+                                                     "frac": round(32.0 * n / (ms_per_step * 1e-3) / 1e9 / peak, 4)},
                         "kernels": {k: {"ms_per_step": round(v["ms"] / args.steps, 3),
                                         "GBps": round(v["bytes"] / max(v["ms"], 1e-9) / 1e6, 1)} for k, v in
                                     sorted(kstats.items(), key=lambda kv: -kv[1]["ms"])}}
         cpu = None
-        if not args.no_cpu:
-            ncpu = int(DENSITY * 3000.0 * 1000.0 * args.cpu_scale)
-            v, dt = cpu_oracle_run(ncpu, (0.0, 3000.0, 0.0, 1000.0), 1)
+        if not args.no_cpu and args.workload != "merge":
+            ncpu = max(10_000, int(n * args.cpu_scale))
+            v, dt = cpu_oracle_run((host.numpy() if host is not None else pts.cpu().numpy())[:ncpu], 1)
             cpu = {"value": round(v, 4), "unit": UNIT, "cores": 1, "kind": "port", "seconds": round(dt, 2),
-                   "sample": f"{ncpu} points: three level-0 cells (3 km x 1 km) of the same terrain generator at the "
-                             f"workload's density ({DENSITY}/m^2); sequential oracle = the reference CLI's own "
-                             f"concurrency (single-threaded)"}
+                   "sample": f"{ncpu} points: {'the full workload, the very bytes the GPU converted' if ncpu == n else 'the first records of the workload'}"
+                             f"; sequential oracle = the reference CLI's own concurrency (single-threaded), cells in RAM"}
         out = {"metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                "warmup": args.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True,
                "scaling": "weak", "vs_baseline": None, "dtype": "f32+u64", "data": "synthetic",
@@ -392,9 +595,21 @@ def main():
                           **({"ranks": ranks_info} if ranks_info else {})},
                "e2e": e2e, "gpu_launches": int(launches) + route_timed, "roofline": roofline, "cpu_baseline": cpu,
                "clocks": clocks}
+        if e2e_files is not None:
+            out["e2e_files"] = e2e_files
+        if check is not None:
+            out["check"] = check["result"]
+            out["check_detail"] = check
         print(json.dumps(out))
+    shutil.rmtree(scratch_dir, ignore_errors=True)
+    failed = check is not None and check["result"] != "ok"
     if world > 1:
+        f = torch.tensor([1 if failed else 0], device=dev)
+        dist.all_reduce(f, op=dist.ReduceOp.MAX)
+        failed = bool(f.item())
         dist.destroy_process_group()
+    if failed:
+        sys.exit(3)
 
 
 if __name__ == "__main__":

@@ -20,6 +20,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <list>
 #include <map>
 #include <memory>
 #include <optional>
@@ -236,6 +237,13 @@ struct Converter {
     std::unordered_map<CellId, std::unique_ptr<Cell>, CellIdHash> cells;
     uint64_t arrivals = 0;          // statistic: sum over levels of delivered points
     int error = 0;                  // 1 = hierarchy >= 32 (reference would overflow 2u32.pow)
+    // Optional residency emulation of converter.rs:92, 160-178: at most lru_capacity cells in RAM (the reference
+    // uses LRUCache::with_hasher(100, ..)); a miss loads the node file or creates the cell, the evicted cell is
+    // written out whole (save_cell).  0 = keep everything in RAM (the default; results are identical either way).
+    size_t lru_capacity = 0;
+    std::list<CellId> lru_order;    // front = most recently used
+    std::unordered_map<CellId, std::list<CellId>::iterator, CellIdHash> lru_pos;
+    uint64_t lru_evictions = 0, lru_loads = 0;
 
     void update_bounding_box(const std::vector<Point>& points);  // converter.rs:96-104
     void add_points_batch(const std::vector<Point>& points);     // converter.rs:106-112

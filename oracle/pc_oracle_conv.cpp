@@ -117,13 +117,37 @@ void Converter::create_hierarchy_folder(uint32_t hierarchy) {
 // converter.rs:160-207 — cache miss: read the node file, NotFound => Cell::new.
 Cell& Converter::get_cell_mut(const CellId& id) {
     auto it = cells.find(id);
-    if (it != cells.end()) return *it->second;
+    if (it != cells.end()) {
+        if (lru_capacity) {   // LRUCache::get_mut refreshes the entry (converter.rs:176-178)
+            auto pos = lru_pos.find(id);
+            lru_order.splice(lru_order.begin(), lru_order, pos->second);
+        }
+        return *it->second;
+    }
     auto cell = std::make_unique<Cell>();
     bool loaded = false;
     if (!working_directory.empty()) {
         std::vector<uint8_t> bytes;
-        if (read_file(working_directory + "/" + cell_path(id), &bytes))
+        if (read_file(working_directory + "/" + cell_path(id), &bytes)) {
             loaded = Cell::read_from(bytes.data(), bytes.size(), cell.get());
+            lru_loads += loaded ? 1 : 0;
+        }
+    }
+    if (lru_capacity) {
+        if (!loaded) cell->points_grid.reserve(50000);   // Cell::new(.., 50_000), converter.rs:199
+        if (cells.size() >= lru_capacity) {   // PutResult::Evicted => save_cell (converter.rs:166-173)
+            const CellId victim = lru_order.back();
+            lru_order.pop_back();
+            lru_pos.erase(victim);
+            auto vit = cells.find(victim);
+            std::vector<uint8_t> buf;
+            vit->second->write_to(buf);
+            if (!write_file(working_directory + "/" + cell_path(victim), buf.data(), buf.size())) error |= 2;
+            cells.erase(vit);
+            lru_evictions++;
+        }
+        lru_order.push_front(id);
+        lru_pos[id] = lru_order.begin();
     }
     if (!loaded) {
         float cell_size = metadata.config.cell_size(id.hierarchy);
@@ -575,6 +599,20 @@ int orc_metadata_json(void* hv, char* buf, uint64_t cap) {
 }
 
 void orc_close(void* hv) { delete (OrcHandle*)hv; }
+
+// The reference CLI's cell residency (converter.rs:92: LRU of 100 cells, evicted cells rewritten whole, misses
+// re-read and re-hashed).  Needs an output directory; single-threaded runs only.  Returns 0 on success.
+int orc_set_lru(void* hv, uint32_t capacity) {
+    auto* h = (OrcHandle*)hv;
+    if (h->conv.working_directory.empty() || h->threads > 1 || !h->conv.cells.empty()) return -1;
+    h->conv.lru_capacity = capacity;
+    return 0;
+}
+void orc_lru_stats(void* hv, uint64_t* evictions, uint64_t* loads) {
+    auto* h = (OrcHandle*)hv;
+    *evictions = h->conv.lru_evictions;
+    *loads = h->conv.lru_loads;
+}
 
 // --- primitive probes for known-answer tests -------------------------------
 float orc_cell_size(uint32_t limit, uint32_t dim, float max_cell_size, uint32_t h) {

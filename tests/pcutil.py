@@ -59,6 +59,8 @@ def oracle_lib():
         L.orc_hex_d2.restype = C.c_float
         L.orc_hex_d2.argtypes = [C.c_void_p, C.c_float]
         L.orc_format_f32.argtypes = [C.c_float, C.c_char_p, C.c_uint64]
+        L.orc_set_lru.argtypes = [C.c_void_p, C.c_uint32]
+        L.orc_lru_stats.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _orc = L
     return _orc
 
@@ -96,14 +98,18 @@ class OracleRun:
 
 
 def oracle_convert(files, out_dir: Optional[str] = None, config=None, batch_size=10_000, threads=1,
-                   dump=True) -> OracleRun:
-    """files: list of point arrays, each one input file (lib.rs:17-52)."""
+                   dump=True, lru=0) -> OracleRun:
+    """files: list of point arrays, each one input file (lib.rs:17-52).  lru > 0: emulate the reference CLI's
+    cell residency (converter.rs:92: LRU of `lru` cells spilling whole node files to out_dir); the dump then only
+    holds the cells still resident - read the tree from out_dir instead."""
     L = oracle_lib()
     h = L.orc_open(out_dir.encode() if out_dir else None, batch_size, threads)
     assert h, "oracle failed to open (bad metadata.json?)"
     try:
         if config is not None:
             L.orc_set_config(h, int(config[0]), int(config[1]), float(config[2]))
+        if lru:
+            assert L.orc_set_lru(h, int(lru)) == 0, "LRU emulation needs an output directory and one thread"
         for f in files:
             a = as_points(f)
             rc = L.orc_add_file(h, a.ctypes.data if len(a) else None, len(a))
@@ -235,6 +241,43 @@ def sort_records(rec: np.ndarray) -> np.ndarray:
     if len(rec) == 0:
         return rec
     return rec[np.lexsort(rec.T[::-1])]
+
+
+def records_digest(rec: np.ndarray):
+    """Order-independent digest of 16-byte records: (count, sum and xor of a 64-bit mix of both halves)."""
+    w = np.ascontiguousarray(rec).view(np.uint64).reshape(-1, 2)
+    with np.errstate(over="ignore"):
+        h = (w[:, 0] * np.uint64(0x9E3779B97F4A7C15)) ^ (w[:, 1] * np.uint64(0xC2B2AE3D27D4EB4F))
+        h ^= h >> np.uint64(29)
+        h *= np.uint64(0xBF58476D1CE4E5B9)
+        h ^= h >> np.uint64(32)
+        return len(w), int(h.sum(dtype=np.uint64)), int(np.bitwise_xor.reduce(h)) if len(h) else 0
+
+
+def combine_digests(a, b):
+    return a[0] + b[0], (a[1] + b[1]) & 0xFFFFFFFFFFFFFFFF, a[2] ^ b[2]
+
+
+def check_tree_cells(nodes: Dict[str, bytes], limit=5000, max_cell=1000.0):
+    """Size-independent properties of a converted tree: header accounting, overflow lists within the limit, every
+    stored point inside its node's cell under the reference's f32 division (metadata.rs:100-102).  Returns the digest
+    of all stored records."""
+    import re
+    total = (0, 0, 0)
+    for path, data in nodes.items():
+        m = re.fullmatch(r"h_(\d+)/c_(-?\d+)_(-?\d+)_(-?\d+)\.bin", path)
+        h, idx = int(m.group(1)), np.array([int(m.group(k)) for k in (2, 3, 4)], dtype=np.int64)
+        nd = Node(data)
+        lists = [v for v in nd.entries.values() if v is not None]
+        assert all(len(v) <= limit for v in lists), f"{path}: overflow list longer than the limit"
+        stored = np.concatenate([nd.grid] + lists, axis=0) if lists else nd.grid
+        assert int(nd.header["total"]) == len(stored) and int(nd.header["npoints"]) == len(nd.grid), path
+        size = np.float32(max_cell) / np.float32(2 ** h)
+        xyz = np.ascontiguousarray(stored[:, :12]).view(np.float32).reshape(-1, 3)
+        cell = np.floor(xyz / size).astype(np.int64)
+        assert np.all(cell == idx[None, :]), f"{path}: a stored point lies outside the node's cell"
+        total = combine_digests(total, records_digest(stored))
+    return total
 
 
 def load_pcb():

@@ -11,47 +11,16 @@ import pytest
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT / "tests"))
 sys.path.insert(0, str(ROOT / "point-cloud_b200"))
-from pcutil import Node, load_pcb  # noqa: E402
+from pcutil import Node, check_tree_cells, load_pcb, records_digest as _digest  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 N_FULL = 100_000_000
 LIMIT, DIM, MAX_CELL = 5000, 96, np.float32(1000.0)
 
 
-def _digest(rec: np.ndarray):
-    """Order-independent digest of 16-byte records: (count, sum and xor of a 64-bit mix of both halves)."""
-    w = np.ascontiguousarray(rec).view(np.uint64).reshape(-1, 2)
-    with np.errstate(over="ignore"):
-        h = (w[:, 0] * np.uint64(0x9E3779B97F4A7C15)) ^ (w[:, 1] * np.uint64(0xC2B2AE3D27D4EB4F))
-        h ^= h >> np.uint64(29)
-        h *= np.uint64(0xBF58476D1CE4E5B9)
-        h ^= h >> np.uint64(32)
-        return len(w), int(h.sum(dtype=np.uint64)), int(np.bitwise_xor.reduce(h)) if len(h) else 0
-
-
-def _combine(a, b):
-    return a[0] + b[0], (a[1] + b[1]) & 0xFFFFFFFFFFFFFFFF, a[2] ^ b[2]
-
-
 def _check_tree(nodes, expect_digest, n_points):
-    total = (0, 0, 0)
-    header_total = 0
-    for path, data in nodes.items():
-        m = re.fullmatch(r"h_(\d+)/c_(-?\d+)_(-?\d+)_(-?\d+)\.bin", path)
-        h, idx = int(m.group(1)), np.array([int(m.group(k)) for k in (2, 3, 4)], dtype=np.int64)
-        nd = Node(data)
-        lists = [v for v in nd.entries.values() if v is not None]
-        assert all(len(v) <= LIMIT for v in lists), f"{path}: overflow list longer than the limit"
-        stored = np.concatenate([nd.grid] + lists, axis=0) if lists else nd.grid
-        assert int(nd.header["total"]) == len(stored) and int(nd.header["npoints"]) == len(nd.grid), path
-        header_total += int(nd.header["total"])
-        # every stored point lies in this node's cell: floor(p / cell_size(h)) with the reference's f32 division
-        size = MAX_CELL / np.float32(2 ** h)
-        xyz = np.ascontiguousarray(stored[:, :12]).view(np.float32).reshape(-1, 3)
-        cell = np.floor(xyz / size).astype(np.int64)
-        assert np.all(cell == idx[None, :]), f"{path}: a stored point lies outside the node's cell"
-        total = _combine(total, _digest(stored))
-    assert header_total == n_points == total[0]
+    total = check_tree_cells(nodes, LIMIT, MAX_CELL)
+    assert total[0] == n_points
     assert total == expect_digest, "multiset of stored points differs from the input"
 
 

@@ -263,3 +263,23 @@ def test_empty_batch_still_visits_level_zero():
     # converter.rs:111,120: add_points_in_hierarchy(0, ..) runs create_hierarchy_folder(0) unconditionally
     o = oracle_convert([make_points(np.zeros((0, 3)))])
     assert o.hierarchies == 1 and o.number_of_points == 0 and not o.nodes
+
+
+def test_lru_residency_is_transparent(tmp_path):
+    """converter.rs:92, 160-178: the reference keeps at most 100 cells in RAM and spills evicted cells as whole node
+    files.  The oracle's emulation of that (used by bench.py's "what the real CLI pays" CPU line) must not change a
+    single byte of the result: a capacity of 3 cells against everything-in-RAM, fresh run and merge run."""
+    from pcutil import compare_trees, read_tree
+    rng = np.random.default_rng(5)
+    a = make_points(rng.random((30_000, 3)) * 90 - 45)
+    b = make_points(rng.random((20_000, 3)) * 120 - 60)
+    cfg = (60, 8, 32.0)
+    d0, d1 = str(tmp_path / "ram"), str(tmp_path / "lru")
+    oracle_convert([a], out_dir=d0, config=cfg, batch_size=1000, dump=False)
+    oracle_convert([b], out_dir=d0, batch_size=1000, dump=False)
+    oracle_convert([a], out_dir=d1, config=cfg, batch_size=1000, dump=False, lru=3)
+    oracle_convert([b], out_dir=d1, batch_size=1000, dump=False, lru=3)
+    t0, t1 = read_tree(d0), read_tree(d1)
+    assert len(t0) > 20
+    compare_trees(t0, t1, "in-ram", "lru-3")
+    assert open(d0 + "/metadata.json").read() == open(d1 + "/metadata.json").read()
