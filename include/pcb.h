@@ -115,7 +115,11 @@ int pcb_reserve(pcb_handle* h, uint64_t n);
    caller's CUDA events bracket it.  Call right after pcb_open. */
 int pcb_set_stream(pcb_handle* h, void* cuda_stream);
 /* Same, but `d_pts` is a device pointer on the handle's device (resident-input path).  When it is the first
-   add on the handle the buffer is aliased, not copied: keep it valid and unchanged until pcb_finish returns. */
+   add on the handle the buffer is aliased, not copied: keep it valid and unchanged until pcb_finish returns.
+   STREAM ORDER: the handle works on its own non-blocking stream unless pcb_set_stream gave it the caller's.  Borrowed
+   device inputs (this call and pcb_add_points_device_batched) must be COMPLETE on the handle's stream when the call is
+   made: produce them on the stream passed to pcb_set_stream, or synchronise the producer stream first.  The library
+   inserts no cross-stream dependency of its own. */
 int pcb_add_points_device(pcb_handle* h, const pcb_point* d_pts, uint64_t n);
 /* Multi-GPU ingest: points that were routed to this device by the level-0 exchange, still in the order of the
    undivided input stream, each with the ordinal (0-based, global) of the batch it belonged to (lib.rs:31-35 cut

@@ -181,14 +181,30 @@ def _p2p_buffers(dev, group, cap):
     """Symmetric receive buffer for `cap` points: [cap x 16 B points][cap x 4 B batch ordinals].  Collective."""
     if _P2P["buf"] is not None and _P2P["cap"] >= cap:
         return _P2P["buf"], _P2P["hdl"], _P2P["cap"]
+    # (Re)allocation: `cap` derives from all-gathered counts and the cached capacity has the same history on every rank,
+    # so every rank takes this branch together.  The allocation or the rendezvous can still fail on ONE rank only; the
+    # ranks therefore agree on the outcome (all-reduce MIN of an ok flag) and fall back to NCCL together or not at all -
+    # a rank that fell back alone would enter all_to_all_single while its peers wait in the symmetric-memory barrier.
+    why, buf, hdl, ptrs = None, None, None, None
     try:
         import torch.distributed._symmetric_memory as symm
         cap = (int(cap * 1.1) + 4095) // 4096 * 4096
         buf = symm.empty(cap * 20, dtype=torch.uint8, device=dev)
+    except Exception as e:   # noqa: BLE001 - anything here means "no peer-mapped memory on this system"
+        why = f"{type(e).__name__}: {e}"
+    ok = torch.tensor([0 if why else 1], dtype=torch.int32, device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+    if not bool(ok.item()):
+        raise _P2PUnavailable(why or "symmetric memory unavailable on a peer rank")
+    try:   # collective; every rank is here
         hdl = symm.rendezvous(buf, group if group is not None else dist.group.WORLD)
         ptrs = list(hdl.buffer_ptrs)
-    except Exception as e:   # noqa: BLE001 - anything here means "no peer-mapped memory on this system"
-        raise _P2PUnavailable(f"{type(e).__name__}: {e}") from e
+    except Exception as e:   # noqa: BLE001
+        why = f"{type(e).__name__}: {e}"
+    ok = torch.tensor([0 if why else 1], dtype=torch.int32, device=dev)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+    if not bool(ok.item()):
+        raise _P2PUnavailable(why or "symmetric-memory rendezvous failed on a peer rank")
     _P2P.update(buf=buf, hdl=hdl, cap=cap, ptrs=ptrs)
     return buf, hdl, cap
 
@@ -215,6 +231,8 @@ def _route_scatter_p2p(pcb, pts_u8, first_index, batch_size, max_cell_size, orig
         nl = pcb.route_scatter(dev.index, st.cuda_stream, pts_u8.data_ptr(), n, first_index, batch_size, max_cell_size,
                                origin, dims, owner_dev.data_ptr(), world, ptrs, [p + cap * 16 for p in ptrs], offs)
         hdl.barrier(channel=0)                     # every rank's stores have landed
+    # NOTE: views of the persistent symmetric buffer - the next route_device call on ANY rank overwrites them (after its
+    # entry barrier).  Consume them (pcb_finish) or copy them before routing again.
     recv_pts = buf[:m * 16].view(m, 16)
     recv_bat = buf[cap * 16:cap * 16 + m * 4].view(torch.int32)
     mark("scatter (partition + exchange)")
