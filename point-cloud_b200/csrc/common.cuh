@@ -29,6 +29,7 @@ typedef int32_t i32;
 #define PCB_DERR_L0RANGE 2u     // level-0 cell index outside +-2^20
 #define PCB_DERR_HEXRANGE 4u    // hex key outside the per-cell window (coordinate precision exhausted)
 #define PCB_DERR_NEST 8u        // child index does not nest in its parent (SURVEY N1 violated)
+#define PCB_DERR_TIMEOUT 16u    // a look-back waited too long for an earlier tile (blocks not dispatched in order?)
 
 struct __align__(16) PcbPoint {
     float x, y, z;

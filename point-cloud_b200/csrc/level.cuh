@@ -246,7 +246,8 @@ struct L0SplitSmem {
 __global__ void __launch_bounds__(L0S_THREADS, 4)   // 64 registers, four blocks per SM (three: 1.63 ms, four: 1.37 ms per 100 M points)
 k_l0_split(const PcbPoint* __restrict__ in_pts, u32 n, float S0, L0Box box, u32 nb, int bits,
            const u32* __restrict__ dbase, const BatchSeg* __restrict__ segs, u32 nseg, const u32* __restrict__ in_bat,
-           PcbPoint* __restrict__ pts, u32* __restrict__ bat, u32* __restrict__ status /* [ntiles][nb] */) {
+           PcbPoint* __restrict__ pts, u32* __restrict__ bat, u32* __restrict__ status /* [ntiles][nb] */,
+           u32* __restrict__ err = nullptr) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint4* s_pts = (uint4*)smem_raw;
     u32* s_idx = (u32*)(s_pts + L0S_TILE);
@@ -368,7 +369,14 @@ k_l0_split(const PcbPoint* __restrict__ in_pts, u32 n, float S0, L0Box box, u32 
                     for (int x = 0; x < RADIX_WINDOW; x++) {
                         if (!done) {
                             u32 sw = w[x];
-                            while ((sw & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u) sw = *(sp - (size_t)x * nb);
+                            u32 spins = 0;
+                            while ((sw & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u) {
+                                sw = *(sp - (size_t)x * nb);
+                                if (++spins > PCB_SPIN_LIMIT) {
+                                    if (err) atomicOr(err, PCB_DERR_TIMEOUT);
+                                    sw = RADIX_FLAG_INCL;
+                                }
+                            }
                             prev += sw & RADIX_COUNT_MASK;
                             done = (sw & RADIX_FLAG_INCL) != 0u;
                         }
@@ -880,6 +888,7 @@ struct OctScanOp {
     u32* rank;     // [n] rank of the loser emitted at this position inside its bucket (new losers only)
     u32* bcnt;     // [ncell * 8] new losers per bucket
     u32* special;  // [ncell * 8][4] trigger batch (+1) at ranks 0, L-1, L, and (merge) max(L-1-m0, 0)
+    u32* err = nullptr;   // device error word (look-back timeout)
     __device__ static void pack(const State& s, u32 status, uint4& a, uint4& b) {   // counters < 2^30
         a = make_uint4(s.c[0], s.c[1], s.c[2], s.c[3] | status);
         b = make_uint4(s.c[4], s.c[5], s.c[6] | ((s.head & 1u) << 31), s.c[7] | status);
@@ -1038,7 +1047,7 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
             tot8.c[4 + k] = (u32)(total.hi >> (16 * k)) & 0xFFFFu;
         }
         tot8.head = total.head;
-        Oct8 prefix = chain_lookback(op, desc, tile, tot8);
+        Oct8 prefix = chain_lookback(op, desc, tile, tot8, op.err);
         if (lane == 0) s_prefix = prefix;
     }
     __syncthreads();

@@ -23,6 +23,7 @@
 // own digit histograms, and a look-back ends at the first tile of the segment.
 #pragma once
 #include "common.cuh"
+#include "scan.cuh"
 
 #define RADIX_THREADS 256
 #define RADIX_ITEMS 16
@@ -122,7 +123,7 @@ __device__ __forceinline__ void radix_hist_flush(const u32* __restrict__ hist, c
 // ---- one pass -----------------------------------------------------------------------------------------------
 // dynamic shared memory: u64 skeys[TILE]; u32 svals[TILE] (PAIRS); u32 cnt[WARPS][bins]; u32 dig_excl[bins];
 //                        u32 gbase[bins]
-// THREADS = 512 (8192-key tiles, two resident blocks per SM) is the production shape: the look-back costs
+// THREADS = 256 is the production shape (512 = 8192-key tiles, two resident blocks per SM, measured equal): the look-back costs
 // bins x window status loads per TILE, so the bigger tile halves it per key and halves the tile rate (the depth
 // of the look-back is the number of tiles that publish between a tile's aggregate and its inclusive prefix).
 // Lanes of the warp whose digit equals mine (restricted to valid lanes).  Two ways: one vote per digit bit (a fixed
@@ -174,7 +175,7 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
            u32* __restrict__ vals_out, u32 n, int shift, int bits, const u32* __restrict__ ghist /* [bins] */,
            u32* __restrict__ status /* [ntiles][bins] */, u32* __restrict__ counter,
            const uint4* __restrict__ tinfo /* segmented: per tile {first key, keys, segment, first key of the segment} */,
-           u32 hist_stride /* words between the histograms of consecutive segments */) {
+           u32 hist_stride /* words between the histograms of consecutive segments */, u32* __restrict__ err) {
     constexpr int TILE = THREADS * RADIX_ITEMS, WARPS = THREADS / 32;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     u64* skeys = (u64*)smem_raw;
@@ -338,7 +339,14 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
                     for (int x = 0; x < RADIX_WINDOW; x++) {
                         if (!done) {
                             u32 s = w[x];
-                            while ((s & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u) s = *(sp - (size_t)x * back);
+                            u32 spins = 0;
+                            while ((s & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u) {
+                                s = *(sp - (size_t)x * back);
+                                if (++spins > PCB_SPIN_LIMIT) {   // starved (see scan.cuh): fail the build, do not hang
+                                    if (err) atomicOr(err, PCB_DERR_TIMEOUT);
+                                    s = RADIX_FLAG_INCL;
+                                }
+                            }
                             prev += s & RADIX_COUNT_MASK;
                             done = (s & RADIX_FLAG_INCL) != 0u;
                         }
@@ -410,6 +418,7 @@ __global__ void k_seg_tiles(const u32* __restrict__ cell_start, u32 ncell, int k
 struct RadixTemp {
     u32* ghist = nullptr;    // [MAX_PASSES * MAX_BINS], zeroed before the key-producing kernel runs
     u32* status = nullptr;   // [npass][ntiles * bins + 1] (last word of each pass = tile counter), zeroed
+    u32* err = nullptr;      // device error word (PCB_DERR_TIMEOUT), optional
     const uint4* tinfo = nullptr;   // segmented sort: tile table (k_seg_tiles), else nullptr
     u32 ntiles_seg = 0;             // ... its length (upper bound of the number of tiles)
     u32 nseg = 1;                   // ... ghist then holds [nseg][npass][RADIX_MAX_BINS]
@@ -448,7 +457,7 @@ static inline int radix_sort_shape(u64* k0, u32* v0, u64* k1, u32* v1, u32 n, co
         prof.pb();
         kern<<<ntiles, THREADS, smem, st>>>(ki, ko, vi, vo, n, plan.shift[p], plan.bits[p],
                                             tmp.ghist + p * RADIX_MAX_BINS, status, status + words, tmp.tinfo,
-                                            hist_stride);
+                                            hist_stride, tmp.err);
         static const bool by_pass = pcb_tuning_env("PCB_PROF_PASSES") != nullptr;   // diagnostics: one stats row per pass index
         static const char* const pass_name[RADIX_MAX_PASSES] = {"radix_p0", "radix_p1", "radix_p2", "radix_p3",
                                                                 "radix_p4", "radix_p5", "radix_p6", "radix_p7"};

@@ -1,148 +1,28 @@
-// scan.cuh — device-wide scan with a user operator (reduce-then-scan, no spin-waits).
-//
-// Three launches: (1) every tile reduces its elements to one State, (2) one block
-// turns the tile aggregates into exclusive prefixes, (3) every tile re-reads its
-// elements and hands each one its exclusive and inclusive prefix.  The operator
-// need not be commutative (segmented scans).  Elements are assigned blocked:
-// thread t of a tile owns ITEMS consecutive elements, so `consume` sees them in
-// sequence order.
+// scan.cuh - single-pass device-wide scans with a user operator (decoupled look-back), hand-written for sm_100a.
 //
 // Op interface:
-//   typedef ... State;
+//   typedef ... State;                                              // multiple of 4 bytes
+//   static constexpr bool kTileLoad;                                // true: load_items() fills a thread's items at once
 //   __device__ State identity() const;
-//   __device__ State load(u32 i) const;                         // element i as a State
-//   __device__ State combine(const State& a, const State& b) const;   // a before b
-//   __device__ void consume(u32 i, const State& excl, const State& incl) const;
-//   __device__ void finish(const State& total) const;           // once, reduction of everything
+//   __device__ State load(u32 i) const;                             // element i as a State
+//   __device__ State combine(const State& a, const State& b) const;   // a before b; need not commute (segmented scans)
+//   __device__ void consume(u32 i, const State& excl, const State& incl, const State& self) const;
+//                                                                   // (`self` = load(i), kept in registers)
+//   __device__ void finish(const State& total) const;               // once, reduction of everything
+//   static pack / unpack: the tile descriptor words, see below;  optional member  u32* err  (device error word)
+// Elements are assigned blocked: thread t of a tile owns ITEMS consecutive elements, so `consume` sees them in
+// sequence order.
+//
+// Every element is read ONCE.  Tile = block index: a tile publishes its aggregate, then folds its predecessors'
+// published aggregates / inclusive prefixes (one warp, 32 predecessors per step, in order) and publishes its own
+// inclusive prefix.  The look-back needs every earlier tile to be resident or done, i.e. blocks of a 1-D grid
+// dispatched in index order (the assumption CUB's decoupled look-back makes as well: true on a dedicated device, not
+// guaranteed under MPS time-slicing, a debugger or compute-sanitizer's serialisation); a look-back that starves gives
+// up with PCB_DERR_TIMEOUT instead of hanging the GPU (PCB_SPIN_LIMIT).
 #pragma once
 #include "common.cuh"
 
-template <class Op, int THREADS>
-__device__ __forceinline__ typename Op::State block_exclusive_scan(const Op& op, typename Op::State mine,
-                                                                   typename Op::State* sh /*[2*THREADS]*/,
-                                                                   typename Op::State* block_total) {
-    typedef typename Op::State State;
-    const int t = threadIdx.x;
-    int cur = 0;
-    sh[t] = mine;
-    __syncthreads();
-#pragma unroll 1
-    for (int d = 1; d < THREADS; d <<= 1) {
-        State v = sh[cur * THREADS + t];
-        if (t >= d) v = op.combine(sh[cur * THREADS + t - d], v);
-        sh[(cur ^ 1) * THREADS + t] = v;
-        cur ^= 1;
-        __syncthreads();
-    }
-    State excl = (t == 0) ? op.identity() : sh[cur * THREADS + t - 1];
-    if (block_total) *block_total = sh[cur * THREADS + THREADS - 1];
-    __syncthreads();
-    return excl;
-}
-
-template <class Op, int THREADS, int ITEMS>
-__global__ void __launch_bounds__(THREADS) k_scan_reduce(Op op, u32 n, typename Op::State* __restrict__ agg) {
-    typedef typename Op::State State;
-    __shared__ State sh[2 * THREADS];
-    const u64 base = (u64)blockIdx.x * (THREADS * ITEMS) + (u64)threadIdx.x * ITEMS;
-    State acc = op.identity();
-#pragma unroll
-    for (int k = 0; k < ITEMS; k++) {
-        u64 i = base + k;
-        if (i < n) acc = op.combine(acc, op.load((u32)i));
-    }
-    State total;
-    block_exclusive_scan<Op, THREADS>(op, acc, sh, &total);
-    if (threadIdx.x == 0) agg[blockIdx.x] = total;
-}
-
-// one block; agg[0..ntiles) -> exclusive prefixes in place
-template <class Op, int THREADS>
-__global__ void __launch_bounds__(THREADS) k_scan_agg(Op op, typename Op::State* __restrict__ agg, u32 ntiles) {
-    typedef typename Op::State State;
-    __shared__ State sh[2 * THREADS];
-    const u32 per = (ntiles + THREADS - 1) / THREADS;
-    const u32 lo = min(ntiles, threadIdx.x * per), hi = min(ntiles, lo + per);
-    State acc = op.identity();
-    for (u32 i = lo; i < hi; i++) acc = op.combine(acc, agg[i]);
-    State total;
-    State run = block_exclusive_scan<Op, THREADS>(op, acc, sh, &total);
-    for (u32 i = lo; i < hi; i++) {
-        State v = agg[i];
-        agg[i] = run;
-        run = op.combine(run, v);
-    }
-    if (threadIdx.x == 0) op.finish(total);
-}
-
-template <class Op, int THREADS, int ITEMS>
-__global__ void __launch_bounds__(THREADS) k_scan_apply(Op op, u32 n, const typename Op::State* __restrict__ agg) {
-    typedef typename Op::State State;
-    __shared__ State sh[2 * THREADS];
-    const u64 base = (u64)blockIdx.x * (THREADS * ITEMS) + (u64)threadIdx.x * ITEMS;
-    State acc = op.identity();
-#pragma unroll
-    for (int k = 0; k < ITEMS; k++) {
-        u64 i = base + k;
-        if (i < n) acc = op.combine(acc, op.load((u32)i));
-    }
-    State run = block_exclusive_scan<Op, THREADS>(op, acc, sh, (State*)nullptr);
-    run = op.combine(agg[blockIdx.x], run);
-#pragma unroll
-    for (int k = 0; k < ITEMS; k++) {
-        u64 i = base + k;
-        if (i < n) {
-            State incl = op.combine(run, op.load((u32)i));  // re-load: L1 hit, saves registers
-            op.consume((u32)i, run, incl);
-            run = incl;
-        }
-    }
-}
-
-// Host launcher.  `agg` must hold div_up(n, THREADS*ITEMS) States.  Returns launches made.
-template <class Op, int THREADS = 256, int ITEMS = 8>
-static inline int device_scan(const Op& op, u32 n, typename Op::State* agg, cudaStream_t st) {
-    const u32 tile = THREADS * ITEMS;
-    const u32 ntiles = n ? div_up(n, tile) : 0;
-    if (ntiles) k_scan_reduce<Op, THREADS, ITEMS><<<ntiles, THREADS, 0, st>>>(op, n, agg);
-    k_scan_agg<Op, 256><<<1, 256, 0, st>>>(op, agg, ntiles);
-    if (ntiles) k_scan_apply<Op, THREADS, ITEMS><<<ntiles, THREADS, 0, st>>>(op, n, agg);
-    return ntiles ? 3 : 1;
-}
-
-template <class Op, int THREADS = 256, int ITEMS = 8>
-static inline u64 device_scan_temp_states(u64 n) {
-    return (n + (u64)THREADS * ITEMS - 1) / ((u64)THREADS * ITEMS) + 1;
-}
-
-// ---- plain exclusive sums ---------------------------------------------------
-template <class TIn, class TOut>
-struct SumOp {
-    typedef TOut State;
-    const TIn* in;
-    TOut* out;        // exclusive prefix per element (may alias in when types match)
-    TOut* total_out;  // optional: sum of everything (also written to out[n] by the caller's choice)
-    __device__ State identity() const { return 0; }
-    __device__ State load(u32 i) const { return (TOut)in[i]; }
-    __device__ State combine(const State& a, const State& b) const { return a + b; }
-    __device__ void consume(u32 i, const State& excl, const State&) const { out[i] = excl; }
-    __device__ void finish(const State& total) const {
-        if (total_out) *total_out = total;
-    }
-};
-
-// ---------------------------------------------------------------------------------------------
-// Single-pass chained scan (decoupled look-back): every element is read ONCE.  Tiles take their
-// ordinal from an atomic counter, so every predecessor of a running tile is itself running or done
-// (forward progress); a tile publishes its aggregate, then folds its predecessors' published
-// aggregates / inclusive prefixes (one warp, 32 predecessors per step, in order: the operator need
-// not commute) and publishes its own inclusive prefix.  Publication is data-then-flag with
-// st.release.gpu / ld.acquire.gpu.
-//
-// Op interface as above, except
-//   __device__ void consume(u32 i, const State& excl, const State& incl, const State& self) const;
-// (`self` = load(i), kept in registers: load may be expensive, e.g. a gather).
-// temp layout of a chained scan: uint4 desc[2 * ntiles], then the u32 tile counter; all zero at launch
+// temp layout of a chained scan: uint4 desc[2 * ntiles] (+ 16 spare bytes); all zero at launch
 static inline u64 chain_temp_bytes(u64 ntiles) { return 32 * ntiles + 16; }
 
 __device__ __forceinline__ u32 ld_acquire_u32(const u32* p) {
@@ -194,7 +74,7 @@ __device__ __forceinline__ State ldcg_state(const State* p) {
 
 // Tile descriptor of the chained scans: 32 bytes = two 16-byte words, each carrying the status (0 nothing,
 // 1 aggregate, 2 inclusive prefix) in bits 30-31 of its .w, so that data and status travel in the same
-// memory transaction: no fence, no L1 invalidation, one volatile 16-byte load per word and poll.
+// memory transaction: no fence, no L1 invalidation, one 16-byte load per word and poll.
 // Every Op supplies   static void pack(const State&, u32 status, uint4& a, uint4& b)   (status already
 // shifted: PCB_DESC_AGG / PCB_DESC_INCL OR-ed into a.w and b.w by pack) and   static State unpack(a, b).
 // An Op whose State fits the first word sets  static constexpr bool kOneWord = true;  the second word is then neither
@@ -206,47 +86,73 @@ struct ChainOneWord<Op, decltype((void)Op::kOneWord)> { static constexpr bool va
 #define PCB_DESC_AGG 0x40000000u
 #define PCB_DESC_INCL 0x80000000u
 #define PCB_DESC_MASK 0xC0000000u
-__device__ __forceinline__ uint4 ld_volatile_v4(const uint4* p) {
-    uint4 v;
-    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-    return v;
+// One 128-bit relaxed.gpu access per word (ld/st .b128: ONE scalar access in the PTX memory model - the four elements
+// of a .v4 vector access may legally be observed torn, new status with old payload).  SASS: LDG/STG.E.128.STRONG.GPU.
+__device__ __forceinline__ uint4 ld_desc(const uint4* p) {
+    unsigned long long lo, hi;
+    asm volatile("{\n\t.reg .b128 t;\n\tld.relaxed.gpu.global.b128 t, [%2];\n\tmov.b128 {%0, %1}, t;\n\t}"
+                 : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
+    return make_uint4((u32)lo, (u32)(lo >> 32), (u32)hi, (u32)(hi >> 32));
 }
-__device__ __forceinline__ void st_volatile_v4(uint4* p, const uint4& v) {
-    asm volatile("st.volatile.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+__device__ __forceinline__ void st_desc(uint4* p, const uint4& v) {
+    const unsigned long long lo = ((unsigned long long)v.y << 32) | v.x, hi = ((unsigned long long)v.w << 32) | v.z;
+    asm volatile("{\n\t.reg .b128 t;\n\tmov.b128 t, {%1, %2};\n\tst.relaxed.gpu.global.b128 [%0], t;\n\t}"
+                 ::"l"(p), "l"(lo), "l"(hi) : "memory");
+}
+// A look-back that polls longer than this gives up, raises PCB_DERR_TIMEOUT and carries on with an identity prefix: the
+// build then FAILS with an error instead of hanging.  ~2^22 polls of >= 0.5 us each: seconds.
+#ifndef PCB_SPIN_LIMIT
+#define PCB_SPIN_LIMIT (1u << 22)
+#endif
+// device error word of an Op (member `u32* err`), or null
+template <class Op, class = void>
+struct ChainErr { __device__ static u32* get(const Op&) { return nullptr; } };
+template <class Op>
+struct ChainErr<Op, decltype((void)((Op*)nullptr)->err)> { __device__ static u32* get(const Op& op) { return op.err; } };
+
+template <class Op>
+__device__ __forceinline__ void chain_publish(uint4* __restrict__ desc, u32 tile, const typename Op::State& s, u32 status) {
+    uint4 a, b;
+    Op::pack(s, status, a, b);
+    st_desc(desc + 2 * (u64)tile, a);
+    if (!ChainOneWord<Op>::value) st_desc(desc + 2 * (u64)tile + 1, b);
 }
 
 // Warp-wide look-back of tile `tile` (call with all 32 lanes of ONE warp): publishes `total` as the tile's
 // aggregate, folds the predecessors, publishes the inclusive prefix and returns the exclusive one (all lanes).
 template <class Op>
 __device__ __forceinline__ typename Op::State chain_lookback(const Op& op, uint4* __restrict__ desc, u32 tile,
-                                                             const typename Op::State& total) {
+                                                             const typename Op::State& total, u32* err = nullptr) {
     typedef typename Op::State State;
     const int lane = threadIdx.x & 31;
-    if (lane == 0) {
-        uint4 a, b;
-        Op::pack(total, tile == 0 ? PCB_DESC_INCL : PCB_DESC_AGG, a, b);
-        st_volatile_v4(desc + 2 * (u64)tile, a);
-        if (!ChainOneWord<Op>::value) st_volatile_v4(desc + 2 * (u64)tile + 1, b);
-    }
+    if (lane == 0) chain_publish<Op>(desc, tile, total, tile == 0 ? PCB_DESC_INCL : PCB_DESC_AGG);
     State prefix = op.identity();
     if (tile > 0) {
         int look = (int)tile - 1;
+        u32 spins = 0;
         for (;;) {
             int t = look - lane;
             u32 f = PCB_DESC_INCL;
             State s = op.identity();
             if (t >= 0) {
                 uint4 a, b;
+                bool gave_up = false;
                 for (;;) {   // both words of one publication (a reader may catch the writer between its two stores)
-                    a = ld_volatile_v4(desc + 2 * (u64)t);
-                    if (ChainOneWord<Op>::value) b = a; else b = ld_volatile_v4(desc + 2 * (u64)t + 1);
+                    a = ld_desc(desc + 2 * (u64)t);
+                    if (ChainOneWord<Op>::value) b = a; else b = ld_desc(desc + 2 * (u64)t + 1);
                     f = a.w & PCB_DESC_MASK;
                     if (f != 0u && f == (b.w & PCB_DESC_MASK)) break;
+                    if (++spins > PCB_SPIN_LIMIT) {   // starved: fail the build, do not hang
+                        if (err) atomicOr(err, PCB_DERR_TIMEOUT);
+                        gave_up = true;
+                        f = PCB_DESC_INCL;
+                        break;
+                    }
 #ifdef PCB_SPIN_BACKOFF
                     __nanosleep(PCB_SPIN_BACKOFF);
 #endif
                 }
-                s = Op::unpack(a, b);
+                if (!gave_up) s = Op::unpack(a, b);
             }
             const u32 m = __ballot_sync(0xFFFFFFFFu, f == PCB_DESC_INCL);
             const int last = m ? (__ffs(m) - 1) : 31;
@@ -261,12 +167,7 @@ __device__ __forceinline__ typename Op::State chain_lookback(const Op& op, uint4
             if (m) break;
             look -= 32;
         }
-        if (lane == 0) {
-            uint4 a, b;
-            Op::pack(op.combine(prefix, total), PCB_DESC_INCL, a, b);
-            st_volatile_v4(desc + 2 * (u64)tile, a);
-            if (!ChainOneWord<Op>::value) st_volatile_v4(desc + 2 * (u64)tile + 1, b);
-        }
+        if (lane == 0) chain_publish<Op>(desc, tile, op.combine(prefix, total), PCB_DESC_INCL);
     }
     return prefix;
 }
@@ -330,7 +231,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_chain_scan(Op op, u32 n, u32 
     texcl = op.combine(wpre, texcl);   // exclusive prefix of this thread inside the tile
 
     if (warp == 0) {
-        State prefix = chain_lookback(op, desc, tile, total);
+        State prefix = chain_lookback(op, desc, tile, total, ChainErr<Op>::get(op));
         if (lane == 0) s_prefix = prefix;
     }
     __syncthreads();
