@@ -171,6 +171,19 @@ int pcb_route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t
                       const uint8_t* d_owner, uint32_t world, const uint64_t* recv_pts_ptrs,
                       const uint64_t* recv_batch_ptrs, const uint64_t* recv_offsets);
 
+/* pcb_route_bbox without any allocation.  NO counterpart in the reference: added
+   for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+   it).  The kernel's scratch (min / max / error words) lives in a file-scope device array of PCB_STATIC_SCRATCH_BYTES
+   = 256 bytes that every GPU loading the library holds until exit; the call performs no cudaMalloc / cudaFree /
+   allocating library routine, no host synchronisation and no device-to-host copy.  d_out6 (device, 6 floats: min xyz,
+   max xyz; +inf / -inf when n == 0) and d_err (device u32, may be NULL: 1 = non-finite coordinate, 2 = level-0 index
+   outside +-2^20) are written on `stream`.  n > PCB_BBOX_STATIC_MAX_POINTS is rejected with PCB_ERR_RANGE.  Every call
+   on a device shares the scratch array (re-initialised at the start of each call): calls that OVERLAP on the GPU
+   (different streams) race - serialise them.  Returns the number of kernels launched, or a negative pcb_status. */
+#define PCB_BBOX_STATIC_MAX_POINTS ((1ull << 30) - 1)
+int pcb_route_bbox_static(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size,
+                          float* d_out6, uint32_t* d_err);
+
 const char* pcb_version(void);
 int pcb_device_count(void);
 

@@ -30,6 +30,7 @@ int route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n
 int route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
                float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner, uint32_t world,
                pcb_point* d_send_pts, uint32_t* d_send_batch, uint64_t* send_counts);
+int route_bbox_static(int device, void* stream, const pcb_point* d_pts, uint64_t n, float S0, float* d_out6, uint32_t* d_err);
 int route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
                   float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner, uint32_t world,
                   const uint64_t* recv_pts_ptrs, const uint64_t* recv_batch_ptrs, const uint64_t* recv_offsets);
@@ -222,6 +223,11 @@ int pcb_route_bbox(int device, void* stream, const pcb_point* d_pts, uint64_t n,
                    float out_max[3]) {
     if (!out_min || !out_max || (n && !d_pts)) return PCB_ERR_ARG;
     PCB_ROUTE_GUARD(pcb::route_bbox(device, stream, d_pts, n, max_cell_size, out_min, out_max))
+}
+int pcb_route_bbox_static(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size,
+                          float* d_out6, uint32_t* d_err) {
+    if (!d_out6 || (n && !d_pts)) return fail(nullptr, PCB_ERR_ARG, "pcb_route_bbox_static: null pointer");
+    PCB_ROUTE_GUARD(pcb::route_bbox_static(device, stream, d_pts, n, max_cell_size, d_out6, d_err))
 }
 int pcb_route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size,
                         const int32_t origin[3], const uint32_t dims[3], uint32_t* d_hist) {

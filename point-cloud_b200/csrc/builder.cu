@@ -1344,6 +1344,54 @@ int route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t n, 
     });
 }
 
+// ---- allocation-free bounding box (no counterpart in the reference) ----
+// Same result as route_bbox, for callers that must not allocate (CUDA graph capture, tight serving loops): the
+// min / max / error scratch of k_bbox_check lives in a file-scope device array instead of a cudaMallocAsync block.
+// The array's name is a host-side stand-in in host code: its device address is taken ONCE per device, with that device
+// current, through cudaGetSymbolAddress.  Every call on a device shares the array: it is re-initialised by the first
+// kernel of each call, and calls that overlap on the GPU (two streams) race.
+#define PCB_STATIC_SCRATCH_BYTES 256   // held by every GPU that loads the library until exit
+static __device__ __align__(256) int g_static_scratch[PCB_STATIC_SCRATCH_BYTES / 4];
+__global__ void k_bbox_static_init(int* __restrict__ s) {
+    const int t = threadIdx.x;
+    if (t < 8) s[t] = t < 3 ? INT_MAX : t < 6 ? INT_MIN : 0;
+}
+__global__ void k_bbox_static_finish(const int* __restrict__ s, u32 n, float* __restrict__ out6, u32* __restrict__ err) {
+    const int t = threadIdx.x;
+    if (t < 6) {
+        int i = s[t];
+        i = i ^ ((i >> 31) & 0x7FFFFFFF);   // inverse of f2ord
+        out6[t] = n ? __int_as_float(i) : (t < 3 ? INFINITY : -INFINITY);
+    }
+    if (t == 6 && err) *err = (u32)s[6];
+}
+static std::mutex g_static_mu;
+static int* g_static_ptr[64] = {nullptr};
+int route_bbox_static(int device, void* stream, const pcb_point* d_pts, uint64_t n, float S0, float* d_out6, uint32_t* d_err) {
+    return guarded([&] {
+        if (device < 0 || device >= 64) throw Error{PCB_ERR_ARG, "bad device ordinal"};
+        if (n > PCB_BBOX_STATIC_MAX_POINTS)
+            throw Error{PCB_ERR_RANGE, "pcb_route_bbox_static: more than PCB_BBOX_STATIC_MAX_POINTS (2^30 - 1) points in one call"};
+        CUDA_TRY(cudaSetDevice(device));
+        int* scratch = nullptr;
+        {
+            std::lock_guard<std::mutex> g(g_static_mu);
+            if (!g_static_ptr[device]) {   // once per device, with that device current
+                void* q = nullptr;
+                CUDA_TRY(cudaGetSymbolAddress(&q, g_static_scratch));
+                g_static_ptr[device] = (int*)q;
+            }
+            scratch = g_static_ptr[device];
+        }
+        cudaStream_t st = (cudaStream_t)stream;
+        k_bbox_static_init<<<1, 32, 0, st>>>(scratch);
+        if (n) k_bbox_check<<<148 * 8, 256, 0, st>>>((const PcbPoint*)d_pts, (u32)n, S0, scratch, (u32*)(scratch + 6));
+        k_bbox_static_finish<<<1, 32, 0, st>>>(scratch, (u32)n, d_out6, d_err);
+        CUDA_TRY(cudaGetLastError());
+        return n ? 3 : 2;
+    });
+}
+
 void trim_host_cache() {
     g_pinned.trim();
     g_arenas.trim();

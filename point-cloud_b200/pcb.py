@@ -27,7 +27,7 @@ FLAG_NO_METADATA_FILE = 8
 EXPORTS = [
     "pcb_open", "pcb_set_stream", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
     "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
-    "pcb_route_bbox", "pcb_route_histogram", "pcb_route_pack", "pcb_route_scatter",
+    "pcb_route_bbox", "pcb_route_bbox_static", "pcb_route_histogram", "pcb_route_pack", "pcb_route_scatter",
     "pcb_add_points_device_batched", "pcb_write_metadata", "pcb_get_config", "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
 
@@ -84,6 +84,7 @@ def load_library():
                                      C.c_uint32, C.c_uint32, C.c_float]
     L.pcb_get_config.argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_float)]
     L.pcb_route_bbox.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    L.pcb_route_bbox_static.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_float, vp, vp]
     L.pcb_route_histogram.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_float, C.POINTER(C.c_int32),
                                       C.POINTER(C.c_uint32), vp]
     L.pcb_route_pack.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_uint64, C.c_uint32, C.c_float, C.POINTER(C.c_int32),
@@ -236,6 +237,14 @@ def route_bbox(device, stream, pts_ptr, n, max_cell_size):
     nl = _route_check(load_library().pcb_route_bbox(device, C.c_void_p(stream), C.c_void_p(pts_ptr), n,
                                                     max_cell_size, lo, hi))
     return list(lo), list(hi), nl
+
+
+def route_bbox_static(device, stream, pts_ptr, n, max_cell_size, out6_ptr, err_ptr=0):
+    """pcb_route_bbox_static: the bounding box without any allocation (scratch in a static device array); outputs stay on
+    the device."""
+    return _route_check(load_library().pcb_route_bbox_static(device, C.c_void_p(stream), C.c_void_p(pts_ptr), n,
+                                                             max_cell_size, C.c_void_p(out6_ptr),
+                                                             C.c_void_p(err_ptr) if err_ptr else None))
 
 
 def route_histogram(device, stream, pts_ptr, n, max_cell_size, origin, dims, hist_ptr):
