@@ -59,6 +59,12 @@ typedef enum pcb_status {
                                     nodes into the shared directory, rank 0 writes the reduced metadata.json with
                                     pcb_write_metadata) */
 
+#define PCB_FLAG_COUNT_BY_DELTA 16u /* GUI-caller accounting (src/plugins/converter.rs:565-573): number_of_points advances
+                                    by the change of every touched node's header total_number_of_points (grid + kept
+                                    overflow, negative when a list is flushed) instead of by batch lengths
+                                    (converter.rs:108).  Together with batch_size = 50000 (src/plugins/converter.rs:600)
+                                    this is the in-app converter's preset.  Not with PCB_FLAG_DEVICE_ONLY. */
+
 typedef struct pcb_options {
     uint32_t struct_size;   /* sizeof(pcb_options), for ABI growth */
     int32_t device;         /* CUDA device ordinal */
@@ -109,6 +115,18 @@ int pcb_add_points(pcb_handle* h, const pcb_point* pts, uint64_t n);
 /* Exactly ONE batch, the direct mirror of Converter::add_points_batch(Vec<Point>) (converter.rs:106-112;
    the GUI caller src/plugins/converter.rs:203 uses its own batch sizes).  n may be 0. */
 int pcb_add_points_batch(pcb_handle* h, const pcb_point* pts, uint64_t n);
+/* Uncompressed LAS point records of the current input file, as they lie in the file (`stride` bytes each, host
+   memory): X, Y, Z as little-endian i32 at bytes 0-11, red / green / blue as u16 at colour_off (-1: none).  The
+   records are copied to the device and decoded THERE exactly as converter/las.rs:32-41 does on the host:
+   pos = (X * scale + offset) in f64, then `as f32`; colour = low byte of each channel; alpha 255.  Cut into batches
+   like pcb_add_points.  stride 12..96. */
+int pcb_add_las_records(pcb_handle* h, const uint8_t* records, uint64_t n, uint32_t stride, int32_t colour_off,
+                        const double scale[3], const double offset[3]);
+/* Page-locked host memory for input chunks (from the library's recycled cache; pcb_add_points from such a buffer is
+   one DMA at full PCIe speed).  pcb_free_host returns it to the cache.  The streamed ingest of the CLI
+   (lib.rs:31-52: one bounded batch of input at a time) uses three such chunks in rotation. */
+void* pcb_alloc_host(uint64_t bytes);
+void pcb_free_host(void* p);
 /* Optional capacity hint (total points this handle will receive). */
 int pcb_reserve(pcb_handle* h, uint64_t n);
 /* Run all device work of this handle on the caller's CUDA stream (a cudaStream_t), e.g. so that the

@@ -236,6 +236,9 @@ struct Converter {
     std::string working_directory;  // empty => no file IO at all
     std::unordered_map<CellId, std::unique_ptr<Cell>, CellIdHash> cells;
     uint64_t arrivals = 0;          // statistic: sum over levels of delivered points
+    // the GUI caller's accounting (src/plugins/converter.rs:565-573): sum over add_points_to_cell calls of
+    // header.total_number_of_points after - before (an i32 per call there)
+    int64_t points_by_delta = 0;
     int error = 0;                  // 1 = hierarchy >= 32 (reference would overflow 2u32.pow)
     // Optional residency emulation of converter.rs:92, 160-178: at most lru_capacity cells in RAM (the reference
     // uses LRUCache::with_hasher(100, ..)); a miss loads the node file or creates the cell, the evicted cell is

@@ -86,7 +86,9 @@ void Converter::add_points_in_hierarchy(uint32_t hierarchy, const MetadataConfig
             CellId id{hierarchy, kv.first};
             Cell& cell = get_cell_mut(id);
             arrivals += kv.second.size();
+            const uint32_t points_before = cell.header.total_number_of_points;   // src/plugins/converter.rs:566
             PointMap remaining = add_points_to_cell(config, kv.second, cell);
+            points_by_delta += (int32_t)cell.header.total_number_of_points - (int32_t)points_before;   // :571-573
             // merge_point_maps, converter.rs:49-60
             for (auto& r : remaining) {
                 auto it = next.find(r.first);
@@ -554,6 +556,8 @@ int orc_finish(void* hv) {
         w->cells.clear();
         h->conv.arrivals += w->arrivals;
         w->arrivals = 0;
+        h->conv.points_by_delta += w->points_by_delta;
+        w->points_by_delta = 0;
     }
     return h->conv.save_all() ? 0 : -1;
 }
@@ -561,6 +565,7 @@ int orc_finish(void* hv) {
 uint64_t orc_number_of_points(void* hv) { return ((OrcHandle*)hv)->conv.metadata.number_of_points; }
 uint32_t orc_hierarchies(void* hv) { return ((OrcHandle*)hv)->conv.metadata.hierarchies; }
 uint64_t orc_arrivals(void* hv) { return ((OrcHandle*)hv)->conv.arrivals; }
+int64_t orc_points_by_delta(void* hv) { return ((OrcHandle*)hv)->conv.points_by_delta; }
 uint64_t orc_cell_count(void* hv) { return ((OrcHandle*)hv)->conv.cells.size(); }
 void orc_bounding_box(void* hv, float* out6) {
     auto& b = ((OrcHandle*)hv)->conv.metadata.bounding_box;

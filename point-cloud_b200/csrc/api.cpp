@@ -7,7 +7,9 @@
 
 #include <algorithm>
 #include <atomic>
+#include <map>
 #include <memory>
+#include <mutex>
 #include <vector>
 #include <chrono>
 #include <cmath>
@@ -95,6 +97,7 @@ static bool write_file(const std::string& path, const void* data, size_t n) {
 // converter.rs:180-207: a missing file means a new cell; any other failure is fatal (reference panics)
 struct DirNodeSource : NodeSource {
     std::string dir;
+    std::atomic<uint64_t> total_before{0};   // header totals of the nodes loaded (PCB_FLAG_COUNT_BY_DELTA)
     bool load(uint32_t hierarchy, const int32_t idx[3], ExistingNode* out) override {
         std::vector<uint8_t> bytes;
         bool nf = false;
@@ -104,6 +107,11 @@ struct DirNodeSource : NodeSource {
             throw Error{PCB_ERR_IO, "cannot read node file " + p};
         }
         if (!parse_node(bytes.data(), bytes.size(), out)) throw Error{PCB_ERR_FORMAT, "corrupt node file " + p};
+        if (bytes.size() >= 20) {   // Header.total_number_of_points (cell.rs:286)
+            uint32_t t;
+            std::memcpy(&t, bytes.data() + 16, 4);
+            total_before += t;
+        }
         return true;
     }
 };
@@ -119,6 +127,8 @@ int pcb_open(const char* out_dir, const pcb_options* opt, pcb_handle** out) {
     std::unique_ptr<pcb_handle> h(new pcb_handle());
     std::memset(&h->opt, 0, sizeof h->opt);
     if (opt) std::memcpy(&h->opt, opt, std::min<size_t>(sizeof h->opt, opt->struct_size ? opt->struct_size : sizeof h->opt));
+    if ((h->opt.flags & PCB_FLAG_DEVICE_ONLY) && (h->opt.flags & PCB_FLAG_COUNT_BY_DELTA))
+        return fail(nullptr, PCB_ERR_ARG, "PCB_FLAG_COUNT_BY_DELTA needs the node images on the host (not with PCB_FLAG_DEVICE_ONLY)");
     if (h->opt.flags & PCB_FLAG_DEVICE_ONLY) h->opt.flags |= PCB_FLAG_NO_FILES;
     h->out_dir = out_dir ? out_dir : "";
     if (h->out_dir.empty()) h->opt.flags |= PCB_FLAG_NO_FILES;
@@ -181,6 +191,40 @@ int pcb_add_points(pcb_handle* h, const pcb_point* pts, uint64_t n) {
     if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
     if (h && n && !pts) return fail(h, PCB_ERR_ARG, "null points");
     PCB_GUARD(h, h->builder->add_points(pts, n, h->opt.batch_size, false))
+}
+
+int pcb_add_las_records(pcb_handle* h, const uint8_t* records, uint64_t n, uint32_t stride, int32_t colour_off,
+                        const double scale[3], const double offset[3]) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    if (h && ((n && !records) || !scale || !offset)) return fail(h, PCB_ERR_ARG, "null records");
+    PCB_GUARD(h, h->builder->add_las_records(records, n, stride, colour_off, scale, offset, h->opt.batch_size))
+}
+
+// pinned chunks handed out to callers: pointer -> capacity (the cache wants it back)
+static std::mutex g_host_mu;
+static std::map<void*, uint64_t> g_host_chunks;
+void* pcb_alloc_host(uint64_t bytes) {
+    try {
+        uint64_t got = 0;
+        void* p = Builder::alloc_host(bytes ? bytes : 16, &got);
+        std::lock_guard<std::mutex> g(g_host_mu);
+        g_host_chunks[p] = got;
+        return p;
+    } catch (...) {
+        return nullptr;
+    }
+}
+void pcb_free_host(void* p) {
+    if (!p) return;
+    uint64_t got = 0;
+    {
+        std::lock_guard<std::mutex> g(g_host_mu);
+        auto it = g_host_chunks.find(p);
+        if (it == g_host_chunks.end()) return;
+        got = it->second;
+        g_host_chunks.erase(it);
+    }
+    Builder::free_host(p, got);
 }
 
 int pcb_add_points_device(pcb_handle* h, const pcb_point* d_pts, uint64_t n) {
@@ -307,8 +351,21 @@ int pcb_finish(pcb_handle* h, pcb_stats* stats) {
         auto t0 = std::chrono::steady_clock::now();
         DirNodeSource src;
         src.dir = h->out_dir;
+        const uint64_t points_before = h->meta.number_of_points;
         h->builder->build(&h->meta, h->merge ? &src : nullptr);
         h->finished = true;
+        if (h->opt.flags & PCB_FLAG_COUNT_BY_DELTA) {
+            // src/plugins/converter.rs:565-573: every add_points_to_cell call reports total_after - total_before of its
+            // cell; over a run that telescopes to (header totals of the touched nodes now) - (their totals before)
+            uint64_t after = 0;
+            const auto& lv = h->builder->levels();
+            for (auto& n : h->builder->nodes()) {
+                uint32_t t;
+                std::memcpy(&t, lv[n.level_slot].h_image + n.offset + 16, 4);
+                after += t;
+            }
+            h->meta.number_of_points = points_before + after - src.total_before.load();
+        }
         h->meta_json = metadata_to_json(h->meta);
         h->kstats = h->builder->kernel_stats();
         pcb_stats s;

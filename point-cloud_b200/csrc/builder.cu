@@ -241,6 +241,7 @@ class BuilderImpl {
             if (l.h_image) g_pinned.put(l.h_image, l.h_cap);
         }
         if (d_in && !in_borrowed) cudaFree(d_in);
+        if (d_raw) cudaFree(d_raw);
         if (d_bat_in && bat_owned) cudaFree(d_bat_in);
         if (d_scr) cudaFreeAsync(d_scr, st);
         if (h_scr) g_pinned.put(h_scr, h_scr_cap);
@@ -369,6 +370,9 @@ class BuilderImpl {
         if (e & PCB_DERR_HEXRANGE)
             throw Error{PCB_ERR_RANGE, "hex key outside its cell window (coordinate precision exhausted)"};
         if (e & PCB_DERR_NEST) throw Error{PCB_ERR_RANGE, "child cell index does not nest in its parent"};
+        if (e & PCB_DERR_TIMEOUT)
+            throw Error{PCB_ERR_CUDA, "a look-back starved waiting for an earlier tile (device shared / time-sliced?): "
+                                      "the build was abandoned instead of hanging"};
     }
 
     void reserve(u64 n) {
@@ -406,8 +410,9 @@ class BuilderImpl {
     }
     void begin_file() { open_run(); }
 
-    void add(const pcb_point* pts, u64 n, u32 batch_size, bool device_ptr, bool one_batch) {
-        CUDA_TRY(cudaSetDevice(device));
+    // batch bookkeeping of n more points of the current input file
+    void note_points(u64 n, u32& batch_size, bool one_batch) {
+        if (d_bat_in) throw Error{PCB_ERR_ARG, "points cannot be added after routed points"};
         if (n_in + n >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "more than 2^30-1 points on one device"};
         if (one_batch) {
             open_run();
@@ -422,6 +427,47 @@ class BuilderImpl {
             segs.push_back(s);
         }
         run_points += n;
+    }
+
+    // Uncompressed LAS records decoded on the device (k_las_decode): the host only copies bytes.
+    unsigned char* d_raw = nullptr;
+    u64 raw_cap = 0;
+    void add_las(const uint8_t* rec, u64 n, u32 stride, int colour_off, const double scale[3], const double offset[3],
+                 u32 batch_size) {
+        CUDA_TRY(cudaSetDevice(device));
+        if (stride < 12 || stride > LAS_DEC_MAX_STRIDE || (colour_off >= 0 && (u32)colour_off + 6 > stride))
+            throw Error{PCB_ERR_ARG, "LAS record layout not supported by the device decoder"};
+        note_points(n, batch_size, false);
+        if (!n) return;
+        if (in_borrowed) throw Error{PCB_ERR_ARG, "cannot append to a borrowed device buffer"};
+        if (n_in + n > cap_in) reserve(std::min<u64>(std::max<u64>(n_in + n, cap_in + cap_in / 2), (1ull << 30) - 1));
+        const u64 bytes = n * stride, padded = (bytes + 3) & ~3ull;
+        if (padded > raw_cap) {
+            CUDA_TRY(cudaStreamSynchronize(st));
+            if (d_raw) CUDA_TRY(cudaFree(d_raw));
+            d_raw = nullptr;
+            raw_cap = 0;
+            CUDA_TRY(cudaMalloc((void**)&d_raw, padded + 256));
+            raw_cap = padded;
+        }
+        double t0 = now_s();
+        CUDA_TRY(cudaMemcpyAsync(d_raw, rec, bytes, cudaMemcpyHostToDevice, st));
+        k_las_decode<<<div_up(n, LAS_DEC_THREADS), LAS_DEC_THREADS, 0, st>>>(d_raw, (u32)n, stride, colour_off, scale[0], scale[1],
+                                                                             scale[2], offset[0], offset[1], offset[2],
+                                                                             d_in + n_in);
+        const int c = cls("las_decode");
+        stats[c].launches += 1;
+        stats[c].units += n;
+        stats[c].bytes += bytes + 16 * n;
+        launches += 1;
+        CUDA_TRY(cudaStreamSynchronize(st));   // the caller may reuse `rec`
+        h2d_s += now_s() - t0;
+        n_in += n;
+    }
+
+    void add(const pcb_point* pts, u64 n, u32 batch_size, bool device_ptr, bool one_batch) {
+        CUDA_TRY(cudaSetDevice(device));
+        note_points(n, batch_size, one_batch);
         if (n && device_ptr && n_in == 0 && cap_in == 0) {
             // resident input: alias the caller's buffer instead of copying it (it must stay valid and
             // unchanged until the build has run)
@@ -606,7 +652,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
         pe("l0_hist", 2, n0, 16ull * n0);
         pb();
         k_l0_split<<<ntiles, L0S_THREADS, smem, st>>>(d_in, n0, S0, box, nb, dbits, dbase, d_segs, (u32)segs.size(), d_bat_in,
-                                                      pts, bat, status);
+                                                      pts, bat, status, &d_scr->err);
         pe("l0_split", 1, n0, 36ull * n0);
         dfree(tmp);
     } else {
@@ -617,6 +663,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
         const u64 rwords = RadixTemp::ghist_words() + RadixTemp::status_words(n0, plan0);
         rt.ghist = dalloc<u32>(rwords);
         rt.status = rt.ghist + RadixTemp::ghist_words();
+        rt.err = &d_scr->err;
         CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
         pb();
         k_l0_key<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, pb0, plan0, kA, vA, rt.ghist);
@@ -917,6 +964,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         rt_mem = dalloc<u32>(rwords);
         rt.ghist = rt_mem;
         rt.status = rt.ghist + hwords;
+        rt.err = &d_scr->err;
         CUDA_TRY(cudaMemsetAsync(rt.ghist, 0, rwords * 4, st));
         if (table) {
             rt.nseg = nseg;
@@ -1049,7 +1097,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
     u32* rank = dalloc<u32>(n);
     u32* bcnt = dalloc<u32>(8ull * ncell);
     u32* special = dalloc<u32>(32ull * ncell);
-    OctScanOp oop{em, bat, cell_start, ncell, n, limit, ex_state, ex_m0, rank, bcnt, special};
+    OctScanOp oop{em, bat, cell_start, ncell, n, limit, ex_state, ex_m0, rank, bcnt, special, &d_scr->err};
     pb();
     nl = octscan(oop, n, scan_tmp, st);
     pe("oct_scan", nl, n, 12ull * n);
@@ -1176,6 +1224,12 @@ void Builder::add_points(const pcb_point* pts, uint64_t n, uint32_t batch_size, 
 void Builder::add_points_batched(const pcb_point* d_pts, const uint32_t* d_batch, uint64_t n) {
     guarded([&] { impl_->add_batched(d_pts, d_batch, n); return 0; });
 }
+void Builder::add_las_records(const uint8_t* records, uint64_t n, uint32_t stride, int32_t colour_off, const double scale[3],
+                              const double offset[3], uint32_t batch_size) {
+    guarded([&] { impl_->add_las(records, n, stride, colour_off, scale, offset, batch_size ? batch_size : 10000u); return 0; });
+}
+void* Builder::alloc_host(uint64_t bytes, uint64_t* got) { return guarded([&] { return g_pinned.get(bytes, got); }); }
+void Builder::free_host(void* p, uint64_t bytes) { g_pinned.put(p, bytes); }
 void Builder::add_points_one_batch(const pcb_point* pts, uint64_t n, bool device_ptr) {
     guarded([&] { impl_->add(pts, n, 0, device_ptr, true); return 0; });
 }

@@ -81,6 +81,11 @@ class Builder {
     void add_points(const pcb_point* pts, uint64_t n, uint32_t batch_size, bool device_ptr);
     void add_points_one_batch(const pcb_point* pts, uint64_t n, bool device_ptr);  // converter.rs:106
     void add_points_batched(const pcb_point* d_pts, const uint32_t* d_batch, uint64_t n);  // explicit batch ordinals
+    // uncompressed LAS point records (host bytes), decoded on the device (converter/las.rs:32-41)
+    void add_las_records(const uint8_t* records, uint64_t n, uint32_t stride, int32_t colour_off, const double scale[3],
+                         const double offset[3], uint32_t batch_size);
+    static void* alloc_host(uint64_t bytes, uint64_t* got);   // pinned staging from the process-wide cache
+    static void free_host(void* p, uint64_t bytes);
     // Runs the level-synchronous build.  meta: in = state before this run, out = after.
     void build(Metadata* meta, NodeSource* existing);
     const std::vector<NodeRec>& nodes() const;

@@ -6,11 +6,16 @@
 #include <dirent.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <chrono>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/pcb.h"
@@ -28,6 +33,7 @@ static void usage() {
         "  -d, --directories <DIRS>   Directories with input files to convert.\n"
         "  -f, --files <FILES>        Input files with the points to convert.\n"
         "      --device <N>           CUDA device ordinal (default 0)\n"
+        "      --host-las             decode LAS records on the host (default: on the device)\n"
         "  -h, --help                 Print help\n  -V, --version              Print version\n");
 }
 
@@ -36,6 +42,7 @@ int main(int argc, char** argv) {
     std::vector<std::string> dirs, files;
     int device = 0;
     std::string dump_points;   // test hook: read the inputs, write the 16-byte records, do not touch a GPU
+    bool host_las = false;     // --host-las: decode LAS records on the host instead of on the device
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
         auto values = [&](std::vector<std::string>* dst) {
@@ -49,6 +56,7 @@ int main(int argc, char** argv) {
         else if (a == "-f" || a == "--files") values(&files);
         else if (a == "--device" && i + 1 < argc) device = std::atoi(argv[++i]);
         else if (a == "--dump-points" && i + 1 < argc) dump_points = argv[++i];
+        else if (a == "--host-las") host_las = true;
         else {
             std::fprintf(stderr, "error: unexpected argument '%s'\n\n", a.c_str());
             usage();
@@ -105,29 +113,115 @@ int main(int argc, char** argv) {
         return 101;  // the reference panics
     }
     const uint64_t BATCH = 10000;  // lib.rs:32
+    // Streamed ingest (lib.rs:31-52 never holds more than one batch of input; here: never more than three chunks).
+    // A reader thread fills page-locked chunks (file read + decode on up to 8 host threads) while this thread hands
+    // the previous chunk to the device (pcb_add_points: one DMA from pinned memory).  Uncompressed LAS records travel
+    // raw and are decoded on the device (pcb_add_las_records).
+    const uint64_t chunk_pts = (4u << 20) / BATCH * BATCH;   // points per chunk, a multiple of the batch size (~64 MB)
+    struct Chunk {
+        void* mem = nullptr;
+        uint64_t n = 0;
+        int status = pcb::READ_OK;
+        bool raw = false, last = false;
+        std::string message;
+    };
+    uint64_t total_added = 0;
     auto t0 = std::chrono::steady_clock::now();
     for (size_t pi = 0; pi < paths.size(); pi++) {
         log_line("INFO ", "Converting file " + std::to_string(pi + 1) + "/" + std::to_string(paths.size()) + ", \"" + paths[pi] + "\"");
-        std::vector<pcb_point> pts;
-        pcb::ReadInfo info;
-        int rs = pcb::read_points_file(paths[pi], &pts, &info);
+        int rs = pcb::READ_OK;
+        std::string msg;
+        std::unique_ptr<pcb::PointStream> ps(pcb::PointStream::open(paths[pi], &rs, &msg));
         if (rs == pcb::READ_UNSUPPORTED) {
-            if (!info.message.empty()) log_line("WARN ", info.message);  // lib.rs:78-81
+            if (!msg.empty()) log_line("WARN ", msg);  // lib.rs:78-81
             continue;
         }
-        if (rs == pcb::READ_FATAL) {
-            log_line("ERROR", info.message);
+        if (rs == pcb::READ_FATAL || !ps) {
+            log_line("ERROR", msg);
             pcb_close(h);
             return 101;
         }
-        log_line("INFO ", "Converting " + std::to_string(info.total_points) + " points");
-        uint64_t keep = pts.size();
-        if (rs == pcb::READ_TRUNCATED) {  // lib.rs:36-39: the failing get_batch delivers nothing, the file ends there
-            log_line("ERROR", info.message);
-            keep = keep / BATCH * BATCH;
-            if (keep == 0) continue;
+        log_line("INFO ", "Converting " + std::to_string(ps->total_points()) + " points");
+        const pcb::LasLayout* las = host_las ? nullptr : ps->las_layout();
+        if (las && (las->stride < 12 || las->stride > 96)) las = nullptr;
+        if (!ps->ascii_ply()) pcb_reserve(h, std::min<uint64_t>(total_added + ps->total_points(), (1ull << 30) - 1));
+        // three chunks in rotation: one being filled, one queued, one being copied
+        std::vector<Chunk> ring(3);
+        const uint64_t want_pts = std::max<uint64_t>(BATCH, std::min<uint64_t>(chunk_pts, (ps->total_points() + BATCH - 1) / BATCH * BATCH));
+        for (auto& c : ring) {
+            c.mem = pcb_alloc_host(las ? want_pts * las->stride : want_pts * sizeof(pcb_point));
+            if (!c.mem) {
+                log_line("ERROR", "cannot allocate page-locked input chunks");
+                pcb_close(h);
+                return 101;
+            }
         }
-        if (pcb_begin_file(h) != PCB_OK || pcb_add_points(h, keep ? pts.data() : nullptr, keep) != PCB_OK) {
+        std::mutex mu;
+        std::condition_variable cv;
+        size_t filled = 0, consumed = 0;   // chunk k lives in ring[k % 3]
+        bool stop = false;
+        std::thread reader([&] {
+            for (size_t k = 0;; k++) {
+                {
+                    std::unique_lock<std::mutex> lk(mu);
+                    cv.wait(lk, [&] { return stop || k < consumed + ring.size(); });
+                    if (stop) return;
+                }
+                Chunk& c = ring[k % ring.size()];
+                c.raw = las != nullptr;
+                c.status = las ? ps->next_raw(want_pts, (uint8_t*)c.mem, &c.n, &c.message)
+                               : ps->next(want_pts, (pcb_point*)c.mem, &c.n, &c.message);
+                c.last = c.n == 0 || c.status != pcb::READ_OK;
+                const bool last = c.last;
+                {
+                    std::lock_guard<std::mutex> lk(mu);
+                    filled = k + 1;
+                }
+                cv.notify_all();
+                if (last) return;
+            }
+        });
+        bool failed = false, began = false;
+        uint64_t file_points = 0;
+        for (size_t k = 0;; k++) {
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return filled > k; });
+            }
+            Chunk& c = ring[k % ring.size()];
+            uint64_t keep = c.n;
+            if (c.status == pcb::READ_TRUNCATED) {  // lib.rs:36-39: the failing get_batch delivers nothing, the file ends there
+                log_line("ERROR", c.message);
+                keep = (file_points + keep) / BATCH * BATCH - file_points;   // chunks are whole batches: trim the last one
+            }
+            int rc = PCB_OK;
+            // a file without points still yields one (empty) batch (lib.rs:32-34); a file whose FIRST get_batch fails
+            // yields none (lib.rs:36-39)
+            if (keep || (c.last && file_points == 0 && c.status == pcb::READ_OK)) {
+                if (!began) rc = pcb_begin_file(h);
+                began = true;
+                if (rc == PCB_OK)
+                    rc = c.raw ? pcb_add_las_records(h, (const uint8_t*)c.mem, keep, las->stride, las->colour_off, las->scale, las->offset)
+                               : pcb_add_points(h, keep ? (const pcb_point*)c.mem : nullptr, keep);
+            }
+            file_points += keep;
+            const bool last = c.last;
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                consumed = k + 1;
+                if (rc != PCB_OK) stop = true;
+            }
+            cv.notify_all();
+            if (rc != PCB_OK) {
+                failed = true;
+                break;
+            }
+            if (last) break;
+        }
+        reader.join();
+        for (auto& c : ring) pcb_free_host(c.mem);
+        total_added += file_points;
+        if (failed) {
             log_line("ERROR", pcb_last_error(h));
             pcb_close(h);
             return 101;

@@ -83,6 +83,36 @@ __global__ void k_bbox_check(const PcbPoint* __restrict__ pts, u32 n, float S0, 
     }
 }
 
+// Input side: uncompressed LAS point records (fixed stride) -> 16-byte Points on the device.  converter/las.rs:32-41:
+// pos = (x, y, z) as f32 of the scaled f64 coordinates (las 0.8.4: X * scale + offset, one f64 multiply and one f64
+// add, never fused), colour = low byte of each little-endian u16 channel (`as u8`), alpha 255; formats without colour
+// give (0, 0, 0).  A block stages the records of its 256 points in shared memory with coalesced word loads (records
+// are 20-70 bytes at arbitrary alignment), then every thread decodes its own.
+#define LAS_DEC_THREADS 256
+#define LAS_DEC_MAX_STRIDE 96
+__global__ void __launch_bounds__(LAS_DEC_THREADS)
+k_las_decode(const unsigned char* __restrict__ rec, u32 n, u32 stride, int colour_off, double sx, double sy, double sz,
+             double ox, double oy, double oz, PcbPoint* __restrict__ out) {
+    __shared__ u32 s_words[LAS_DEC_THREADS * LAS_DEC_MAX_STRIDE / 4 + 2];
+    const u64 p0 = (u64)blockIdx.x * LAS_DEC_THREADS;
+    const u32 cnt = (u32)min((u64)LAS_DEC_THREADS, (u64)n - p0);
+    const u64 b0 = p0 * stride, b1 = b0 + (u64)cnt * stride;
+    const u64 w0 = b0 >> 2, w1 = (b1 + 3) >> 2;   // `rec` is 4-byte aligned and padded to a multiple of 4 bytes
+    for (u64 w = w0 + threadIdx.x; w < w1; w += LAS_DEC_THREADS) s_words[w - w0] = __ldg((const u32*)rec + w);
+    __syncthreads();
+    if (threadIdx.x >= cnt) return;
+    const unsigned char* p = (const unsigned char*)s_words + (b0 - (w0 << 2)) + (u64)threadIdx.x * stride;
+    auto le32 = [&](int o) { return (i32)((u32)p[o] | ((u32)p[o + 1] << 8) | ((u32)p[o + 2] << 16) | ((u32)p[o + 3] << 24)); };
+    PcbPoint q;
+    q.x = __double2float_rn(__dadd_rn(__dmul_rn((double)le32(0), sx), ox));
+    q.y = __double2float_rn(__dadd_rn(__dmul_rn((double)le32(4), sy), oy));
+    q.z = __double2float_rn(__dadd_rn(__dmul_rn((double)le32(8), sz), oz));
+    u32 rgba = 0xFF000000u;
+    if (colour_off >= 0) rgba |= (u32)p[colour_off] | ((u32)p[colour_off + 2] << 8) | ((u32)p[colour_off + 4] << 16);
+    q.rgba = rgba;
+    out[p0 + threadIdx.x] = q;
+}
+
 // Sort-key layout of a level (host decides, kernels follow):
 //   embedded (PAIRS = false): key = [cell ordinal : cb][Z : bz][Y : by][X : bx][arrival position : pb]
 //   pairs    (PAIRS = true) : key = [cell ordinal : cb][Z][Y][X], value = arrival position

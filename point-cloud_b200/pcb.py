@@ -23,11 +23,14 @@ FLAG_NO_FILES = 1
 FLAG_DEVICE_ONLY = 2
 FLAG_PROFILE = 4
 FLAG_NO_METADATA_FILE = 8
+FLAG_COUNT_BY_DELTA = 16   # GUI-caller accounting (src/plugins/converter.rs:565-573)
+GUI_BATCH_SIZE = 50_000    # src/plugins/converter.rs:600-606
 
 EXPORTS = [
     "pcb_open", "pcb_set_stream", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
     "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
     "pcb_route_bbox", "pcb_route_bbox_static", "pcb_route_histogram", "pcb_route_pack", "pcb_route_scatter",
+    "pcb_add_las_records", "pcb_alloc_host", "pcb_free_host",
     "pcb_add_points_device_batched", "pcb_write_metadata", "pcb_get_config", "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
 
@@ -93,6 +96,11 @@ def load_library():
                                     C.POINTER(C.c_uint32), vp, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                     C.POINTER(C.c_uint64)]
     L.pcb_reserve.argtypes = [vp, C.c_uint64]
+    L.pcb_add_las_records.argtypes = [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.pcb_alloc_host.argtypes = [C.c_uint64]
+    L.pcb_alloc_host.restype = vp
+    L.pcb_free_host.argtypes = [vp]
+    L.pcb_free_host.restype = None
     L.pcb_set_stream.argtypes = [vp, vp]
     L.pcb_finish.argtypes = [vp, C.POINTER(PcbStats)]
     L.pcb_close.argtypes = [vp]
@@ -170,6 +178,12 @@ class Converter:
     def add_points_device_batched(self, device_ptr: int, batch_ptr: int, n: int):
         """Routed points with explicit global batch ordinals (multi-GPU ingest)."""
         self._check(self._L.pcb_add_points_device_batched(self._h, C.c_void_p(device_ptr), C.c_void_p(batch_ptr), n))
+
+    def add_las_records(self, raw, n: int, stride: int, colour_off: int, scale, offset):
+        """Raw uncompressed LAS point records, decoded on the device (converter/las.rs:32-41)."""
+        raw = np.ascontiguousarray(raw, dtype=np.uint8)
+        sc, of = (C.c_double * 3)(*scale), (C.c_double * 3)(*offset)
+        self._check(self._L.pcb_add_las_records(self._h, raw.ctypes.data if n else None, n, stride, colour_off, sc, of))
 
     def config(self):
         a, b, c = C.c_uint32(), C.c_uint32(), C.c_float()

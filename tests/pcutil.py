@@ -44,6 +44,8 @@ def oracle_lib():
         L.orc_hierarchies.argtypes = [C.c_void_p]
         L.orc_arrivals.restype = C.c_uint64
         L.orc_arrivals.argtypes = [C.c_void_p]
+        L.orc_points_by_delta.restype = C.c_int64
+        L.orc_points_by_delta.argtypes = [C.c_void_p]
         L.orc_cell_count.restype = C.c_uint64
         L.orc_cell_count.argtypes = [C.c_void_p]
         L.orc_bounding_box.argtypes = [C.c_void_p, C.c_void_p]
@@ -125,8 +127,10 @@ def oracle_convert(files, out_dir: Optional[str] = None, config=None, batch_size
         L.orc_metadata_json(h, mj, 4096)
         bb = np.zeros(6, dtype=np.float32)
         L.orc_bounding_box(h, bb.ctypes.data)
-        return OracleRun(nodes, mj.value.decode(), L.orc_number_of_points(h), L.orc_hierarchies(h), bb,
-                         L.orc_arrivals(h))
+        run = OracleRun(nodes, mj.value.decode(), L.orc_number_of_points(h), L.orc_hierarchies(h), bb,
+                        L.orc_arrivals(h))
+        run.points_by_delta = L.orc_points_by_delta(h)   # the GUI caller's count (src/plugins/converter.rs:565-573)
+        return run
     finally:
         L.orc_close(h)
 

@@ -288,3 +288,26 @@ def test_level0_sort_path_forced_and_wide_boxes():
     env = dict(os.environ, PCB_ENABLE_TUNING="1", PCB_L0_SORT="1")
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "l0 sort ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_gui_converter_preset_batch_50000_count_by_delta(tmp_path):
+    """Second caller of the boundary: the in-app converter feeds batches of 50 000 points
+    (src/plugins/converter.rs:600-606) and advances number_of_points by the per-cell change of the header total
+    (:565-573) instead of by batch length.  Fresh run and merge run, limit edges included (a list that is flushed
+    reports a NEGATIVE delta in its cell)."""
+    pcb = load_pcb()
+    rng = np.random.default_rng(53)
+    A = make_points(rng.random((180_000, 3)) * [1500, 900, 40] - [700, 400, 5])
+    B = make_points(rng.random((120_001, 3)) * [1500, 900, 40] - [700, 400, 5])
+    for cfg in ((5000, 96, 1000.0), (64, 12, 400.0)):
+        d_o, d_g = str(tmp_path / f"o{cfg[0]}"), str(tmp_path / f"g{cfg[0]}")
+        o1 = oracle_convert([A], out_dir=d_o, config=cfg, batch_size=pcb.GUI_BATCH_SIZE)
+        _, mj1, st1, _ = pcb.convert([A], d_g, config=cfg, batch_size=pcb.GUI_BATCH_SIZE, flags=pcb.FLAG_COUNT_BY_DELTA)
+        assert o1.points_by_delta == len(A) == st1.number_of_points
+        compare_trees(read_tree(d_o), read_tree(d_g), "oracle-50k", "gpu-50k")
+        assert mj1 == o1.meta_json
+        o2 = oracle_convert([B], out_dir=d_o, batch_size=pcb.GUI_BATCH_SIZE)
+        _, mj2, st2, _ = pcb.convert([B], d_g, batch_size=pcb.GUI_BATCH_SIZE, flags=pcb.FLAG_COUNT_BY_DELTA)
+        assert o2.points_by_delta == len(B) and st2.number_of_points == len(A) + o2.points_by_delta
+        compare_trees(read_tree(d_o), read_tree(d_g), "oracle-50k-merge", "gpu-50k-merge")
+        assert mj2 == o2.meta_json
