@@ -143,6 +143,30 @@ int pcb_add_points_device(pcb_handle* h, const pcb_point* d_pts, uint64_t n);
    undivided input stream, each with the ordinal (0-based, global) of the batch it belonged to (lib.rs:31-35 cut
    of the undivided stream).  Device pointers, borrowed until pcb_finish returns; the only add on the handle. */
 int pcb_add_points_device_batched(pcb_handle* h, const pcb_point* d_pts, const uint32_t* d_batch, uint64_t n);
+/* Multi-GPU ingest, generalised: the arrivals of ONE level of the hierarchy in (cell, arrival order), with their CSR -
+   what converter.rs:124-134 would hand to the cells of that level over the whole run.  d_batch_plus1[i] = global batch
+   ordinal + 1 of arrival i (lib.rs:31-35 cut of the undivided stream); d_cell_start[ncell + 1] = first arrival of every
+   cell; d_cell_idx[3 * ncell] = cell indices (metadata.rs:100-102) at `level`, every cell non-empty.  Level 0: what the
+   fused exchange pcb_route_scatter_cells delivers; level l > 0: the pending arrivals of another handle's partial build
+   (pcb_set_stop_level), re-balanced across ranks.  bbox6 (min xyz, max xyz; may be NULL) and count_points update
+   metadata.json's bounding_box / number_of_points like converter.rs:96-108 would.  Device pointers on the handle's
+   device, complete on the handle's stream (pcb_set_stream) and borrowed until pcb_finish returns (in merge mode
+   d_cell_start is updated in place); the only add on the handle. */
+int pcb_add_arrivals(pcb_handle* h, uint32_t level, const pcb_point* d_pts, const uint32_t* d_batch_plus1, uint64_t n,
+                     const uint32_t* d_cell_start, const int32_t* d_cell_idx, uint64_t ncell, const float* bbox6,
+                     uint64_t count_points);
+/* Partial build: pcb_finish builds (and writes) the levels < stop_level only; the arrivals of level stop_level stay on
+   the device and are described by pcb_pending_arrivals (valid until pcb_close).  Call before pcb_finish. */
+int pcb_set_stop_level(pcb_handle* h, uint32_t stop_level);
+typedef struct pcb_arrivals {
+    uint32_t level, reserved;
+    uint64_t n, ncell;
+    const pcb_point* d_pts;
+    const uint32_t* d_batch_plus1;
+    const uint32_t* d_cell_start;   /* [ncell + 1] */
+    const int32_t* d_cell_idx;      /* [3 * ncell] */
+} pcb_arrivals;
+int pcb_pending_arrivals(const pcb_handle* h, pcb_arrivals* out);
 int pcb_finish(pcb_handle* h, pcb_stats* stats);
 /* Metadata::write_to (metadata.rs:51-53) for a reduced result: used by rank 0 after the per-rank builds. */
 int pcb_write_metadata(const char* out_dir, uint64_t number_of_points, uint32_t hierarchies, const float bbox_min[3],
@@ -188,6 +212,20 @@ int pcb_route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t
                       uint32_t batch_size, float max_cell_size, const int32_t origin[3], const uint32_t dims[3],
                       const uint8_t* d_owner, uint32_t world, const uint64_t* recv_pts_ptrs,
                       const uint64_t* recv_batch_ptrs, const uint64_t* recv_offsets);
+
+/* 4b. pcb_route_scatter_cells (world <= 8, level-0 box of at most 512 cells): exchange AND level-0 split in one kernel.
+   d_dst_base[cell] = first slot of this rank's points of `cell` inside the receive buffer of owner[cell] (= first slot
+   of the cell there + the points lower ranks send to it: the caller derives both from the all-gathered per-rank
+   histograms).  Every owner receives its level-0 arrivals in (cell, stream order) with batch ordinal + 1, ready for
+   pcb_add_arrivals(level 0).  d_err (device u32, may be NULL): PCB_DERR bits, non-zero = the pass starved (time-sliced
+   device) and the buffers must not be used. */
+int pcb_route_scatter_cells(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index,
+                            uint32_t batch_size, float max_cell_size, const int32_t origin[3], const uint32_t dims[3],
+                            const uint8_t* d_owner, const uint32_t* d_dst_base, uint32_t world,
+                            const uint64_t* recv_pts_ptrs, const uint64_t* recv_batch_ptrs, uint32_t* d_err);
+/* Deterministic greedy owner plan (largest cell first onto the least loaded rank; host arrays): owner[i] for every
+   cell ordinal i of the histogram `counts`.  A pure function of the global histogram: every rank computes the same. */
+int pcb_plan_owners(const uint64_t* counts, uint64_t ncells, uint32_t world, uint8_t* owner);
 
 /* pcb_route_bbox without any allocation.  NO counterpart in the reference: added
    for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid

@@ -32,6 +32,11 @@ int route_histogram(int device, void* stream, const pcb_point* d_pts, uint64_t n
 int route_pack(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
                float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner, uint32_t world,
                pcb_point* d_send_pts, uint32_t* d_send_batch, uint64_t* send_counts);
+int route_scatter_cells(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
+                        float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner,
+                        const uint32_t* d_dst_base, uint32_t world, const uint64_t* recv_pts_ptrs,
+                        const uint64_t* recv_batch_ptrs, uint32_t* d_err);
+void plan_owners(const uint64_t* counts, uint64_t ncells, uint32_t world, uint8_t* owner);
 int route_bbox_static(int device, void* stream, const pcb_point* d_pts, uint64_t n, float S0, float* d_out6, uint32_t* d_err);
 int route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
                   float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner, uint32_t world,
@@ -239,6 +244,33 @@ int pcb_add_points_device_batched(pcb_handle* h, const pcb_point* d_pts, const u
     PCB_GUARD(h, h->builder->add_points_batched(d_pts, d_batch, n))
 }
 
+int pcb_add_arrivals(pcb_handle* h, uint32_t level, const pcb_point* d_pts, const uint32_t* d_batch_plus1, uint64_t n,
+                     const uint32_t* d_cell_start, const int32_t* d_cell_idx, uint64_t ncell, const float* bbox6,
+                     uint64_t count_points) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    if (h && n && (!d_pts || !d_batch_plus1 || !d_cell_start || !d_cell_idx || !ncell)) return fail(h, PCB_ERR_ARG, "null arrivals");
+    PCB_GUARD(h, h->builder->add_arrivals(level, d_pts, d_batch_plus1, n, d_cell_start, d_cell_idx, ncell, bbox6, count_points))
+}
+
+int pcb_set_stop_level(pcb_handle* h, uint32_t stop_level) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    PCB_GUARD(h, h->builder->set_stop_level(stop_level))
+}
+
+int pcb_pending_arrivals(const pcb_handle* h, pcb_arrivals* out) {
+    if (!h || !out || !h->finished) return PCB_ERR_ARG;
+    const PendingArrivals p = h->builder->pending();
+    out->level = p.level;
+    out->reserved = 0;
+    out->n = p.n;
+    out->ncell = p.ncell;
+    out->d_pts = p.d_pts;
+    out->d_batch_plus1 = p.d_bat;
+    out->d_cell_start = p.d_cell_start;
+    out->d_cell_idx = p.d_cell_idx;
+    return PCB_OK;
+}
+
 int pcb_write_metadata(const char* out_dir, uint64_t number_of_points, uint32_t hierarchies, const float bbox_min[3],
                        const float bbox_max[3], uint32_t limit, uint32_t dim, float max_cell_size) {
     if (!out_dir || !bbox_min || !bbox_max) return PCB_ERR_ARG;
@@ -294,6 +326,25 @@ int pcb_route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t
     if (!origin || !dims || !d_owner || !recv_pts_ptrs || !recv_batch_ptrs || !recv_offsets || (n && !d_pts)) return PCB_ERR_ARG;
     PCB_ROUTE_GUARD(pcb::route_scatter(device, stream, d_pts, n, first_index, batch_size, max_cell_size, origin, dims,
                                        d_owner, world, recv_pts_ptrs, recv_batch_ptrs, recv_offsets))
+}
+
+int pcb_route_scatter_cells(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index,
+                            uint32_t batch_size, float max_cell_size, const int32_t origin[3], const uint32_t dims[3],
+                            const uint8_t* d_owner, const uint32_t* d_dst_base, uint32_t world,
+                            const uint64_t* recv_pts_ptrs, const uint64_t* recv_batch_ptrs, uint32_t* d_err) {
+    if (!origin || !dims || !d_owner || !d_dst_base || !recv_pts_ptrs || !recv_batch_ptrs || (n && !d_pts)) return PCB_ERR_ARG;
+    PCB_ROUTE_GUARD(pcb::route_scatter_cells(device, stream, d_pts, n, first_index, batch_size, max_cell_size, origin, dims,
+                                             d_owner, d_dst_base, world, recv_pts_ptrs, recv_batch_ptrs, d_err))
+}
+
+int pcb_plan_owners(const uint64_t* counts, uint64_t ncells, uint32_t world, uint8_t* owner) {
+    if (!counts || !owner || world == 0 || world > 256) return PCB_ERR_ARG;
+    try {
+        pcb::plan_owners(counts, ncells, world, owner);
+    } catch (const std::exception&) {
+        return PCB_ERR_NOMEM;
+    }
+    return PCB_OK;
 }
 
 int pcb_get_config(const pcb_handle* h, uint32_t* limit, uint32_t* dim, float* max_cell_size) {

@@ -242,6 +242,11 @@ class BuilderImpl {
         }
         if (d_in && !in_borrowed) cudaFree(d_in);
         if (d_raw) cudaFree(d_raw);
+        if (pend_owned) {
+            void* pend[4] = {pend_pts, pend_bat, pend_cell_start, pend_cell_idx};
+            for (void* q : pend)
+                if (q && !in_arena(q)) cudaFreeAsync(q, st);
+        }
         if (d_bat_in && bat_owned) cudaFree(d_bat_in);
         if (d_scr) cudaFreeAsync(d_scr, st);
         if (h_scr) g_pinned.put(h_scr, h_scr_cap);
@@ -251,6 +256,29 @@ class BuilderImpl {
         if (st && own_stream) cudaStreamDestroy(st);
         if (copy_st) cudaStreamDestroy(copy_st);
     }
+
+    // Arrivals of level `ext.level` supplied by the caller in (cell, tau) order with their CSR (multi-GPU: the fused
+    // level-0 exchange delivers them that way; level-l re-balance: the deliveries of another rank's level l - 1).
+    // Device pointers, borrowed until build() returns.  Stage 0 is skipped.
+    struct ExtArrivals {
+        bool set = false;
+        u32 level = 0, n = 0, ncell = 0;
+        const PcbPoint* pts = nullptr;
+        const u32* bat = nullptr;          // batch ordinal + 1
+        const u32* cell_start = nullptr;   // [ncell + 1]
+        const int* cell_idx = nullptr;     // [3 * ncell]
+        bool has_box = false;
+        float lo[3], hi[3];
+        u64 count_points = 0;              // added to metadata.number_of_points (0: counted by another handle)
+    } ext;
+    // partial build: levels >= stop_level are not built; their arrivals stay on the device (pend_*)
+    u32 stop_level = 0xFFFFFFFFu;
+    PcbPoint* pend_pts = nullptr;
+    u32* pend_bat = nullptr;
+    u32* pend_cell_start = nullptr;
+    int* pend_cell_idx = nullptr;
+    u32 pend_n = 0, pend_ncell = 0, pend_level = 0;
+    bool pend_owned = false;
 
     ArenaSet* arenas = nullptr;
     double last_mult = 0;   // arrivals per occupied prism on the level just built (same wave)
@@ -412,7 +440,7 @@ class BuilderImpl {
 
     // batch bookkeeping of n more points of the current input file
     void note_points(u64 n, u32& batch_size, bool one_batch) {
-        if (d_bat_in) throw Error{PCB_ERR_ARG, "points cannot be added after routed points"};
+        if (d_bat_in || ext.set) throw Error{PCB_ERR_ARG, "points cannot be added after routed points"};
         if (n_in + n >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "more than 2^30-1 points on one device"};
         if (one_batch) {
             open_run();
@@ -505,7 +533,32 @@ class BuilderImpl {
         segs.push_back(BatchSeg{0u, 0u, 1u, 0u});
     }
 
+    void add_arrivals(u32 level, const pcb_point* d_pts, const u32* d_bat, u64 n, const u32* d_cell_start,
+                      const int32_t* d_cell_idx, u64 ncell, const float* bbox6, u64 count_points) {
+        CUDA_TRY(cudaSetDevice(device));
+        if (n_in != 0 || batches != 0 || run_open || ext.set) throw Error{PCB_ERR_ARG, "pcb_add_arrivals must be the only add"};
+        if (n >= (1ull << 30) || ncell > n) throw Error{PCB_ERR_RANGE, "bad arrival counts"};
+        if (level >= 32) throw Error{PCB_ERR_RANGE, "octree deeper than 31 levels"};
+        ext.set = true;
+        ext.level = level;
+        ext.n = (u32)n;
+        ext.ncell = (u32)ncell;
+        ext.pts = (const PcbPoint*)d_pts;
+        ext.bat = d_bat;
+        ext.cell_start = d_cell_start;
+        ext.cell_idx = d_cell_idx;
+        ext.has_box = bbox6 != nullptr;
+        if (bbox6)
+            for (int a = 0; a < 3; a++) { ext.lo[a] = bbox6[a]; ext.hi[a] = bbox6[3 + a]; }
+        ext.count_points = count_points;
+        batches = 1;
+        n_in = count_points;   // points_added of this handle
+    }
+
     void build(Metadata* meta, NodeSource* existing);
+    void finish_build(double t_start);
+    void run_levels(Metadata* meta, NodeSource* existing, u32 h0, PcbPoint* pts, u32* bat, u32* cell_start, int* cell_idx,
+                    u32 n0, u32 ncell);
     template <bool PAIRS>
     void build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start, int*& cell_idx, u32& n, u32& ncell,
                      NodeSource* existing);
@@ -515,6 +568,7 @@ class BuilderImpl {
     // launches) until the per-level arrays (72 B per arrival, twice) would crowd the device.
     u64 wave_points(u64 n0) const {
         static const u64 forced = pcb_tuning_env("PCB_WAVE_POINTS") ? strtoull(pcb_tuning_env("PCB_WAVE_POINTS"), nullptr, 10) : 0;
+        if (stop_level != 0xFFFFFFFFu) return 1ull << 40;   // a partial build keeps ONE set of pending arrivals: one wave
         if (forced) return forced;
         if (flags & PCB_FLAG_DEVICE_ONLY) return 400ull << 20;
         return std::min<u64>(std::max<u64>(n0 / 4, 16ull << 20), 400ull << 20);
@@ -573,12 +627,39 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     if (dim == 0 || !(max_cell_size > 0.0f) || !std::isfinite(max_cell_size))
         throw Error{PCB_ERR_ARG, "bad config (sub_grid_dimension / max_cell_size)"};
     if (batches == 0) return;                                   // nothing was ever added
+    if (!d_scr) CUDA_TRY(cudaMallocAsync((void**)&d_scr, sizeof(Scratch), st));
+    if (!arenas) arenas = g_arenas.acquire(device);
+    if (ext.set) {
+        // ---- arrivals of one level handed in with their CSR: no stage 0
+        if (ext.level == 0) meta->hierarchies = std::max<uint32_t>(meta->hierarchies, 1);
+        if (ext.has_box && ext.count_points) {
+            if (meta->number_of_points == 0) {              // converter.rs:98-99: first points REPLACE the box
+                for (int a = 0; a < 3; a++) { meta->bbox_min[a] = ext.lo[a]; meta->bbox_max[a] = ext.hi[a]; }
+            } else {                                        // converter.rs:100-102
+                for (int a = 0; a < 3; a++) {
+                    meta->bbox_min[a] = std::fmin(meta->bbox_min[a], ext.lo[a]);
+                    meta->bbox_max[a] = std::fmax(meta->bbox_max[a], ext.hi[a]);
+                }
+            }
+        }
+        meta->number_of_points += ext.count_points;         // converter.rs:108
+        if (ext.n) {
+            Scratch init;
+            memset(&init, 0, sizeof init);
+            *h_scr = init;
+            CUDA_TRY(cudaMemcpyAsync(d_scr, h_scr, sizeof init, cudaMemcpyHostToDevice, st));
+            arena_prepare(2, 18ull * ext.n + (64ull << 20));
+            cur_arena = 0;
+            run_levels(meta, existing, ext.level, (PcbPoint*)ext.pts, (u32*)ext.bat, (u32*)ext.cell_start, (int*)ext.cell_idx,
+                       ext.n, ext.ncell);
+        }
+        finish_build(t_start);
+        return;
+    }
     meta->hierarchies = std::max<uint32_t>(meta->hierarchies, 1);  // converter.rs:111,120: level 0 always visited
     if (n_in == 0) return;
     const u32 n0 = (u32)n_in;
     const float S0 = max_cell_size;
-    if (!d_scr) CUDA_TRY(cudaMallocAsync((void**)&d_scr, sizeof(Scratch), st));
-    if (!arenas) arenas = g_arenas.acquire(device);
     // Arena 0 first serves the level-0 staging (keys A/B, histograms, look-back state: ~17 B per point); arenas 0/1
     // are sized for the largest wave once the level-0 cells are known (below).  Sizes only ever grow, so a process
     // that converts clouds of one size allocates once.
@@ -644,15 +725,15 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
         CUDA_TRY(cudaMemsetAsync(tmp, 0, 4 * words, st));
         u32 *lhist = tmp, *dbase = tmp + nb, *status = tmp + 2ull * nb;
         const int smem = L0S_TILE * 22 + (L0S_WARPS + 2) * (int)nb * 4;
-        CUDA_TRY(cudaFuncSetAttribute(k_l0_split, cudaFuncAttributeMaxDynamicSharedMemorySize, L0SplitSmem::bytes));
-        CUDA_TRY(cudaFuncSetAttribute(k_l0_split, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        CUDA_TRY(cudaFuncSetAttribute(k_l0_split<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L0SplitSmem::bytes));
+        CUDA_TRY(cudaFuncSetAttribute(k_l0_split<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
         pb();
         k_route_hist<<<grid_big, 256, 0, st>>>(d_in, n0, S0, box, nb, lhist);
         k_l0_cells<<<1, L0S_MAX_BINS, 0, st>>>(lhist, nb, box, n0, dbase, cell_start, cell_idx, &d_scr->ncell);
         pe("l0_hist", 2, n0, 16ull * n0);
         pb();
-        k_l0_split<<<ntiles, L0S_THREADS, smem, st>>>(d_in, n0, S0, box, nb, dbits, dbase, d_segs, (u32)segs.size(), d_bat_in,
-                                                      pts, bat, status, &d_scr->err);
+        k_l0_split<false><<<ntiles, L0S_THREADS, smem, st>>>(d_in, n0, S0, box, nb, dbits, dbase, d_segs, (u32)segs.size(),
+                                                             d_bat_in, pts, bat, status, &d_scr->err, nullptr, RouteDst(), 0, 1);
         pe("l0_split", 1, n0, 36ull * n0);
         dfree(tmp);
     } else {
@@ -688,10 +769,31 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     trace_mark(st, "l0_gather", 0, n0);
     dfree(d_segs);
 
-    // ---- waves of level-0 cells.  Level-0 cells never interact (converter.rs:124-134: a cell only receives from
-    // its parent), so the forest is built a contiguous group of level-0 cells at a time: the node images of one
-    // wave travel to the host while the next wave is built, and the per-level arrays are sized for a wave, not
-    // for the run.
+    run_levels(meta, existing, 0, pts, bat, cell_start, cell_idx, n0, ncell);
+    dfree(pts); dfree(bat); dfree(cell_start); dfree(cell_idx);
+    finish_build(t_start);
+}
+
+void BuilderImpl::finish_build(double t_start) {
+    CUDA_TRY(cudaStreamSynchronize(st));
+    build_s += now_s() - t_start;
+    double t1 = now_s();
+    CUDA_TRY(cudaStreamSynchronize(copy_st));
+    d2h_s += now_s() - t1;
+    for (auto& l : levels)
+        if (l.h_image && l.d_image) {
+            dfree(l.d_image);
+            l.d_image = nullptr;
+        }
+    prof_collect();
+}
+
+// The levels from h0 down for the cells of level h0 given by (pts, bat, cell_start, cell_idx): arrivals in (cell, tau)
+// order, borrowed.  Cells of one level never interact (converter.rs:124-134: a cell only receives from its parent), so
+// the forest is built a contiguous group of them ("wave") at a time: the node images of one wave travel to the host
+// while the next wave is built, and the per-level arrays are sized for a wave, not for the run.
+void BuilderImpl::run_levels(Metadata* meta, NodeSource* existing, u32 h0, PcbPoint* pts, u32* bat, u32* cell_start,
+                             int* cell_idx, u32 n0, u32 ncell) {
     u32* const h_cs = (u32*)host_tmp(4ull * ((u64)ncell + 1));
     publish(h_cs, cell_start, 4ull * ((u64)ncell + 1));
     CUDA_TRY(cudaStreamSynchronize(st));
@@ -717,21 +819,23 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
     }
     arena_prepare(0, std::max<u64>(arenas->a[0].cap, 72ull * wave_max + (64ull << 20)));
     arena_prepare(1, std::max<u64>(arenas->a[1].cap, 72ull * wave_max + (64ull << 20)));
-    u32 hmax = 0, c0 = 0;
+    u32 hmax = h0, c0 = 0;
     for (u32 c1 : wave_end) {
-        u32 n = h_cs[c1] - h_cs[c0], wcell = c1 - c0, h = 0;
+        u32 n = h_cs[c1] - h_cs[c0], wcell = c1 - c0, h = h0;
         PcbPoint* wpts = pts + h_cs[c0];
         u32* wbat = bat + h_cs[c0];
         int* widx = cell_idx + 3ull * c0;
         u32* wstart = cell_start;
         if (wave_end.size() > 1) {
-            cur_arena = 1;                    // level 0 of the wave resets arena 0 and reads its inputs from arena 1
-            arenas->a[1].off = 0;
+            // the wave's first level (h0) resets arena h0 & 1 and reads its inputs from the other one
+            cur_arena = (int)((h0 & 1u) ^ 1u);
+            arenas->a[cur_arena].off = 0;
             wstart = dalloc<u32>((u64)wcell + 1);
             k_wave_starts<<<div_up(wcell + 1, 256), 256, 0, st>>>(cell_start + c0, h_cs[c0], wcell + 1, wstart);
         }
-        inputs_borrowed = true;               // the wave's level-0 inputs are slices of the run's arrays
-        while (n) {
+        bool first = true;                    // the wave's first inputs are slices of the run's arrays: not freed
+        inputs_borrowed = true;
+        while (n && h < stop_level) {
             if (h >= 32) throw Error{PCB_ERR_RANGE, "octree deeper than 31 levels (reference overflows 2u32.pow, metadata.rs:92)"};
             meta->hierarchies = std::max<uint32_t>(meta->hierarchies, h + 1);  // converter.rs:141-144
             if (pairs_mode_for(n, wcell, make_geom(max_cell_size, dim, h)))
@@ -739,28 +843,24 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
             else
                 build_level<false>(h, wpts, wbat, wstart, widx, n, wcell, existing);
             inputs_borrowed = false;
+            first = false;
             h++;
         }
-        dfree(wpts); dfree(wbat); dfree(wstart); dfree(widx);   // (empty) inputs of the level that was not built
+        if (n && h >= stop_level) {
+            // partial build (single wave): the arrivals of level `stop_level` stay on the device for the caller
+            pend_pts = wpts; pend_bat = wbat; pend_cell_start = wstart; pend_cell_idx = widx;
+            pend_n = n; pend_ncell = wcell; pend_level = h;
+            pend_owned = !first;
+        } else if (!first) {
+            dfree(wpts); dfree(wbat); dfree(wstart); dfree(widx);   // (empty) inputs of the level that was not built
+        }
+        inputs_borrowed = false;
         hmax = std::max(hmax, h);
         c0 = c1;
         trace_mark(st, "wave done", hmax, c1);
     }
-    const u32 h = hmax;
-    levels_built = h;
+    levels_built = hmax - h0;
     trace_mark(st, "levels done");
-    dfree(pts); dfree(bat); dfree(cell_start); dfree(cell_idx);
-    CUDA_TRY(cudaStreamSynchronize(st));
-    build_s += now_s() - t_start;
-    double t1 = now_s();
-    CUDA_TRY(cudaStreamSynchronize(copy_st));
-    d2h_s += now_s() - t1;
-    for (auto& l : levels)
-        if (l.h_image && l.d_image) {
-            dfree(l.d_image);
-            l.d_image = nullptr;
-        }
-    prof_collect();
 }
 
 bool BuilderImpl::pairs_mode_for(u32 n, u32 ncell, const LevelGeom& g) {
@@ -1230,6 +1330,23 @@ void Builder::add_las_records(const uint8_t* records, uint64_t n, uint32_t strid
 }
 void* Builder::alloc_host(uint64_t bytes, uint64_t* got) { return guarded([&] { return g_pinned.get(bytes, got); }); }
 void Builder::free_host(void* p, uint64_t bytes) { g_pinned.put(p, bytes); }
+void Builder::add_arrivals(uint32_t level, const pcb_point* d_pts, const uint32_t* d_bat, uint64_t n,
+                           const uint32_t* d_cell_start, const int32_t* d_cell_idx, uint64_t ncell, const float* bbox6,
+                           uint64_t count_points) {
+    guarded([&] { impl_->add_arrivals(level, d_pts, d_bat, n, d_cell_start, d_cell_idx, ncell, bbox6, count_points); return 0; });
+}
+void Builder::set_stop_level(uint32_t level) { impl_->stop_level = level; }
+PendingArrivals Builder::pending() const {
+    PendingArrivals p;
+    p.level = impl_->pend_level;
+    p.n = impl_->pend_n;
+    p.ncell = impl_->pend_ncell;
+    p.d_pts = (const pcb_point*)impl_->pend_pts;
+    p.d_bat = impl_->pend_bat;
+    p.d_cell_start = impl_->pend_cell_start;
+    p.d_cell_idx = impl_->pend_cell_idx;
+    return p;
+}
 void Builder::add_points_one_batch(const pcb_point* pts, uint64_t n, bool device_ptr) {
     guarded([&] { impl_->add(pts, n, 0, device_ptr, true); return 0; });
 }
@@ -1396,6 +1513,73 @@ int route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t n, 
         CUDA_TRY(cudaFreeAsync(desc, st));
         return 1;
     });
+}
+
+// Level-0 exchange fused with the level-0 split (world <= 8, level-0 box of at most 512 cells): ONE pass reads every
+// point of the slice and stores it, with its global batch ordinal + 1, at its final level-0 arrival slot in the
+// receive buffer of the rank that owns its cell: d_dst_base[cell] = (first slot of the cell in the owner's buffer) +
+// (points of lower ranks in the cell).  The owner then builds straight from pcb_add_arrivals(level 0).
+int route_scatter_cells(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
+                        float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner,
+                        const uint32_t* d_dst_base, uint32_t world, const uint64_t* recv_pts_ptrs,
+                        const uint64_t* recv_batch_ptrs, uint32_t* d_err) {
+    return guarded([&] {
+        CUDA_TRY(cudaSetDevice(device));
+        cudaStream_t st = (cudaStream_t)stream;
+        if (!n) return 0;
+        const u64 vol = (u64)dims[0] * dims[1] * dims[2];
+        if (n >= (1ull << 30) || world == 0 || world > 8 || batch_size == 0 || vol == 0 || vol > L0S_MAX_BINS)
+            throw Error{PCB_ERR_ARG, "bad routing arguments (fused cell scatter: world <= 8, level-0 box <= 512 cells)"};
+        RouteDst dst8;
+        for (u32 o = 0; o < 8; o++) {
+            const u32 q = o < world ? o : 0;
+            dst8.pts[o] = (PcbPoint*)(uintptr_t)recv_pts_ptrs[q];
+            dst8.bat[o] = (u32*)(uintptr_t)recv_batch_ptrs[q];
+            dst8.off[o] = 0;
+        }
+        const u32 nb = (u32)vol, ntiles = div_up(n, L0S_TILE);
+        const int dbits = std::max(1, bits_count(vol));
+        struct Tmp {   // look-back status words; freed on every path
+            u32* p = nullptr;
+            cudaStream_t st;
+            ~Tmp() { if (p) cudaFreeAsync(p, st); }
+        } tmp;
+        tmp.st = st;
+        const u64 words = (u64)ntiles * nb + 4;
+        CUDA_TRY(cudaMallocAsync((void**)&tmp.p, 4 * words, st));
+        CUDA_TRY(cudaMemsetAsync(tmp.p, 0, 4 * words, st));
+        const int smem = L0S_TILE * 22 + (L0S_WARPS + 2) * (int)nb * 4;
+        static bool attr_set = false;
+        if (!attr_set) {
+            CUDA_TRY(cudaFuncSetAttribute(k_l0_split<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L0SplitSmem::bytes));
+            CUDA_TRY(cudaFuncSetAttribute(k_l0_split<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+            attr_set = true;
+        }
+        k_l0_split<true><<<ntiles, L0S_THREADS, smem, st>>>((const PcbPoint*)d_pts, (u32)n, S0, make_box(origin, dims), nb, dbits,
+                                                            d_dst_base, nullptr, 0, nullptr, nullptr, nullptr, tmp.p,
+                                                            d_err, d_owner, dst8, first_index, batch_size);
+        CUDA_TRY(cudaGetLastError());
+        return 1;
+    });
+}
+
+// Deterministic greedy bin packing of cells onto ranks: largest cell first (ties: lower cell ordinal), onto the least
+// loaded rank (ties: lower rank).  A pure function of the global histogram, so every rank computes the same plan.
+void plan_owners(const uint64_t* counts, uint64_t ncells, uint32_t world, uint8_t* owner) {
+    std::vector<uint64_t> order;
+    order.reserve(ncells);
+    for (uint64_t i = 0; i < ncells; i++)
+        if (counts[i]) order.push_back(i);
+    std::stable_sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) { return counts[a] > counts[b]; });
+    std::vector<uint64_t> load(world, 0);
+    for (uint64_t i = 0; i < ncells; i++) owner[i] = 0;
+    for (uint64_t i : order) {
+        uint32_t r = 0;
+        for (uint32_t q = 1; q < world; q++)
+            if (load[q] < load[r]) r = q;
+        owner[i] = (uint8_t)r;
+        load[r] += counts[i];
+    }
 }
 
 // ---- allocation-free bounding box (no counterpart in the reference) ----

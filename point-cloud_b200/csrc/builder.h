@@ -69,6 +69,16 @@ struct KernelStat {
     double ms = 0;
 };
 
+// arrivals of the first level a partial build did not build (device pointers, valid while the Builder lives)
+struct PendingArrivals {
+    uint32_t level = 0;
+    uint64_t n = 0, ncell = 0;
+    const pcb_point* d_pts = nullptr;
+    const uint32_t* d_bat = nullptr;          // batch ordinal + 1
+    const uint32_t* d_cell_start = nullptr;   // [ncell + 1]
+    const int32_t* d_cell_idx = nullptr;      // [3 * ncell]
+};
+
 class BuilderImpl;
 class Builder {
    public:
@@ -81,6 +91,12 @@ class Builder {
     void add_points(const pcb_point* pts, uint64_t n, uint32_t batch_size, bool device_ptr);
     void add_points_one_batch(const pcb_point* pts, uint64_t n, bool device_ptr);  // converter.rs:106
     void add_points_batched(const pcb_point* d_pts, const uint32_t* d_batch, uint64_t n);  // explicit batch ordinals
+    // arrivals of one level in (cell, tau) order with their CSR (multi-GPU); device pointers, borrowed; the only add
+    void add_arrivals(uint32_t level, const pcb_point* d_pts, const uint32_t* d_bat_plus1, uint64_t n,
+                      const uint32_t* d_cell_start, const int32_t* d_cell_idx, uint64_t ncell, const float* bbox6,
+                      uint64_t count_points);
+    void set_stop_level(uint32_t level);   // build() stops before this level; its arrivals stay on the device
+    PendingArrivals pending() const;
     // uncompressed LAS point records (host bytes), decoded on the device (converter/las.rs:32-41)
     void add_las_records(const uint8_t* records, uint64_t n, uint32_t stride, int32_t colour_off, const double scale[3],
                          const double offset[3], uint32_t batch_size);

@@ -273,11 +273,21 @@ struct L0SplitSmem {
                                  2 * L0S_MAX_BINS * 4;
 };
 
+// ROUTE (multi-GPU, route.cuh): the same pass IS the level-0 exchange - cell d's points go to the receive buffer of rank
+// owner[d] (peer-mapped memory reached over NVLink, or local memory), at slot dbase[d] + rank among this slice's points
+// of d, with their global batch ordinal (first_index + i) / route_batch + 1: every owner receives its level-0 arrivals
+// already in (cell, stream order), no second split on the receiving side.
+struct RouteDst {
+    PcbPoint* pts[8];
+    u32* bat[8];
+    u32 off[8];
+};
+template <bool ROUTE>
 __global__ void __launch_bounds__(L0S_THREADS, 4)   // 64 registers, four blocks per SM (three: 1.63 ms, four: 1.37 ms per 100 M points)
 k_l0_split(const PcbPoint* __restrict__ in_pts, u32 n, float S0, L0Box box, u32 nb, int bits,
            const u32* __restrict__ dbase, const BatchSeg* __restrict__ segs, u32 nseg, const u32* __restrict__ in_bat,
            PcbPoint* __restrict__ pts, u32* __restrict__ bat, u32* __restrict__ status /* [ntiles][nb] */,
-           u32* __restrict__ err = nullptr) {
+           u32* __restrict__ err, const unsigned char* __restrict__ owner, RouteDst dst8, u64 first_index, u32 route_batch) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint4* s_pts = (uint4*)smem_raw;
     u32* s_idx = (u32*)(s_pts + L0S_TILE);
@@ -286,11 +296,14 @@ k_l0_split(const PcbPoint* __restrict__ in_pts, u32 n, float S0, L0Box box, u32 
     u32* dig_excl = cnt + L0S_WARPS * nb;
     u32* gbase = dig_excl + nb;
     __shared__ u32 s_warp_sums[L0S_WARPS];
+    __shared__ unsigned char s_own[ROUTE ? L0S_MAX_BINS : 4];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const u32 tile = blockIdx.x;   // tile = block index, see k_chain_scan
     const u64 tbase = (u64)tile * L0S_TILE;
     const u32 tile_n = (u32)min((u64)L0S_TILE, (u64)n - tbase);
     for (u32 i = tid; i < L0S_WARPS * nb; i += L0S_THREADS) cnt[i] = 0;
+    if (ROUTE)
+        for (u32 i = tid; i < nb; i += L0S_THREADS) s_own[i] = owner[i] & 7u;
     __syncthreads();
 
     // warp-striped ownership: item k of lane l in warp w is element w * 32 * ITEMS + 32 k + l of the tile
@@ -423,6 +436,19 @@ k_l0_split(const PcbPoint* __restrict__ in_pts, u32 n, float S0, L0Box box, u32 
     for (u32 j = tid; j < tile_n; j += L0S_THREADS) {
         const u32 g = gbase[s_dig[j]] + j;
         const u32 i = s_idx[j];
+        if (ROUTE) {
+            const u32 o = s_own[s_dig[j]];
+            PcbPoint* dp = nullptr;
+            u32* db = nullptr;
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                dp = (o == (u32)q) ? dst8.pts[q] : dp;
+                db = (o == (u32)q) ? dst8.bat[q] : db;
+            }
+            *(uint4*)(dp + g) = s_pts[j];
+            db[g] = (u32)((first_index + i) / route_batch) + 1u;
+            continue;
+        }
         *(uint4*)(pts + g) = s_pts[j];
         u32 b;
         if (in_bat) {

@@ -143,13 +143,9 @@ __global__ void k_route_owner_counts(const u32* __restrict__ lhist, u32 vol, con
     }
 }
 
-// Where owner o's points go: slot off[o] (+ dev_bases[o] when given) of (pts[o], bat[o]).  All eight equal = a local
-// send buffer; peer-mapped receive buffers of the other ranks = the exchange itself (stores travel over NVLink).
-struct RouteDst {
-    PcbPoint* pts[8];
-    u32* bat[8];
-    u32 off[8];
-};
+// Where owner o's points go: slot off[o] (+ dev_bases[o] when given) of (pts[o], bat[o]) - struct RouteDst, level.cuh.
+// All eight equal = a local send buffer; peer-mapped receive buffers of the other ranks = the exchange itself (stores
+// travel over NVLink).
 __global__ void __launch_bounds__(ROUTE_SPLIT_THREADS)
 k_route_split(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, const unsigned char* __restrict__ owner,
               const u32* __restrict__ dev_bases, u64 first_index, u32 batch_size, RouteDst dst8, u32 world,

@@ -30,7 +30,8 @@ EXPORTS = [
     "pcb_open", "pcb_set_stream", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
     "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
     "pcb_route_bbox", "pcb_route_bbox_static", "pcb_route_histogram", "pcb_route_pack", "pcb_route_scatter",
-    "pcb_add_las_records", "pcb_alloc_host", "pcb_free_host",
+    "pcb_add_las_records", "pcb_alloc_host", "pcb_free_host", "pcb_add_arrivals", "pcb_set_stop_level", "pcb_pending_arrivals",
+    "pcb_route_scatter_cells", "pcb_plan_owners",
     "pcb_add_points_device_batched", "pcb_write_metadata", "pcb_get_config", "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
 
@@ -56,6 +57,12 @@ class PcbKernelStat(C.Structure):
 
 class PcbNodeInfo(C.Structure):
     _fields_ = [("hierarchy", C.c_uint32), ("index", C.c_int32 * 3), ("offset", C.c_uint64), ("size", C.c_uint64)]
+
+
+class PcbArrivals(C.Structure):
+    _fields_ = [("level", C.c_uint32), ("reserved", C.c_uint32), ("n", C.c_uint64), ("ncell", C.c_uint64),
+                ("d_pts", C.c_void_p), ("d_batch_plus1", C.c_void_p), ("d_cell_start", C.c_void_p),
+                ("d_cell_idx", C.c_void_p)]
 
 
 class PcbError(RuntimeError):
@@ -96,6 +103,13 @@ def load_library():
                                     C.POINTER(C.c_uint32), vp, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                     C.POINTER(C.c_uint64)]
     L.pcb_reserve.argtypes = [vp, C.c_uint64]
+    L.pcb_add_arrivals.argtypes = [vp, C.c_uint32, vp, vp, C.c_uint64, vp, vp, C.c_uint64, C.POINTER(C.c_float), C.c_uint64]
+    L.pcb_set_stop_level.argtypes = [vp, C.c_uint32]
+    L.pcb_pending_arrivals.argtypes = [vp, C.POINTER(PcbArrivals)]
+    L.pcb_route_scatter_cells.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_uint64, C.c_uint32, C.c_float, C.POINTER(C.c_int32),
+                                          C.POINTER(C.c_uint32), vp, vp, C.c_uint32, C.POINTER(C.c_uint64),
+                                          C.POINTER(C.c_uint64), vp]
+    L.pcb_plan_owners.argtypes = [vp, C.c_uint64, C.c_uint32, vp]
     L.pcb_add_las_records.argtypes = [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.pcb_alloc_host.argtypes = [C.c_uint64]
     L.pcb_alloc_host.restype = vp
@@ -178,6 +192,22 @@ class Converter:
     def add_points_device_batched(self, device_ptr: int, batch_ptr: int, n: int):
         """Routed points with explicit global batch ordinals (multi-GPU ingest)."""
         self._check(self._L.pcb_add_points_device_batched(self._h, C.c_void_p(device_ptr), C.c_void_p(batch_ptr), n))
+
+    def add_arrivals(self, level: int, pts_ptr: int, bat_ptr: int, n: int, cell_start_ptr: int, cell_idx_ptr: int,
+                     ncell: int, bbox6=None, count_points: int = 0):
+        """Arrivals of one level in (cell, arrival order) with their CSR - pcb_add_arrivals (device pointers)."""
+        box = (C.c_float * 6)(*[float(v) for v in bbox6]) if bbox6 is not None else None
+        self._check(self._L.pcb_add_arrivals(self._h, level, C.c_void_p(pts_ptr), C.c_void_p(bat_ptr), n,
+                                             C.c_void_p(cell_start_ptr), C.c_void_p(cell_idx_ptr), ncell, box, count_points))
+
+    def set_stop_level(self, level: int):
+        """finish() builds the levels < level only; pending() then describes the arrivals of `level`."""
+        self._check(self._L.pcb_set_stop_level(self._h, level))
+
+    def pending(self) -> PcbArrivals:
+        a = PcbArrivals()
+        self._check(self._L.pcb_pending_arrivals(self._h, C.byref(a)))
+        return a
 
     def add_las_records(self, raw, n: int, stride: int, colour_off: int, scale, offset):
         """Raw uncompressed LAS point records, decoded on the device (converter/las.rs:32-41)."""
@@ -287,6 +317,28 @@ def route_scatter(device, stream, pts_ptr, n, first_index, batch_size, max_cell_
     return _route_check(load_library().pcb_route_scatter(device, C.c_void_p(stream), C.c_void_p(pts_ptr), n, first_index,
                                                          batch_size, max_cell_size, o, d, C.c_void_p(owner_ptr), world,
                                                          pp, pb, po))
+
+
+def route_scatter_cells(device, stream, pts_ptr, n, first_index, batch_size, max_cell_size, origin, dims, owner_ptr,
+                        dst_base_ptr, world, recv_pts_ptrs, recv_bat_ptrs, err_ptr=0):
+    """pcb_route_scatter_cells: level-0 exchange fused with the level-0 split (world <= 8, <= 512 level-0 cells)."""
+    o, d = (C.c_int32 * 3)(*origin), (C.c_uint32 * 3)(*dims)
+    pp = (C.c_uint64 * world)(*[int(v) for v in recv_pts_ptrs])
+    pb = (C.c_uint64 * world)(*[int(v) for v in recv_bat_ptrs])
+    return _route_check(load_library().pcb_route_scatter_cells(device, C.c_void_p(stream), C.c_void_p(pts_ptr), n, first_index,
+                                                               batch_size, max_cell_size, o, d, C.c_void_p(owner_ptr),
+                                                               C.c_void_p(dst_base_ptr), world, pp, pb,
+                                                               C.c_void_p(err_ptr) if err_ptr else None))
+
+
+def plan_owners(counts, world: int) -> np.ndarray:
+    """pcb_plan_owners: deterministic greedy owner plan over a histogram -> uint8 owner per cell."""
+    c = np.ascontiguousarray(counts, dtype=np.uint64)
+    out = np.zeros(len(c), dtype=np.uint8)
+    rc = load_library().pcb_plan_owners(c.ctypes.data, len(c), world, out.ctypes.data)
+    if rc != 0:
+        raise PcbError(rc, "pcb_plan_owners failed")
+    return out
 
 
 def write_metadata(out_dir, number_of_points, hierarchies, bbox_min, bbox_max, config):
