@@ -321,3 +321,308 @@ def route_device(pcb, pts_u8: torch.Tensor, first_index: int, batch_size: int, m
     info["exchange"] = "NCCL all-to-all-v" + (f" (p2p unavailable: {_P2P['why']})" if _P2P.get("why") else "")
     _mark("all-to-all")
     return recv_pts, recv_bat, info
+
+
+# ---- level-0 exchange fused with the level-0 split (pcb_route_scatter_cells) ------------------------------------------
+def _collective_ok(ok: bool, dev, group) -> bool:
+    """all ranks agree: True only if every rank says ok (one all-reduce)"""
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    return bool(flag.item())
+
+
+def cell_plan(H, owners, rank):
+    """Pure host logic of the fused exchange (exercised by the gloo tests).  H: (world, vol) per-rank dense level-0
+    histograms (numpy int64), owners: (vol,) owner rank per dense cell.  Returns
+      dst_base (vol,) uint32: first slot of THIS rank's points of every cell inside its owner's receive buffer,
+      recv (world,) int64: points every owner receives,
+      my_cells: dense ids of the cells this rank owns (non-empty, ascending), my_start (len + 1,) uint32 their CSR."""
+    import numpy as np
+    world, vol = H.shape
+    total = H.sum(0)
+    excl = np.cumsum(H, axis=0) - H                       # points of lower ranks per cell
+    start = np.zeros(vol, dtype=np.int64)
+    recv = np.zeros(world, dtype=np.int64)
+    for o in range(world):
+        mine = owners == o
+        c = np.cumsum(np.where(mine, total, 0))
+        start[mine] = (c - total)[mine]
+        recv[o] = int(c[-1]) if vol else 0
+    dst_base = (start + excl[rank]).astype(np.uint32)
+    sel = np.nonzero((owners == rank) & (total > 0))[0]
+    my_start = np.concatenate([start[sel], [recv[rank]]]).astype(np.uint32)
+    return dst_base, recv, sel, my_start
+
+
+def _level0_box(glo, ghi, max_cell_size):
+    import numpy as np
+    s = np.float32(max_cell_size)
+    origin = [int(np.floor(np.float32(v) / s)) for v in glo]      # metadata.rs:100-102 at level 0
+    dims = [int(np.floor(np.float32(v) / s)) - o + 1 for v, o in zip(ghi, origin)]
+    return origin, dims
+
+
+def _cell_indices(cells, origin, dims):
+    import numpy as np
+    idx = np.empty((len(cells), 3), dtype=np.int32)
+    idx[:, 0] = origin[0] + cells % dims[0]
+    idx[:, 1] = origin[1] + (cells // dims[0]) % dims[1]
+    idx[:, 2] = origin[2] + cells // (dims[0] * dims[1])
+    return idx
+
+
+def route_cells(pcb, pts_u8: torch.Tensor, first_index: int, batch_size: int, max_cell_size: float, group=None,
+                stream=None):
+    """Steps 1-4 as ONE pass over the slice: bounding box -> dense level-0 histogram -> all-gather of the per-rank
+    histograms -> owner plan (pcb_plan_owners) -> pcb_route_scatter_cells stores every point, with its global batch
+    ordinal + 1, at its final level-0 arrival slot in its owner's receive buffer (symmetric memory, NVLink stores).
+    Returns a dict for Converter.add_arrivals(level 0) - or None when the fused path does not apply (level-0 box wider
+    than 512 cells, more than 8 ranks, no peer-mapped memory): callers then use route_device.  The decision is
+    collective: every rank returns None or none does."""
+    import math
+    import numpy as np
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    dev = pts_u8.device
+    n = pts_u8.shape[0]
+    st = stream if stream is not None else torch.cuda.current_stream(dev)
+    sp = st.cuda_stream
+    if world < 2 or world > 8 or not _P2P["enabled"]:
+        return None
+    launches = 0
+    lo, hi, nl = pcb.route_bbox(dev.index, sp, pts_u8.data_ptr(), n, max_cell_size)
+    launches += nl
+    box = torch.tensor(lo + [-v for v in hi], dtype=torch.float32, device=dev)   # min of (lo, -hi)
+    dist.all_reduce(box, op=dist.ReduceOp.MIN, group=group)
+    b = box.cpu().tolist()
+    glo, ghi = b[:3], [-v for v in b[3:]]
+    if not all(math.isfinite(v) for v in glo + ghi):       # no points anywhere
+        return None
+    origin, dims = _level0_box(glo, ghi, max_cell_size)
+    vol = dims[0] * dims[1] * dims[2]
+    if vol > 512:
+        return None
+    hist = torch.empty(vol, dtype=torch.int32, device=dev)
+    launches += pcb.route_histogram(dev.index, sp, pts_u8.data_ptr(), n, max_cell_size, origin, dims, hist.data_ptr())
+    allh = torch.empty(world * vol, dtype=torch.int32, device=dev)
+    dist.all_gather_into_tensor(allh, hist, group=group)
+    H = allh.view(world, vol).cpu().numpy().astype(np.int64)
+    owners = pcb.plan_owners(H.sum(0), world)
+    dst_base, recv, my_cells, my_start = cell_plan(H, owners, rank)
+    try:   # receive buffers in symmetric memory; _p2p_buffers agrees on the outcome collectively
+        buf, hdl, cap = _p2p_buffers(dev, group, int(recv.max()))
+    except _P2PUnavailable as e:
+        _P2P["enabled"] = False
+        _P2P["why"] = str(e)
+        return None
+    ptrs = _P2P["ptrs"]
+    tab = torch.from_numpy(np.concatenate([dst_base.view(np.uint8), owners.astype(np.uint8)])).to(dev)
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+    m = int(recv[rank])
+    cs = torch.from_numpy(my_start.view(np.int32).copy()).to(dev)
+    ci = torch.from_numpy(_cell_indices(my_cells, origin, dims).reshape(-1).copy()).to(dev)
+    with torch.cuda.stream(st):
+        hdl.barrier(channel=0)                     # every rank is done with the previous contents
+        launches += pcb.route_scatter_cells(dev.index, sp, pts_u8.data_ptr(), n, first_index, batch_size, max_cell_size,
+                                            origin, dims, tab[4 * vol:].data_ptr(), tab[:4 * vol].data_ptr(), world, ptrs,
+                                            [p + cap * 16 for p in ptrs], err.data_ptr())
+        hdl.barrier(channel=0)                     # every rank's stores have landed
+    # NOTE: views of the persistent symmetric buffer - the next routing call on ANY rank overwrites them
+    recv_pts = buf[:m * 16].view(m, 16)
+    recv_bat = buf[cap * 16:cap * 16 + m * 4].view(torch.int32)
+    return {"level": 0, "pts": recv_pts, "bat": recv_bat, "n": m, "cell_start": cs, "cell_idx": ci,
+            "ncell": int(len(my_cells)), "bbox": glo + ghi, "count_points": m, "err": err, "launches": launches,
+            "cells": int((H.sum(0) > 0).sum()), "box": (origin, dims),
+            "sent_bytes": 20 * (n - int(H[rank][owners == rank].sum())),
+            "exchange": "p2p stores fused with the level-0 split (pcb_route_scatter_cells over symmetric memory)",
+            "keep": (tab,)}
+
+
+def add_arrivals_to(cv, arr):
+    """Hands a routing / re-balance result (dict) to a Converter (pcb_add_arrivals)."""
+    cv.add_arrivals(arr["level"], arr["pts"].data_ptr() if arr["n"] else 0, arr["bat"].data_ptr() if arr["n"] else 0,
+                    arr["n"], arr["cell_start"].data_ptr() if arr["n"] else 0, arr["cell_idx"].data_ptr() if arr["n"] else 0,
+                    arr["ncell"], arr.get("bbox"), arr.get("count_points", 0))
+
+
+def route_cells_emulated(pcb, slices: List[torch.Tensor], batch_size: int, max_cell_size: float):
+    """route_cells for G ranks emulated in ONE process on one GPU (tests): the same kernels and the same plan; the
+    "peer" receive buffers are local tensors.  Returns one arrivals dict per owner rank."""
+    import numpy as np
+    world = len(slices)
+    dev = slices[0].device
+    sp = torch.cuda.current_stream(dev).cuda_stream
+    los, his = [], []
+    for s in slices:
+        if s.shape[0]:
+            lo, hi, _ = pcb.route_bbox(dev.index, sp, s.data_ptr(), s.shape[0], max_cell_size)
+            los.append(lo)
+            his.append(hi)
+    glo, ghi = np.min(np.array(los, dtype=np.float32), axis=0).tolist(), np.max(np.array(his, dtype=np.float32), axis=0).tolist()
+    origin, dims = _level0_box(glo, ghi, max_cell_size)
+    vol = dims[0] * dims[1] * dims[2]
+    assert vol <= 512
+    H = np.zeros((world, vol), dtype=np.int64)
+    for r, s in enumerate(slices):
+        hist = torch.zeros(vol, dtype=torch.int32, device=dev)
+        pcb.route_histogram(dev.index, sp, s.data_ptr(), s.shape[0], max_cell_size, origin, dims, hist.data_ptr())
+        H[r] = hist.cpu().numpy()
+    owners = pcb.plan_owners(H.sum(0), world)
+    plans = [cell_plan(H, owners, r) for r in range(world)]
+    recv = plans[0][1]
+    bufs_p = [torch.zeros((max(int(recv[o]), 1), 16), dtype=torch.uint8, device=dev) for o in range(world)]
+    bufs_b = [torch.zeros((max(int(recv[o]), 1),), dtype=torch.int32, device=dev) for o in range(world)]
+    first = 0
+    for r, s in enumerate(slices):
+        tab = torch.from_numpy(np.concatenate([plans[r][0].view(np.uint8), owners.astype(np.uint8)])).to(dev)
+        err = torch.zeros(1, dtype=torch.int32, device=dev)
+        pcb.route_scatter_cells(dev.index, sp, s.data_ptr(), s.shape[0], first, batch_size, max_cell_size, origin, dims,
+                                tab[4 * vol:].data_ptr(), tab[:4 * vol].data_ptr(), world, [b.data_ptr() for b in bufs_p],
+                                [b.data_ptr() for b in bufs_b], err.data_ptr())
+        torch.cuda.synchronize(dev)
+        assert int(err.item()) == 0
+        first += s.shape[0]
+    out = []
+    for o in range(world):
+        _, _, cells, start = plans[o]
+        m = int(recv[o])
+        out.append({"level": 0, "pts": bufs_p[o][:m], "bat": bufs_b[o][:m], "n": m,
+                    "cell_start": torch.from_numpy(start.view(np.int32).copy()).to(dev),
+                    "cell_idx": torch.from_numpy(_cell_indices(cells, origin, dims).reshape(-1).copy()).to(dev),
+                    "ncell": int(len(cells)), "bbox": glo + ghi, "count_points": m})
+    return out
+
+
+# ---- level-l re-balance (SURVEY 8e "Levels above l"): cells above the cut are built whole on the owner of their level-0
+# cell; the arrivals of level l (the pending arrivals of a partial build, pcb_set_stop_level) are then redistributed
+# cell by cell - a cell's state depends only on the deliveries of its single parent (converter.rs:124-134), and those
+# deliveries travel with their batch ordinals, so every cell is still processed on exactly one GPU with the reference's
+# arrival order.
+def pending_to_arrivals(cv, dev):
+    """The pending arrivals of a partial build as an arrivals dict (views of the handle's device memory: keep the
+    Converter open while they are in use)."""
+    import ctypes as C
+    p = cv.pending()
+    n, ncell = int(p.n), int(p.ncell)
+
+    def view(ptr, nbytes, dtype):
+        if not nbytes:
+            return torch.zeros(0, dtype=dtype, device=dev)
+        return _from_ptr(ptr, nbytes, dev).view(dtype)
+    return {"level": int(p.level), "n": n, "ncell": ncell,
+            "pts": view(p.d_pts, 16 * n, torch.uint8).view(n, 16) if n else torch.zeros((0, 16), dtype=torch.uint8, device=dev),
+            "bat": view(p.d_batch_plus1, 4 * n, torch.int32), "cell_start": view(p.d_cell_start, 4 * (ncell + 1) if n else 0, torch.int32),
+            "cell_idx": view(p.d_cell_idx, 12 * ncell, torch.int32), "count_points": 0}
+
+
+def _from_ptr(ptr, nbytes, dev):
+    """uint8 tensor over existing device memory (no copy) through the CUDA array interface"""
+    class _Holder:
+        pass
+    h = _Holder()
+    h.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+    return torch.as_tensor(h, device=dev)
+
+
+def _split_for_owners(arr, owners, world):
+    """arr: arrivals dict of this rank; owners: new owner per local cell (numpy).  Returns per destination the arrival
+    gather index (device int64) and the cell counts (numpy int64), cells in local order."""
+    import numpy as np
+    dev = arr["pts"].device
+    cs = arr["cell_start"].cpu().numpy().astype(np.int64) if arr["n"] else np.zeros(1, dtype=np.int64)
+    lens = np.diff(cs)
+    out = []
+    for o in range(world):
+        sel = np.nonzero(owners == o)[0]
+        cnt = lens[sel]
+        if cnt.sum() == 0:
+            out.append((torch.zeros(0, dtype=torch.int64, device=dev), cnt, sel))
+            continue
+        starts = torch.from_numpy(cs[sel]).to(dev)
+        ln = torch.from_numpy(cnt).to(dev)
+        off = torch.cumsum(ln, 0) - ln
+        idx = torch.arange(int(cnt.sum()), device=dev) + torch.repeat_interleave(starts - off, ln)
+        out.append((idx, cnt, sel))
+    return out
+
+
+def rebalance_emulated(pcb, arrs):
+    """Level-l re-balance for G ranks emulated in one process: arrs[r] = pending arrivals of rank r at the same level.
+    Returns the new arrivals dict per rank (cells ordered by (source rank, local order))."""
+    import numpy as np
+    world = len(arrs)
+    dev = arrs[0]["pts"].device
+    level = max(a["level"] for a in arrs)
+    counts = [np.diff(a["cell_start"].cpu().numpy().astype(np.int64)) if a["n"] else np.zeros(0, dtype=np.int64) for a in arrs]
+    owners = pcb.plan_owners(np.concatenate(counts) if counts else np.zeros(0), world)
+    offs = np.cumsum([0] + [len(c) for c in counts])
+    splits = [_split_for_owners(arrs[r], owners[offs[r]:offs[r + 1]], world) for r in range(world)]
+    out = []
+    for o in range(world):
+        pts = [arrs[r]["pts"][splits[r][o][0]] for r in range(world)]
+        bat = [arrs[r]["bat"][splits[r][o][0]] for r in range(world)]
+        cnt = np.concatenate([splits[r][o][1] for r in range(world)])
+        idx = [arrs[r]["cell_idx"].view(-1, 3)[torch.from_numpy(splits[r][o][2]).to(dev)] for r in range(world)]
+        keep = cnt > 0
+        cs = np.concatenate([[0], np.cumsum(cnt[keep])]).astype(np.int32)
+        ci = torch.cat(idx)[torch.from_numpy(np.nonzero(keep)[0]).to(dev)].contiguous()
+        out.append({"level": level, "pts": torch.cat(pts).contiguous(), "bat": torch.cat(bat).contiguous(), "n": int(cnt.sum()),
+                    "cell_start": torch.from_numpy(cs).to(dev), "cell_idx": ci.view(-1), "ncell": int(keep.sum()),
+                    "count_points": 0})
+    return out
+
+
+def rebalance(pcb, arr, group=None):
+    """Level-l re-balance across the ranks of `group` (collective): all-gather of the (cell count) tables -> the same
+    greedy plan on every rank (pcb_plan_owners) -> ONE all-to-all-v of the point records and one of their batch ordinals.
+    Returns this rank's new arrivals dict."""
+    import numpy as np
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    dev = arr["pts"].device
+    mine = np.diff(arr["cell_start"].cpu().numpy().astype(np.int64)) if arr["n"] else np.zeros(0, dtype=np.int64)
+    ncs = torch.zeros(world, dtype=torch.int64, device=dev)
+    nc = torch.tensor([len(mine)], dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(ncs, nc, group=group)
+    ncs = ncs.cpu().numpy()
+    cap = max(int(ncs.max()), 1)
+    pad = torch.zeros(cap, dtype=torch.int64, device=dev)
+    pad[:len(mine)] = torch.from_numpy(mine).to(dev)
+    allc = torch.zeros(world * cap, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(allc, pad, group=group)
+    allc = allc.view(world, cap).cpu().numpy()
+    counts = [allc[r, :ncs[r]] for r in range(world)]
+    owners = pcb.plan_owners(np.concatenate(counts), world)
+    offs = np.cumsum([0] + [len(c) for c in counts])
+    lv = torch.tensor([arr["level"] if arr["n"] else 0], dtype=torch.int64, device=dev)   # ranks without arrivals do not know it
+    dist.all_reduce(lv, op=dist.ReduceOp.MAX, group=group)
+    arr = dict(arr, level=int(lv.item()))
+    split = _split_for_owners(arr, owners[offs[rank]:offs[rank + 1]], world)
+    gather = torch.cat([s[0] for s in split])
+    send_pts = arr["pts"][gather].contiguous() if arr["n"] else arr["pts"]
+    send_bat = arr["bat"][gather].contiguous() if arr["n"] else arr["bat"]
+    ins = [int(s[1].sum()) for s in split]
+    # what every source sends to me: from the global table (no second count exchange)
+    outs, cnt_in, idx_send = [], [], []
+    for r in range(world):
+        sel = np.nonzero(owners[offs[r]:offs[r + 1]] == rank)[0]
+        cnt_in.append(counts[r][sel])
+        outs.append(int(counts[r][sel].sum()))
+    m = int(sum(outs))
+    recv_pts = torch.empty((m, 16), dtype=torch.uint8, device=dev)
+    recv_bat = torch.empty((m,), dtype=torch.int32, device=dev)
+    dist.all_to_all_single(recv_pts, send_pts, outs, ins, group=group)
+    dist.all_to_all_single(recv_bat, send_bat, outs, ins, group=group)
+    # cell indices of the cells I receive: the senders' index triples, exchanged the same way
+    ci = arr["cell_idx"].view(-1, 3)
+    send_idx = torch.cat([ci[torch.from_numpy(s[2]).to(dev)] for s in split]).contiguous() if len(mine) else ci
+    ins_c = [len(s[2]) for s in split]
+    outs_c = [len(c) for c in cnt_in]
+    recv_idx = torch.empty((int(sum(outs_c)), 3), dtype=torch.int32, device=dev)
+    dist.all_to_all_single(recv_idx, send_idx, outs_c, ins_c, group=group)
+    cnt = np.concatenate(cnt_in) if cnt_in else np.zeros(0, dtype=np.int64)
+    keep = cnt > 0
+    cs = np.concatenate([[0], np.cumsum(cnt[keep])]).astype(np.int32)
+    return {"level": arr["level"], "pts": recv_pts, "bat": recv_bat, "n": m, "cell_start": torch.from_numpy(cs).to(dev),
+            "cell_idx": recv_idx[torch.from_numpy(np.nonzero(keep)[0]).to(dev)].contiguous().view(-1), "ncell": int(keep.sum()),
+            "count_points": 0, "moved_bytes": 20 * (sum(ins) - ins[rank])}

@@ -1,0 +1,4 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_shard.py -m gpu -x -q > gpurun_out/pytest_shard.log 2>&1; echo "shard rc=$?" >> gpurun_out/pytest_shard.log
+tail -30 gpurun_out/pytest_shard.log

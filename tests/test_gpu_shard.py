@@ -104,3 +104,114 @@ def test_route_device_kernels_match_reference_routing():
     assert counts == np.bincount(dest, minlength=world).tolist()
     assert np.array_equal(send_pts.cpu().numpy(), pts.view(np.uint8).reshape(-1, 16)[order])
     assert np.array_equal(send_bat.cpu().numpy(), ((first + order) // bs).astype(np.int32))
+
+
+def _finish_arrivals(pcb, shard, arr, cfg, bs, stop=None):
+    """One owner's build from an arrivals dict; returns (Converter kept open, nodes, stats)."""
+    cv = pcb.Converter(None, device=0, batch_size=bs, config=cfg)
+    shard.add_arrivals_to(cv, arr)
+    if stop is not None:
+        cv.set_stop_level(stop)
+    st = cv.finish()
+    return cv, cv.nodes(), st
+
+
+@pytest.mark.parametrize("world", [2, 3, 5])
+def test_fused_cell_exchange_equals_oracle(world):
+    """pcb_route_scatter_cells (exchange + level-0 split in ONE kernel) + pcb_add_arrivals: every emulated owner receives
+    its level-0 arrivals in (cell, stream order) with global batch ordinals and builds from them directly - the union of
+    the owners' trees is the oracle's tree.  Many level-0 cells incl. negative indices, ragged slices."""
+    pcb, shard = load_pcb(), _shard()
+    rng = np.random.default_rng(200 + world)
+    pts = make_points(rng.random((150_001, 3)) * [160, 110, 30] - [85, 40, 10])
+    cfg, bs = (300, 12, 16.0), 1000     # 11 x 8 x 3 level-0 cells
+    o = oracle_convert([pts], config=cfg, batch_size=bs)
+    raw = torch.from_numpy(pts.view(np.uint8).reshape(-1, 16)).cuda()
+    n = raw.shape[0]
+    cuts = [0] + sorted(rng.integers(0, n, world - 1).tolist()) + [n]
+    arrs = shard.route_cells_emulated(pcb, [raw[cuts[r]:cuts[r + 1]] for r in range(world)], bs, cfg[2])
+    assert sum(a["n"] for a in arrs) == n
+    assert max(a["n"] for a in arrs) <= 1.25 * n / world      # greedy plan over ~260 cells
+    nodes, total, hmax = {}, 0, 0
+    for a in arrs:
+        cv, mine, st = _finish_arrivals(pcb, shard, a, cfg, bs)
+        assert not (set(mine) & set(nodes)), "two ranks produced the same node"
+        nodes.update(mine)
+        total += a["n"]
+        hmax = max(hmax, st.hierarchies)
+        assert list(st.bbox_min) + list(st.bbox_max) == [np.float32(v) for v in a["bbox"]]
+        cv.close()
+    compare_trees(o.nodes, nodes, "oracle", f"fused exchange, {world} ranks")
+    assert total == o.number_of_points and hmax == o.hierarchies
+    assert np.array_equal(np.array(arrs[0]["bbox"], dtype=np.float32), o.bbox)
+
+
+@pytest.mark.parametrize("stop", [1, 2, 4])
+def test_partial_build_and_resume_equals_oracle(stop):
+    """pcb_set_stop_level + pcb_pending_arrivals + pcb_add_arrivals(level l): building the levels < l on one handle and the
+    levels >= l on another from the pending arrivals gives the oracle's tree (the split point of the level-l re-balance)."""
+    pcb, shard = load_pcb(), _shard()
+    rng = np.random.default_rng(300 + stop)
+    pts = make_points(rng.random((120_000, 3)) * [70, 50, 20] - [30, 20, 5])
+    cfg, bs = (200, 10, 32.0), 1000
+    o = oracle_convert([pts], config=cfg, batch_size=bs)
+    dev = torch.device("cuda", 0)
+    with pcb.Converter(None, device=0, batch_size=bs, config=cfg) as top:
+        top.begin_file()
+        top.add_points(pts)
+        top.set_stop_level(stop)
+        st_top = top.finish()
+        nodes = dict(top.nodes())
+        assert all(int(k.split("/")[0][2:]) < stop for k in nodes)
+        pend = shard.pending_to_arrivals(top, dev)
+        assert pend["level"] == stop and pend["n"] > 0
+        cv, low, st_low = _finish_arrivals(pcb, shard, pend, cfg, bs)
+        assert all(int(k.split("/")[0][2:]) >= stop for k in low)
+        nodes.update(low)
+        cv.close()
+    compare_trees(o.nodes, nodes, "oracle", f"partial build, cut at level {stop}")
+    assert st_top.number_of_points == o.number_of_points and max(st_top.hierarchies, st_low.hierarchies) == o.hierarchies
+
+
+@pytest.mark.parametrize("world,stop", [(2, 1), (4, 2), (3, 3)])
+def test_level_l_rebalance_equals_oracle(world, stop):
+    """SURVEY 8e "Levels above l" on emulated ranks: ONE dominant level-0 cell (a C1-shaped cloud: the level-0 cut gives all
+    the work to one rank).  Owners build the levels < l, the level-l arrivals are re-balanced cell by cell across the
+    ranks (same plan as the distributed path), every rank finishes its share: the union is the oracle's tree and the
+    level-l arrivals are spread evenly."""
+    pcb, shard = load_pcb(), _shard()
+    rng = np.random.default_rng(400 + world)
+    dense = rng.random((140_000, 3)) * [15.0, 15.0, 6.0]                       # inside level-0 cell (0, 0, 0)
+    sparse = rng.random((10_000, 3)) * [60, 60, 10] - [30, 30, 2]
+    xyz = np.concatenate([dense, sparse])[rng.permutation(150_000)]
+    pts = make_points(xyz)
+    cfg, bs = (150, 10, 16.0), 1000
+    o = oracle_convert([pts], config=cfg, batch_size=bs)
+    raw = torch.from_numpy(pts.view(np.uint8).reshape(-1, 16)).cuda()
+    n = raw.shape[0]
+    dev = torch.device("cuda", 0)
+    cuts = [r * n // world for r in range(world + 1)]
+    arrs = shard.route_cells_emulated(pcb, [raw[cuts[r]:cuts[r + 1]] for r in range(world)], bs, cfg[2])
+    assert max(a["n"] for a in arrs) > 0.85 * n                               # the level-0 cut cannot balance this cloud
+    nodes, tops, pend, hmax = {}, [], [], 0
+    for a in arrs:
+        cv, mine, st = _finish_arrivals(pcb, shard, a, cfg, bs, stop=stop)
+        nodes.update(mine)
+        hmax = max(hmax, st.hierarchies)
+        tops.append(cv)                                                        # pending arrivals live in the handle
+        pend.append(shard.pending_to_arrivals(cv, dev))
+    new = shard.rebalance_emulated(pcb, pend)
+    tot = sum(a["n"] for a in new)
+    assert tot == sum(p["n"] for p in pend) > 0
+    if 8 ** stop >= 4 * world:                                                 # enough level-l cells to balance
+        assert max(a["n"] for a in new) <= 1.35 * tot / world
+    for a in new:
+        cv, mine, st = _finish_arrivals(pcb, shard, a, cfg, bs)
+        assert not (set(mine) & set(nodes)), "two ranks produced the same node"
+        nodes.update(mine)
+        hmax = max(hmax, st.hierarchies)
+        cv.close()
+    for cv in tops:
+        cv.close()
+    compare_trees(o.nodes, nodes, "oracle", f"level-{stop} re-balance, {world} ranks")
+    assert hmax == o.hierarchies
