@@ -256,6 +256,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-files", action="store_true", help="skip the e2e_files legs (tmpfs node files, cold CLI process)")
     ap.add_argument("--no-check", action="store_true", help="skip the verified step at N > 1")
+    ap.add_argument("--rebalance", default="auto", help="N > 1: level-l re-balance: auto (default) | off | <level>")
     ap.add_argument("--check", action="store_true", help="run the verified step at N = 1 as well")
     ap.add_argument("--no-profile", action="store_true", help="debug: no per-kernel CUDA events in the timed steps")
     ap.add_argument("--no-clocks", action="store_true", help="debug: do not run the clock sampler")
@@ -327,9 +328,31 @@ def main():
         return rp, rb   # keep alive until finish
 
     host_log = []
+    shard_info = [{}]
+
+    def sharded(flags, src, keep_open=False):
+        """N GPUs: one collective conversion step of this rank through shard.ShardedBuild (fused level-0 exchange, level-l
+        re-balance by the automatic rule unless --rebalance says otherwise, build).  Returns (stats, kernel stats[, sb])."""
+        rb = args.rebalance if args.rebalance in ("auto", "off") else int(args.rebalance)
+        sb = shard.ShardedBuild(pcb, local_rank, group=None, stream=stream, flags=flags, rebalance=rb)
+        try:
+            st, ks = sb.run(src, rank * n)
+            exchange[0] = sb.info.get("exchange", "")
+            shard_info[0] = dict(sb.info)
+            if keep_open:
+                return st, ks, sb
+            return st, ks
+        finally:
+            if not keep_open:
+                sb.close()
 
     def step(profile=not args.no_profile):
         flags = pcb.FLAG_DEVICE_ONLY | (pcb.FLAG_PROFILE if profile else 0)
+        if world > 1:
+            t0 = time.perf_counter()
+            out = sharded(flags, pts)
+            host_log.append((0.0, round((time.perf_counter() - t0) * 1e3, 2), 0.0))
+            return out
         t0 = time.perf_counter()
         cv = pcb.Converter(merge_dir, device=local_rank, flags=flags)
         try:
@@ -419,18 +442,15 @@ def main():
                     cv.add_points(hnp)
                     st = cv.finish()
                     ph = {"h2d": st.h2d_seconds * 1e3, "build": st.build_seconds * 1e3, "d2h_tail": st.d2h_seconds * 1e3}
-                else:   # host slice -> device, exchange, build
-                    cv.set_stream(stream.cuda_stream)
-                    ea, eb, ec = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+                else:   # host slice -> device, exchange (+ re-balance), build
+                    ea, eb = (torch.cuda.Event(enable_timing=True) for _ in range(2))
                     ea.record(stream)
                     stage.copy_(host, non_blocking=True)
                     eb.record(stream)
-                    keep = ingest(cv, stage)
-                    ec.record(stream)
-                    t1 = time.perf_counter()
-                    st = cv.finish()
+                    st, _ = sharded(pcb.FLAG_NO_FILES, stage)
                     torch.cuda.synchronize()
-                    ph = {"h2d": ea.elapsed_time(eb), "route": eb.elapsed_time(ec), "route_host_wall": (t1 - t0) * 1e3,
+                    t1 = time.perf_counter()
+                    ph = {"h2d": ea.elapsed_time(eb), "route_and_build_wall": (t1 - t0) * 1e3 - ea.elapsed_time(eb),
                           "build": st.build_seconds * 1e3, "d2h_tail": st.d2h_seconds * 1e3}
                 return st, ph
             finally:
@@ -462,11 +482,14 @@ def main():
     if (world > 1 and not args.no_check) or args.check:
         s64 = lambda v: v - (1 << 64) if v >= (1 << 63) else v   # noqa: E731 - u64 digests travel as int64
         mine, src, err = (0, 0, 0), (0, 0, 0), ""
-        cv = pcb.Converter(None, device=local_rank, flags=pcb.FLAG_NO_FILES)
-        try:
+        if world > 1:
+            st, _, cv = sharded(pcb.FLAG_NO_FILES, pts, keep_open=True)   # collective: outside the try block below
+        else:
+            cv = pcb.Converter(None, device=local_rank, flags=pcb.FLAG_NO_FILES)
             cv.set_stream(stream.cuda_stream)
-            keep = ingest(cv, pts)       # collective at N > 1: outside the try block below
+            keep = ingest(cv, pts)
             st = cv.finish()
+        try:
             try:
                 nodes = cv.nodes()
                 mine = check_tree_cells(nodes)   # raises if a stored point lies outside its node's cell, bad headers ...
@@ -592,6 +615,8 @@ def main():
                           "levels": int(last.levels_built), "arrivals_per_point": round(last.arrivals / n, 3),
                           "nodes": int(last.nodes_written), "sharding": ("none (1 GPU)" if world == 1 else
                                        "level-0 cell owners; exchange inside the timed step = " + exchange[0]), "step_ms": step_ms,
+                          **({"rebalance": {"mode": args.rebalance, **{k: v for k, v in shard_info[0].items() if k != "exchange"}}}
+                             if world > 1 else {}),
                           **({"ranks": ranks_info} if ranks_info else {})},
                "e2e": e2e, "gpu_launches": int(launches) + route_timed, "roofline": roofline, "cpu_baseline": cpu,
                "clocks": clocks}

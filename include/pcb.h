@@ -240,6 +240,28 @@ int pcb_plan_owners(const uint64_t* counts, uint64_t ncells, uint32_t world, uin
 int pcb_route_bbox_static(int device, void* stream, const pcb_point* d_pts, uint64_t n, float max_cell_size,
                           float* d_out6, uint32_t* d_err);
 
+/* ---- render-time cull / level-of-detail pass: the compute shader the renderer dispatches per
+   loaded cell, src/plugins/render/point/pipelines/compute.wgsl:81-205, as a CUDA kernel.  For every point of one cell:
+   view / projection transform, frustum test, depth-texture test, pick of the deepest LOADED hierarchy that contains
+   the point (binary search over the loaded cells, optionally overridden by distance to the camera), colour alpha :=
+   that hierarchy, append to d_out through the atomic counter *d_count (the indirect draw buffer's instance_count:
+   the caller zeroes it, or lets several cells accumulate).  Output order is the atomic's, as in the shader.
+   Matrices are column-major (glam / wgpu): m[4 * col + row].  d_hierarchies: number_of_hierarchies x (cell_size,
+   spacing) floats; d_loaded_cells: n_loaded x (hierarchy, x, y, z) i32, sorted ascending, 16-byte aligned;
+   d_far_distances: >= max_hierarchy + 1 floats (only read when size_by_distance); d_depth: depth_height rows of
+   depth_width floats.  Returns kernels launched or a negative pcb_status. */
+typedef struct pcb_cull_params {
+    float view[16], projection[16];
+    float cam_pos[3];
+    uint32_t depth_width, depth_height;
+    uint32_t number_of_hierarchies;
+    uint32_t size_by_distance, max_hierarchy;   /* FrustumsSettings, compute.wgsl:36-39 */
+    uint32_t cell_hierarchy;                    /* hierarchy of the cell whose points d_in holds (compute.wgsl:67-75) */
+} pcb_cull_params;
+int pcb_cull_lod(int device, void* stream, const pcb_cull_params* params, const float* d_hierarchies,
+                 const int32_t* d_loaded_cells, uint32_t n_loaded, const float* d_far_distances, const float* d_depth,
+                 const pcb_point* d_in, uint64_t n, pcb_point* d_out, uint32_t* d_count);
+
 const char* pcb_version(void);
 int pcb_device_count(void);
 

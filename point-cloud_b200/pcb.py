@@ -31,7 +31,7 @@ EXPORTS = [
     "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
     "pcb_route_bbox", "pcb_route_bbox_static", "pcb_route_histogram", "pcb_route_pack", "pcb_route_scatter",
     "pcb_add_las_records", "pcb_alloc_host", "pcb_free_host", "pcb_add_arrivals", "pcb_set_stop_level", "pcb_pending_arrivals",
-    "pcb_route_scatter_cells", "pcb_plan_owners",
+    "pcb_route_scatter_cells", "pcb_plan_owners", "pcb_cull_lod",
     "pcb_add_points_device_batched", "pcb_write_metadata", "pcb_get_config", "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
 
@@ -63,6 +63,12 @@ class PcbArrivals(C.Structure):
     _fields_ = [("level", C.c_uint32), ("reserved", C.c_uint32), ("n", C.c_uint64), ("ncell", C.c_uint64),
                 ("d_pts", C.c_void_p), ("d_batch_plus1", C.c_void_p), ("d_cell_start", C.c_void_p),
                 ("d_cell_idx", C.c_void_p)]
+
+
+class PcbCullParams(C.Structure):
+    _fields_ = [("view", C.c_float * 16), ("projection", C.c_float * 16), ("cam_pos", C.c_float * 3),
+                ("depth_width", C.c_uint32), ("depth_height", C.c_uint32), ("number_of_hierarchies", C.c_uint32),
+                ("size_by_distance", C.c_uint32), ("max_hierarchy", C.c_uint32), ("cell_hierarchy", C.c_uint32)]
 
 
 class PcbError(RuntimeError):
@@ -110,6 +116,7 @@ def load_library():
                                           C.POINTER(C.c_uint32), vp, vp, C.c_uint32, C.POINTER(C.c_uint64),
                                           C.POINTER(C.c_uint64), vp]
     L.pcb_plan_owners.argtypes = [vp, C.c_uint64, C.c_uint32, vp]
+    L.pcb_cull_lod.argtypes = [C.c_int, vp, C.POINTER(PcbCullParams), vp, vp, C.c_uint32, vp, vp, vp, C.c_uint64, vp, vp]
     L.pcb_add_las_records.argtypes = [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.pcb_alloc_host.argtypes = [C.c_uint64]
     L.pcb_alloc_host.restype = vp
@@ -339,6 +346,27 @@ def plan_owners(counts, world: int) -> np.ndarray:
     if rc != 0:
         raise PcbError(rc, "pcb_plan_owners failed")
     return out
+
+
+def cull_params(view, projection, cam_pos, depth_wh, number_of_hierarchies, cell_hierarchy, size_by_distance=False,
+                max_hierarchy=0) -> PcbCullParams:
+    """view / projection: 4 x 4 numpy matrices in the usual math layout (M @ v); stored column-major as glam does."""
+    p = PcbCullParams()
+    p.view = (C.c_float * 16)(*np.asarray(view, dtype=np.float32).T.reshape(-1).tolist())
+    p.projection = (C.c_float * 16)(*np.asarray(projection, dtype=np.float32).T.reshape(-1).tolist())
+    p.cam_pos = (C.c_float * 3)(*[float(v) for v in cam_pos])
+    p.depth_width, p.depth_height = int(depth_wh[0]), int(depth_wh[1])
+    p.number_of_hierarchies, p.cell_hierarchy = int(number_of_hierarchies), int(cell_hierarchy)
+    p.size_by_distance, p.max_hierarchy = int(bool(size_by_distance)), int(max_hierarchy)
+    return p
+
+
+def cull_lod(device, stream, params, hier_ptr, cells_ptr, n_loaded, far_ptr, depth_ptr, in_ptr, n, out_ptr, count_ptr):
+    """pcb_cull_lod: the renderer's per-cell cull / LOD compute pass (compute.wgsl:81-205) on device buffers."""
+    return _route_check(load_library().pcb_cull_lod(device, C.c_void_p(stream), C.byref(params), C.c_void_p(hier_ptr),
+                                                    C.c_void_p(cells_ptr), n_loaded, C.c_void_p(far_ptr) if far_ptr else None,
+                                                    C.c_void_p(depth_ptr), C.c_void_p(in_ptr), n, C.c_void_p(out_ptr),
+                                                    C.c_void_p(count_ptr)))
 
 
 def write_metadata(out_dir, number_of_points, hierarchies, bbox_min, bbox_max, config):

@@ -432,6 +432,7 @@ def route_cells(pcb, pts_u8: torch.Tensor, first_index: int, batch_size: int, ma
     recv_bat = buf[cap * 16:cap * 16 + m * 4].view(torch.int32)
     return {"level": 0, "pts": recv_pts, "bat": recv_bat, "n": m, "cell_start": cs, "cell_idx": ci,
             "ncell": int(len(my_cells)), "bbox": glo + ghi, "count_points": m, "err": err, "launches": launches,
+            "plan_recv": recv.tolist(), "plan_max_cell": int(H.sum(0).max()),
             "cells": int((H.sum(0) > 0).sum()), "box": (origin, dims),
             "sent_bytes": 20 * (n - int(H[rank][owners == rank].sum())),
             "exchange": "p2p stores fused with the level-0 split (pcb_route_scatter_cells over symmetric memory)",
@@ -626,3 +627,124 @@ def rebalance(pcb, arr, group=None):
     return {"level": arr["level"], "pts": recv_pts, "bat": recv_bat, "n": m, "cell_start": torch.from_numpy(cs).to(dev),
             "cell_idx": recv_idx[torch.from_numpy(np.nonzero(keep)[0]).to(dev)].contiguous().view(-1), "ncell": int(keep.sum()),
             "count_points": 0, "moved_bytes": 20 * (sum(ins) - ins[rank])}
+
+
+class ShardedBuild:
+    """One multi-GPU conversion step of this rank: level-0 exchange (fused with the level-0 split when it applies, else
+    route_device), optional level-l re-balance, build.  Collective: every rank of `group` calls run() together.
+
+    rebalance: "off" | "auto" | int l.  auto: while the arrivals per rank differ by more than 10 % from the
+    mean AND the largest cell of the current level still holds more than 1 / (4 G) of the level's arrivals, the owners
+    build one more level; then the arrivals of that level are redistributed cell by cell and every rank finishes its
+    share.  Balanced clouds (C2, C5) never leave level 0 and pay nothing."""
+
+    def __init__(self, pcb, device_index, batch_size=10_000, max_cell_size=1000.0, group=None, stream=None, flags=0,
+                 out_dir=None, rebalance="auto", max_level=8, profile=False):
+        self.pcb, self.dev_index, self.bs, self.S0 = pcb, device_index, batch_size, max_cell_size
+        self.group, self.stream, self.flags, self.out_dir = group, stream, flags, out_dir
+        self.rebalance, self.max_level = rebalance, max_level
+        self.handles = []
+        self.info = {}
+
+    def _open(self):
+        cv = self.pcb.Converter(self.out_dir, device=self.dev_index, batch_size=self.bs, flags=self.flags)
+        if self.stream is not None:
+            cv.set_stream(self.stream.cuda_stream)
+        self.handles.append(cv)
+        return cv
+
+    def close(self):
+        for cv in self.handles:
+            cv.close()
+        self.handles = []
+
+    def nodes(self):
+        out = {}
+        for cv in self.handles:
+            out.update(cv.nodes())
+        return out
+
+    def _level_stats(self, arr, dev):
+        """(max arrivals per rank, mean, largest cell, total) of the current level over all ranks"""
+        import numpy as np
+        world = dist.get_world_size(self.group)
+        if "plan_recv" in arr:   # level 0 after the fused exchange: the plan already knows, no collective
+            r = np.array(arr["plan_recv"], dtype=np.float64)
+            return r.max(), r.mean(), arr["plan_max_cell"], r.sum()
+        big = int(torch.diff(arr["cell_start"]).max().item()) if arr["n"] else 0
+        v = torch.tensor([arr["n"], big], dtype=torch.int64, device=dev)
+        mx = v.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=self.group)
+        sm = v[:1].clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM, group=self.group)
+        return float(mx[0].item()), float(sm[0].item()) / world, int(mx[1].item()), float(sm[0].item())
+
+    def run(self, src: torch.Tensor, first_index: int):
+        """src: this rank's slice of the undivided stream ((n, 16) uint8 on the device).  Returns a namespace with the
+        summed statistics of this rank's handles."""
+        from types import SimpleNamespace
+        pcb = self.pcb
+        dev = src.device
+        world = dist.get_world_size(self.group)
+        launches = 0
+        arr = route_cells(pcb, src, first_index, self.bs, self.S0, group=self.group, stream=self.stream)
+        stats = []
+        if arr is None:   # general path: stream-ordered points + batch ordinals, the owner splits by level-0 cell itself
+            rp, rb, info = route_device(pcb, src, first_index, self.bs, self.S0, group=self.group, stream=self.stream)
+            launches += info["launches"]
+            self.info = {"exchange": info.get("exchange", ""), "rebalance_level": 0}
+            cv = self._open()
+            cv.add_points_device_batched(rp.data_ptr(), rb.data_ptr(), rp.shape[0])
+            self._keep = (rp, rb)
+            stats.append(cv.finish())
+        else:
+            launches += arr["launches"]
+            self.info = {"exchange": arr["exchange"], "rebalance_level": 0}
+            self._keep = [arr]
+            level = 0
+            want = self.rebalance
+            while True:
+                go_deeper = False
+                if want == "auto":
+                    mx, mean, big, total = self._level_stats(arr, dev)
+                    unbalanced = total > 0 and mx > 1.10 * mean
+                    go_deeper = unbalanced and big > total / (4.0 * world) and level < self.max_level
+                    do_rebalance = unbalanced and not go_deeper and level > 0
+                elif want == "off":
+                    do_rebalance = False
+                else:
+                    go_deeper = level < int(want)
+                    do_rebalance = not go_deeper and level > 0
+                if not go_deeper:
+                    break
+                cv = self._open()                       # the owners build exactly one more level
+                add_arrivals_to(cv, arr)
+                cv.set_stop_level(level + 1)
+                stats.append(cv.finish())
+                arr = pending_to_arrivals(cv, dev)
+                arr["level"] = level + 1
+                level += 1
+            if do_rebalance:
+                arr = rebalance(pcb, arr, group=self.group)
+                self._keep.append(arr)
+                self.info["rebalance_level"] = level
+                self.info["rebalance_moved_bytes"] = arr.get("moved_bytes", 0)
+            cv = self._open()
+            add_arrivals_to(cv, arr)
+            stats.append(cv.finish())
+            self.info["build_arrivals_after_cut"] = int(stats[-1].arrivals)
+        ks = {}
+        for cv in self.handles:
+            for k in cv.kernel_stats():
+                d = ks.setdefault(k["name"], dict(name=k["name"], launches=0, units=0, bytes=0, ms=0.0))
+                for f in ("launches", "units", "bytes", "ms"):
+                    d[f] += k[f]
+        tot = SimpleNamespace(
+            points_added=sum(int(s.points_added) for s in stats), arrivals=sum(int(s.arrivals) for s in stats),
+            gpu_launches=sum(int(s.gpu_launches) for s in stats) + launches,
+            levels_built=sum(int(s.levels_built) for s in stats), nodes_written=sum(int(s.nodes_written) for s in stats),
+            node_bytes=sum(int(s.node_bytes) for s in stats), hierarchies=max(int(s.hierarchies) for s in stats),
+            number_of_points=sum(int(s.points_added) for s in stats),
+            build_seconds=sum(s.build_seconds for s in stats), d2h_seconds=sum(s.d2h_seconds for s in stats),
+            h2d_seconds=0.0, bbox_min=list(stats[0].bbox_min), bbox_max=list(stats[0].bbox_max))
+        return tot, list(ks.values())

@@ -284,6 +284,25 @@ def check_tree_cells(nodes: Dict[str, bytes], limit=5000, max_cell=1000.0):
     return total
 
 
+def oracle_cull(params, hier, loaded, far, depth, pts) -> np.ndarray:
+    """CPU restatement of compute.wgsl:81-205 (oracle/cull_oracle.cpp).  params: pcb.PcbCullParams (same layout);
+    hier (nh, 2) f32; loaded (m, 4) i32 sorted; far (k,) f32; depth (h, w) f32; pts: point records.  Returns the kept
+    records (input order)."""
+    L = oracle_lib()
+    L.orc_cull_lod.restype = C.c_uint64
+    L.orc_cull_lod.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                               C.c_uint64, C.c_void_p]
+    hier = np.ascontiguousarray(hier, dtype=np.float32)
+    loaded = np.ascontiguousarray(loaded, dtype=np.int32).reshape(-1, 4)
+    far = np.ascontiguousarray(far, dtype=np.float32)
+    depth = np.ascontiguousarray(depth, dtype=np.float32)
+    a = as_points(pts)
+    out = np.zeros(max(len(a), 1), dtype=POINT_DTYPE)
+    k = L.orc_cull_lod(C.addressof(params), hier.ctypes.data, loaded.ctypes.data, len(loaded), far.ctypes.data,
+                       depth.ctypes.data, a.ctypes.data, len(a), out.ctypes.data)
+    return out[:k]
+
+
 def load_pcb():
     """Import point-cloud_b200/pcb.py (the directory name is not a Python identifier)."""
     import importlib.util
