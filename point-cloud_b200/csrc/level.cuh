@@ -645,10 +645,29 @@ struct ContestOp {
     // meta bits of a single element: 0-3 child octant, 8 group head, 9 group tail, 10 last of its cell in sorted
     // order, 11 first arrival of its cell, 12 last arrival of its cell
     __device__ void load_items(u64 base, State (&v)[ITEMS]) const {
+        u64 hk;
+        uint2 hr;
+        u32 hp;
+        bool hv;
+        load_items_halo<false>(base, v, 0, hk, hr, hp, hv);
+    }
+    // HALO (k_contest_halo): lane l of the block's first warp also loads sorted element tbase - 1 - l (the 32 elements
+    // before the tile) with its contest record: hkey / hrec / hpos, hvalid = that element exists.
+    template <bool HALO>
+    __device__ __forceinline__ void load_items_halo(u64 base, State (&v)[ITEMS], u64 tbase, u64& hkey, uint2& hrec, u32& hpos,
+                                                    bool& hvalid) const {
         const int lane = threadIdx.x & 31;
         const u32 n = n_dev ? __ldg(n_dev) : this->n;
         u64 key[ITEMS];
         u32 pos[ITEMS];
+        hvalid = false;
+        hkey = ~0ull;
+        hrec = make_uint2(0u, 0u);
+        hpos = 0u;
+        if (HALO && threadIdx.x < 32) {
+            hvalid = tbase >= 1ull + (u64)lane && tbase - 1ull - lane < n;
+            if (hvalid) hkey = keys[tbase - 1ull - lane];
+        }
         if (base + ITEMS <= n) {
             const ulonglong2* src = (const ulonglong2*)(keys + base);
 #pragma unroll
@@ -673,6 +692,10 @@ struct ContestOp {
             const uint2 rec = (base + k < n) ? __ldg(d2oct + pos[k]) : make_uint2(0u, 0u);
             d2v[k] = rec.x;
             ocv[k] = rec.y;
+        }
+        if (HALO && hvalid) {
+            hpos = PAIRS ? vals[tbase - 1ull - lane] : (u32)(hkey & ((1ull << lay.pb) - 1ull));
+            hrec = __ldg(d2oct + hpos);
         }
         // neighbours across the thread boundary
         u64 prevk = __shfl_up_sync(0xFFFFFFFFu, key[ITEMS - 1], 1);
@@ -718,6 +741,22 @@ struct ContestOp {
         return r;
     }
     __device__ void consume(u32 j, const State& excl, const State& incl, const State& self) const {
+        winner(j, excl.ntail, incl, self);
+        emit(j, excl, self);
+    }
+    // the winner of the group that ends at sorted element j; wi = its ordinal among all winners
+    __device__ __forceinline__ void winner(u32 j, u32 wi, const State& incl, const State& self) const {
+        if (self.meta & 0x200u) {
+            win_src[wi] = (u32)incl.mn;
+            if (tails) {
+                const u64 G = gid(keys[j]);
+                tails[wi] = make_uint4((u32)G, (u32)(G >> 32), (u32)(incl.mn >> 32), (u32)incl.mn);
+            }
+        }
+        if (self.meta & 0x400u) win_end[(u32)(gid(keys[j]) >> g.hexbits)] = wi + 1;
+    }
+    // the emission triggered by sorted element j (cell.rs:80-92)
+    __device__ __forceinline__ void emit(u32 j, const State& excl, const State& self) const {
         const u32 pos = (u32)self.mn;
         u64 e;
         if (self.meta & 0x100u) {
@@ -727,14 +766,6 @@ struct ContestOp {
         } else {
             e = ((u64)(self.meta & 0xFu) << 32) | pos;
         }
-        if (self.meta & 0x200u) {
-            win_src[excl.ntail] = (u32)incl.mn;
-            if (tails) {
-                const u64 G = gid(keys[j]);
-                tails[excl.ntail] = make_uint4((u32)G, (u32)(G >> 32), (u32)(incl.mn >> 32), (u32)incl.mn);
-            }
-        }
-        if (self.meta & 0x400u) win_end[(u32)(gid(keys[j]) >> g.hexbits)] = excl.ntail + 1;
         if (self.meta & 0x800u) e |= PCB_EM_CELL_FIRST;
         if (self.meta & 0x1000u) e |= PCB_EM_CELL_LAST;
         if (estart) {
@@ -745,6 +776,151 @@ struct ContestOp {
     }
     __device__ void finish(const State& total) const { *nwin_out = total.ntail; }
 };
+
+// warp-wide decoupled look-back over plain 32-bit counts (flag bits inside the word, as the radix passes do):
+// publishes `count` for tile `tile`, returns the sum over the tiles before it (all lanes)
+__device__ __forceinline__ u32 chain_sum_lookback(u32* __restrict__ status, u32 tile, u32 count, u32* err) {
+    const int lane = threadIdx.x & 31;
+    volatile u32* st = status;
+    if (lane == 0) st[tile] = count | (tile == 0 ? RADIX_FLAG_INCL : RADIX_FLAG_AGG);
+    u32 prefix = 0;
+    int look = (int)tile - 1;
+    u32 spins = 0;
+    while (look >= 0) {
+        const int t = look - lane;
+        u32 w = RADIX_FLAG_INCL;
+        if (t >= 0) {
+            w = st[t];
+            while ((w & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u) {
+                w = st[t];
+                if (++spins > PCB_SPIN_LIMIT) {
+                    if (err) atomicOr(err, PCB_DERR_TIMEOUT);
+                    w = RADIX_FLAG_INCL;
+                }
+            }
+        }
+        const u32 m = __ballot_sync(0xFFFFFFFFu, (w & RADIX_FLAG_INCL) != 0u);
+        const int last = m ? (__ffs(m) - 1) : 31;
+        u32 v = lane <= last ? (w & RADIX_COUNT_MASK) : 0u;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+        prefix += v;
+        if (m) break;
+        look -= 32;
+    }
+    if (lane == 0 && tile > 0) st[tile] = ((prefix + count) & RADIX_COUNT_MASK) | RADIX_FLAG_INCL;
+    return prefix;
+}
+
+// The contest of a whole level WITHOUT the block waiting for earlier tiles before it emits.  The scan is segmented by
+// prism group, so the only running-minimum state a tile needs from its predecessors is that of the group that
+// straddles its first element - and that group's earlier members are (almost always) among the 32 sorted elements
+// right before the tile.  The block's first warp loads them as a HALO together with the tile (the same two dependent
+// loads: key, then contest record) and folds them into the tile's exclusive prefix; the tile then knows its inclusive
+// (minimum, octant) state at once and publishes it.  Only when the halo ends inside the group (a prism with more than
+// 32 arrivals before the tile start) does the tile fall back to the chained look-back over those descriptors
+// (scan.cuh), which every tile feeds.  The one thing that still travels between tiles is the NUMBER of groups
+// completed before the tile (the slot of its first winner in win_src): a 32-bit decoupled look-back that the first
+// warp runs WHILE the other warps already emit; winners are written after it.
+template <bool PAIRS, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+k_contest_halo(ContestOp<PAIRS> op, u32 n, u32 ntiles, uint4* __restrict__ desc, u32* __restrict__ wstatus) {
+    typedef ContestState State;
+    typedef ContestOp<PAIRS> Op;
+    constexpr int ITEMS = Op::ITEMS, WARPS = THREADS / 32;
+    if (op.n_dev) n = __ldg(op.n_dev);
+    __shared__ State s_warp[WARPS];
+    __shared__ State s_prefix;
+    __shared__ u32 s_need, s_wbase;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u32 tile = blockIdx.x;
+    const u64 tbase = (u64)tile * (THREADS * ITEMS), base = tbase + (u64)tid * ITEMS;
+
+    State v[ITEMS];
+    u64 hkey;
+    uint2 hrec;
+    u32 hpos;
+    bool hvalid;
+    op.template load_items_halo<true>(base, v, tbase, hkey, hrec, hpos, hvalid);
+    State acc = op.identity();
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) acc = op.combine(acc, v[k]);
+    State winc = acc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        State up = shfl_up_state(winc, d);
+        if (lane >= d) winc = op.combine(up, winc);
+    }
+    if (lane == 31) s_warp[warp] = winc;
+    if (warp == 0) {
+        // halo: the members of the group of sorted element tbase - 1 that lie in [tbase - 32, tbase)
+        const u64 G0 = op.gid(__shfl_sync(0xFFFFFFFFu, hkey, 0));
+        const u32 m = __ballot_sync(0xFFFFFFFFu, hvalid && op.gid(hkey) == G0);
+        const int run = (m == 0xFFFFFFFFu) ? 32 : (__ffs(~m) - 1);
+        u64 mn = (lane < run) ? (((u64)hrec.x << 32) | hpos) : ~0ull;
+        u32 oc = hrec.y & 0xFu;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) {
+            const u64 omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d);
+            const u32 ooc = __shfl_xor_sync(0xFFFFFFFFu, oc, d);
+            if (omn < mn) { mn = omn; oc = ooc; }
+        }
+        if (lane == 0) {
+            s_prefix = State{mn, oc, 0u};
+            // the group may begin before the halo (no matter when the tile starts with a group head)
+            s_need = (run == 32 && tbase > 32u && !(v[0].meta & 0x100u)) ? 1u : 0u;
+        }
+    }
+    __syncthreads();
+    State wpre = op.identity(), total = op.identity();
+    if (warp == 0) {
+#pragma unroll
+        for (int w = 0; w < WARPS; w++) total = op.combine(total, s_warp[w]);
+    } else {
+#pragma unroll
+        for (int w = 0; w < WARPS - 1; w++)
+            if (w < warp) wpre = op.combine(wpre, s_warp[w]);
+    }
+    State texcl = shfl_up_state(winc, 1);
+    if (lane == 0) texcl = op.identity();
+    texcl = op.combine(wpre, texcl);
+    if (s_need) {   // rare: chained look-back for the straddling group
+        if (warp == 0) {
+            State prefix = chain_lookback(op, desc, tile, total, op.err);
+            if (lane == 0) s_prefix = prefix;
+        }
+        __syncthreads();
+    } else if (tid == 0) {
+        chain_publish<Op>(desc, tile, op.combine(s_prefix, total), PCB_DESC_INCL);
+    }
+    if (warp == 0) {   // winners before this tile: overlapped with the emission of the other warps
+        const u32 wbase = chain_sum_lookback(wstatus, tile, total.ntail, op.err);
+        if (lane == 0) s_wbase = wbase;
+    }
+    const State start = op.combine(s_prefix, texcl);
+    State run = start;
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) {
+        const u64 i = base + k;
+        if (i < n) {
+            op.emit((u32)i, run, v[k]);
+            run = op.combine(run, v[k]);
+        }
+    }
+    __syncthreads();
+    u32 wi = s_wbase + texcl.ntail;
+    run = start;
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) {
+        const u64 i = base + k;
+        if (i < n) {
+            run = op.combine(run, v[k]);
+            op.winner((u32)i, wi, run, v[k]);
+            wi += v[k].ntail;
+        }
+    }
+    if (tile == ntiles - 1 && tid == THREADS - 1) *op.nwin_out = wi;
+}
 
 // ---- record filter ---------------------------------------------------------------------------------------------------
 // On the upper levels a prism receives hundreds of arrivals and all but a handful of them lose to an incumbent
