@@ -153,7 +153,7 @@ def test_partial_build_and_resume_equals_oracle(stop):
     pcb, shard = load_pcb(), _shard()
     rng = np.random.default_rng(300 + stop)
     pts = make_points(rng.random((120_000, 3)) * [70, 50, 20] - [30, 20, 5])
-    cfg, bs = (40, 10, 32.0), 1000
+    cfg, bs = (40, 4, 32.0), 1000
     o = oracle_convert([pts], config=cfg, batch_size=bs)
     assert o.hierarchies > 3, "the cloud must be deeper than the deepest cut"
     dev = torch.device("cuda", 0)
