@@ -1204,9 +1204,12 @@ __device__ __forceinline__ OctPacked oct_combine(const OctPacked& a, const OctPa
     r.head = a.head | b.head;
     return r;
 }
-template <int OCT_THREADS, int OCT_ITEMS>
+// MODE 0: single pass with a decoupled look-back (desc).  MODE 1 / 2 (experiment PCB_OCT_3PASS): reduce-then-scan without
+// any waiting - MODE 1 only writes the tile's aggregate to agg[tile], k_oct_tilescan turns the aggregates into exclusive
+// prefixes, MODE 2 is the pass proper with its prefix read from agg[tile] (the 8-byte emission words are read twice).
+template <int OCT_THREADS, int OCT_ITEMS, int MODE = 0>
 __global__ void __launch_bounds__(OCT_THREADS, 5)   // 48 registers: 5 blocks per SM (4: 3.07 ms, 5: 3.00, 6: 3.05 per C2 step)
-k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
+k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc, Oct8* __restrict__ agg = nullptr) {
     constexpr int WARPS = OCT_THREADS / 32;
     constexpr int OCT_TILE = OCT_THREADS * OCT_ITEMS;
     static_assert(OCT_TILE <= OCT_TILE_MAX && OCT_ITEMS % 8 == 0, "tile shape");
@@ -1279,9 +1282,16 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
             tot8.c[4 + k] = (u32)(total.hi >> (16 * k)) & 0xFFFFu;
         }
         tot8.head = total.head;
-        Oct8 prefix = chain_lookback(op, desc, tile, tot8, op.err);
-        if (lane == 0) s_prefix = prefix;
+        if (MODE == 1) {
+            if (lane == 0) agg[tile] = tot8;
+        } else if (MODE == 2) {
+            if (lane == 0) s_prefix = agg[tile];
+        } else {
+            Oct8 prefix = chain_lookback(op, desc, tile, tot8, op.err);
+            if (lane == 0) s_prefix = prefix;
+        }
     }
+    if (MODE == 1) return;
     __syncthreads();
     // running 32-bit counters of this thread: prefix (+) texcl
     u32 run[8];
@@ -1341,6 +1351,40 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
             if (base + k < n) op.rank[base + k] = rk[k];
     }
 }
+// exclusive segmented scan of the tile aggregates (one block): combine(a, b) = b.head ? b : a + b
+__global__ void __launch_bounds__(1024) k_oct_tilescan(Oct8* __restrict__ agg, u32 ntiles) {
+    __shared__ Oct8 sh[1024];
+    OctScanOp op{};
+    const u32 per = (ntiles + 1023u) / 1024u;
+    const u32 lo = min(ntiles, threadIdx.x * per), hi = min(ntiles, lo + per);
+    Oct8 acc = op.identity();
+    for (u32 i = lo; i < hi; i++) acc = op.combine(acc, agg[i]);
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        Oct8 v = sh[threadIdx.x];
+        if (threadIdx.x >= (u32)d) v = op.combine(sh[threadIdx.x - d], v);
+        __syncthreads();
+        sh[threadIdx.x] = v;
+        __syncthreads();
+    }
+    Oct8 run = threadIdx.x ? sh[threadIdx.x - 1] : op.identity();
+    for (u32 i = lo; i < hi; i++) {
+        const Oct8 v = agg[i];
+        agg[i] = run;
+        run = op.combine(run, v);
+    }
+}
+// temp must hold max(chain_temp_bytes(ntiles), 36 * ntiles) bytes
+static inline int octscan_3pass(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
+    const u32 ntiles = div_up(n, 256 * 16);
+    if (!ntiles) return 0;
+    Oct8* agg = (Oct8*)temp;
+    k_octscan<256, 16, 1><<<ntiles, 256, 0, st>>>(op, n, ntiles, nullptr, agg);
+    k_oct_tilescan<<<1, 1024, 0, st>>>(agg, ntiles);
+    k_octscan<256, 16, 2><<<ntiles, 256, 0, st>>>(op, n, ntiles, nullptr, agg);
+    return 3;
+}
 template <int T, int I>
 static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
     const u32 ntiles = div_up(n, T * I);
@@ -1351,6 +1395,8 @@ static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStr
 }
 static inline int octscan(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
     static const int variant = pcb_tuning_env("PCB_OCT_VARIANT") ? atoi(pcb_tuning_env("PCB_OCT_VARIANT")) : 0;   // tuning hook
+    static const bool three = pcb_tuning_env("PCB_OCT_3PASS") != nullptr;   // experiment: reduce / tile scan / apply
+    if (three) return octscan_3pass(op, n, temp, st);
     switch (variant) {
         case 1: return octscan_launch<256, 8>(op, n, temp, st);
         case 2: return octscan_launch<128, 16>(op, n, temp, st);
