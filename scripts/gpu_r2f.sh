@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
 tail -5 gpurun_out/pytest_gpu.log
-PCB_ENABLE_TUNING=1 PCB_CONTEST_HALO=1 PCB_OCT_3PASS=1 timeout 1500 python -m pytest tests/test_gpu_parity.py tests/test_gpu_fullsize.py -m gpu -x -q > gpurun_out/pytest_halo.log 2>&1; echo "halo rc=$?" >> gpurun_out/pytest_halo.log
+PCBTEST_ALLOW_TUNING=1 PCB_ENABLE_TUNING=1 PCB_CONTEST_HALO=1 PCB_OCT_3PASS=1 timeout 1500 python -m pytest tests/test_gpu_parity.py tests/test_gpu_fullsize.py -m gpu -x -q > gpurun_out/pytest_halo.log 2>&1; echo "halo rc=$?" >> gpurun_out/pytest_halo.log
 tail -5 gpurun_out/pytest_halo.log
 B="python bench.py --no-cpu --no-files --e2e-steps 0"
 for w in terrain cube blobs; do
