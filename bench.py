@@ -205,9 +205,13 @@ def run_reference(args, rank, world):
         import synth
         pts = synth.terrain(n, 3, "cpu", terrain_extent(n), surface_seed=2).numpy()
         threads = 1   # the merge run re-reads node files: the oracle's worker split is for fresh runs
+    if args.lru and not out_dir:
+        tmp = tempfile.mkdtemp(prefix="pcb_ref_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+        out_dir = os.path.join(tmp, "out")
+        threads = 1
     vals = []
-    for _ in range(max(1, min(args.steps, 1 if n > 20_000_000 else 2))):
-        v, dt = cpu_oracle_run(pts, threads, out_dir=out_dir)
+    for _ in range(max(1, min(args.steps, 1 if (n > 20_000_000 or args.lru) else 2))):
+        v, dt = cpu_oracle_run(pts, threads, out_dir=out_dir, lru=args.lru)
         vals.append((v, dt))
         if out_dir:
             break
@@ -217,7 +221,9 @@ def run_reference(args, rank, world):
     dt = statistics.median([x[1] for x in vals])
     sample = (f"{n} points = {'the full' if n == args.points else 'a sample of the'} single-GPU workload, same generator on the "
               f"host ({ncell0} level-0 cells), {threads} thread(s): one per level-0 cell, the only parallelism the "
-              f"reference's algorithm has (its CLI is single-threaded)")
+              f"reference's algorithm has (its CLI is single-threaded)" +
+              (f"; cell residency as in the reference CLI: LRU of {args.lru} cells, node files on tmpfs (converter.rs:92, 160-216)"
+               if args.lru else "; all cells in RAM, no files"))
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": round(v, 4), "unit": UNIT, "n_gpus": args.gpus,
         "steps": len(vals), "warmup": 0, "ms_per_step": round(dt * 1e3, 1), "higher_is_better": True,
@@ -254,6 +260,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-scale", type=float, default=1.0, help="scales the CPU legs (1.0 = the full workload)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--lru", type=int, default=0, help="--impl reference: emulate the reference CLI's cell residency (LRU of "
+                    "this many cells, 100 in converter.rs:92, evicted cells rewritten whole to node files on tmpfs); 1 thread")
     ap.add_argument("--no-files", action="store_true", help="skip the e2e_files legs (tmpfs node files, cold CLI process)")
     ap.add_argument("--no-check", action="store_true", help="skip the verified step at N > 1")
     ap.add_argument("--rebalance", default="auto", help="N > 1: level-l re-balance: auto (default) | off | <level>")
