@@ -1067,21 +1067,6 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                                      : chain_scan<ContestOp<PAIRS>, 256, 8, 3>(cop, cnt, scan_tmp, st, nd);
         pe("contest", nl, cnt, (PAIRS ? 28ull : 24ull) * cnt);
     };
-    // experiment (PCB_CONTEST_HALO=1|2|3 = 256 x 8 three blocks | 128 x 8 six | 256 x 8 four): the halo contest, level.cuh
-    static const int contest_halo = pcb_tuning_env("PCB_CONTEST_HALO") ? atoi(pcb_tuning_env("PCB_CONTEST_HALO")) : 0;
-    auto run_contest_halo = [&](const ContestOp<PAIRS>& cop, u32 cnt) {
-        if (!cnt) return;
-        pb();
-        const u32 threads = contest_halo == 2 ? 128 : 256;
-        const u32 nt = div_up(cnt, threads * 8);
-        uint4* desc = (uint4*)scan_tmp;
-        u32* wstatus = (u32*)((unsigned char*)scan_tmp + chain_temp_bytes(nt));
-        CUDA_TRY(cudaMemsetAsync(scan_tmp, 0, chain_temp_bytes(nt) + 4ull * nt, st));
-        if (contest_halo == 2) k_contest_halo<PAIRS, 128, 6><<<nt, 128, 0, st>>>(cop, cnt, nt, desc, wstatus);
-        else if (contest_halo == 3) k_contest_halo<PAIRS, 256, 4><<<nt, 256, 0, st>>>(cop, cnt, nt, desc, wstatus);
-        else k_contest_halo<PAIRS, 256, 3><<<nt, 256, 0, st>>>(cop, cnt, nt, desc, wstatus);
-        pe("contest", 1, cnt, (PAIRS ? 28ull : 24ull) * cnt);
-    };
     // sort plan of `cnt` keys spread over the level's cells: segmented when the cell bits would cost extra passes
     // (radix.cuh): runs of 2^segk consecutive cells are sorted independently inside the same launches.  Taken when
     // segments average >= PCB_SEG_MIN keys (tiles never straddle a segment: small segments mean partly filled tiles).
@@ -1200,12 +1185,8 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
             k_keys_hist<<<std::min<u32>(148 * 4, div_up(nS2, 256)), 256, 0, st>>>(s2A, nS2, plan2, rt2.ghist);
             pe("filter", 3, nS2, 24ull * nS2);
             cur = radix_sort<PAIRS>(s2A, nullptr, s2B, nullptr, nS2, plan2, rt2, st, *this);
-            if (contest_halo)
-                run_contest_halo(ContestOp<PAIRS>{cur ? s2B : s2A, nullptr, nS2, lay, g, d2oct, geo, em, win_src, win_end,
-                                                  &d_scr->nwin, &d_scr->err, nullptr, estart, nullptr}, nS2);
-            else
-                run_contest(ContestOp<PAIRS>{cur ? s2B : s2A, nullptr, nS2, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin,
-                                             &d_scr->err, nullptr, estart, nullptr}, nS2);
+            run_contest(ContestOp<PAIRS>{cur ? s2B : s2A, nullptr, nS2, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin,
+                                         &d_scr->err, nullptr, estart, nullptr}, nS2);
             trace_mark(st, "round2", h, nS2);
             dfree(s2A); dfree(s2B); dfree(T.slots); dfree(ncand); dfree(wkeys);
             filtered = true;
@@ -1239,12 +1220,8 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         trace_mark(st, "sort", h, n);
 
         // ---- stage 4: contest
-        if (contest_halo)
-            run_contest_halo(ContestOp<PAIRS>{ks, vs, n, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err,
-                                              nullptr, nullptr, nullptr}, n);
-        else
-            run_contest(ContestOp<PAIRS>{ks, vs, n, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err, nullptr,
-                                         nullptr, nullptr}, n);
+        run_contest(ContestOp<PAIRS>{ks, vs, n, lay, g, d2oct, geo, em, win_src, win_end, &d_scr->nwin, &d_scr->err, nullptr,
+                                     nullptr, nullptr}, n);
         trace_mark(st, "contest", h, n);
     }
     int nl = 0;

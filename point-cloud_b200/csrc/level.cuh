@@ -645,29 +645,10 @@ struct ContestOp {
     // meta bits of a single element: 0-3 child octant, 8 group head, 9 group tail, 10 last of its cell in sorted
     // order, 11 first arrival of its cell, 12 last arrival of its cell
     __device__ void load_items(u64 base, State (&v)[ITEMS]) const {
-        u64 hk;
-        uint2 hr;
-        u32 hp;
-        bool hv;
-        load_items_halo<false>(base, v, 0, hk, hr, hp, hv);
-    }
-    // HALO (k_contest_halo): lane l of the block's first warp also loads sorted element tbase - 1 - l (the 32 elements
-    // before the tile) with its contest record: hkey / hrec / hpos, hvalid = that element exists.
-    template <bool HALO>
-    __device__ __forceinline__ void load_items_halo(u64 base, State (&v)[ITEMS], u64 tbase, u64& hkey, uint2& hrec, u32& hpos,
-                                                    bool& hvalid) const {
         const int lane = threadIdx.x & 31;
         const u32 n = n_dev ? __ldg(n_dev) : this->n;
         u64 key[ITEMS];
         u32 pos[ITEMS];
-        hvalid = false;
-        hkey = ~0ull;
-        hrec = make_uint2(0u, 0u);
-        hpos = 0u;
-        if (HALO && threadIdx.x < 32) {
-            hvalid = tbase >= 1ull + (u64)lane && tbase - 1ull - lane < n;
-            if (hvalid) hkey = keys[tbase - 1ull - lane];
-        }
         if (base + ITEMS <= n) {
             const ulonglong2* src = (const ulonglong2*)(keys + base);
 #pragma unroll
@@ -692,10 +673,6 @@ struct ContestOp {
             const uint2 rec = (base + k < n) ? __ldg(d2oct + pos[k]) : make_uint2(0u, 0u);
             d2v[k] = rec.x;
             ocv[k] = rec.y;
-        }
-        if (HALO && hvalid) {
-            hpos = PAIRS ? vals[tbase - 1ull - lane] : (u32)(hkey & ((1ull << lay.pb) - 1ull));
-            hrec = __ldg(d2oct + hpos);
         }
         // neighbours across the thread boundary
         u64 prevk = __shfl_up_sync(0xFFFFFFFFu, key[ITEMS - 1], 1);
@@ -741,22 +718,6 @@ struct ContestOp {
         return r;
     }
     __device__ void consume(u32 j, const State& excl, const State& incl, const State& self) const {
-        winner(j, excl.ntail, incl, self);
-        emit(j, excl, self);
-    }
-    // the winner of the group that ends at sorted element j; wi = its ordinal among all winners
-    __device__ __forceinline__ void winner(u32 j, u32 wi, const State& incl, const State& self) const {
-        if (self.meta & 0x200u) {
-            win_src[wi] = (u32)incl.mn;
-            if (tails) {
-                const u64 G = gid(keys[j]);
-                tails[wi] = make_uint4((u32)G, (u32)(G >> 32), (u32)(incl.mn >> 32), (u32)incl.mn);
-            }
-        }
-        if (self.meta & 0x400u) win_end[(u32)(gid(keys[j]) >> g.hexbits)] = wi + 1;
-    }
-    // the emission triggered by sorted element j (cell.rs:80-92)
-    __device__ __forceinline__ void emit(u32 j, const State& excl, const State& self) const {
         const u32 pos = (u32)self.mn;
         u64 e;
         if (self.meta & 0x100u) {
@@ -766,6 +727,14 @@ struct ContestOp {
         } else {
             e = ((u64)(self.meta & 0xFu) << 32) | pos;
         }
+        if (self.meta & 0x200u) {
+            win_src[excl.ntail] = (u32)incl.mn;
+            if (tails) {
+                const u64 G = gid(keys[j]);
+                tails[excl.ntail] = make_uint4((u32)G, (u32)(G >> 32), (u32)(incl.mn >> 32), (u32)incl.mn);
+            }
+        }
+        if (self.meta & 0x400u) win_end[(u32)(gid(keys[j]) >> g.hexbits)] = excl.ntail + 1;
         if (self.meta & 0x800u) e |= PCB_EM_CELL_FIRST;
         if (self.meta & 0x1000u) e |= PCB_EM_CELL_LAST;
         if (estart) {
@@ -776,151 +745,6 @@ struct ContestOp {
     }
     __device__ void finish(const State& total) const { *nwin_out = total.ntail; }
 };
-
-// warp-wide decoupled look-back over plain 32-bit counts (flag bits inside the word, as the radix passes do):
-// publishes `count` for tile `tile`, returns the sum over the tiles before it (all lanes)
-__device__ __forceinline__ u32 chain_sum_lookback(u32* __restrict__ status, u32 tile, u32 count, u32* err) {
-    const int lane = threadIdx.x & 31;
-    volatile u32* st = status;
-    if (lane == 0) st[tile] = count | (tile == 0 ? RADIX_FLAG_INCL : RADIX_FLAG_AGG);
-    u32 prefix = 0;
-    int look = (int)tile - 1;
-    u32 spins = 0;
-    while (look >= 0) {
-        const int t = look - lane;
-        u32 w = RADIX_FLAG_INCL;
-        if (t >= 0) {
-            w = st[t];
-            while ((w & (RADIX_FLAG_AGG | RADIX_FLAG_INCL)) == 0u) {
-                w = st[t];
-                if (++spins > PCB_SPIN_LIMIT) {
-                    if (err) atomicOr(err, PCB_DERR_TIMEOUT);
-                    w = RADIX_FLAG_INCL;
-                }
-            }
-        }
-        const u32 m = __ballot_sync(0xFFFFFFFFu, (w & RADIX_FLAG_INCL) != 0u);
-        const int last = m ? (__ffs(m) - 1) : 31;
-        u32 v = lane <= last ? (w & RADIX_COUNT_MASK) : 0u;
-#pragma unroll
-        for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
-        prefix += v;
-        if (m) break;
-        look -= 32;
-    }
-    if (lane == 0 && tile > 0) st[tile] = ((prefix + count) & RADIX_COUNT_MASK) | RADIX_FLAG_INCL;
-    return prefix;
-}
-
-// The contest of a whole level WITHOUT the block waiting for earlier tiles before it emits.  The scan is segmented by
-// prism group, so the only running-minimum state a tile needs from its predecessors is that of the group that
-// straddles its first element - and that group's earlier members are (almost always) among the 32 sorted elements
-// right before the tile.  The block's first warp loads them as a HALO together with the tile (the same two dependent
-// loads: key, then contest record) and folds them into the tile's exclusive prefix; the tile then knows its inclusive
-// (minimum, octant) state at once and publishes it.  Only when the halo ends inside the group (a prism with more than
-// 32 arrivals before the tile start) does the tile fall back to the chained look-back over those descriptors
-// (scan.cuh), which every tile feeds.  The one thing that still travels between tiles is the NUMBER of groups
-// completed before the tile (the slot of its first winner in win_src): a 32-bit decoupled look-back that the first
-// warp runs WHILE the other warps already emit; winners are written after it.
-template <bool PAIRS, int THREADS, int MINB>
-__global__ void __launch_bounds__(THREADS, MINB)
-k_contest_halo(ContestOp<PAIRS> op, u32 n, u32 ntiles, uint4* __restrict__ desc, u32* __restrict__ wstatus) {
-    typedef ContestState State;
-    typedef ContestOp<PAIRS> Op;
-    constexpr int ITEMS = Op::ITEMS, WARPS = THREADS / 32;
-    if (op.n_dev) n = __ldg(op.n_dev);
-    __shared__ State s_warp[WARPS];
-    __shared__ State s_prefix;
-    __shared__ u32 s_need, s_wbase;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const u32 tile = blockIdx.x;
-    const u64 tbase = (u64)tile * (THREADS * ITEMS), base = tbase + (u64)tid * ITEMS;
-
-    State v[ITEMS];
-    u64 hkey;
-    uint2 hrec;
-    u32 hpos;
-    bool hvalid;
-    op.template load_items_halo<true>(base, v, tbase, hkey, hrec, hpos, hvalid);
-    State acc = op.identity();
-#pragma unroll
-    for (int k = 0; k < ITEMS; k++) acc = op.combine(acc, v[k]);
-    State winc = acc;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        State up = shfl_up_state(winc, d);
-        if (lane >= d) winc = op.combine(up, winc);
-    }
-    if (lane == 31) s_warp[warp] = winc;
-    if (warp == 0) {
-        // halo: the members of the group of sorted element tbase - 1 that lie in [tbase - 32, tbase)
-        const u64 G0 = op.gid(__shfl_sync(0xFFFFFFFFu, hkey, 0));
-        const u32 m = __ballot_sync(0xFFFFFFFFu, hvalid && op.gid(hkey) == G0);
-        const int run = (m == 0xFFFFFFFFu) ? 32 : (__ffs(~m) - 1);
-        u64 mn = (lane < run) ? (((u64)hrec.x << 32) | hpos) : ~0ull;
-        u32 oc = hrec.y & 0xFu;
-#pragma unroll
-        for (int d = 16; d; d >>= 1) {
-            const u64 omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d);
-            const u32 ooc = __shfl_xor_sync(0xFFFFFFFFu, oc, d);
-            if (omn < mn) { mn = omn; oc = ooc; }
-        }
-        if (lane == 0) {
-            s_prefix = State{mn, oc, 0u};
-            // the group may begin before the halo (no matter when the tile starts with a group head)
-            s_need = (run == 32 && tbase > 32u && !(v[0].meta & 0x100u)) ? 1u : 0u;
-        }
-    }
-    __syncthreads();
-    State wpre = op.identity(), total = op.identity();
-    if (warp == 0) {
-#pragma unroll
-        for (int w = 0; w < WARPS; w++) total = op.combine(total, s_warp[w]);
-    } else {
-#pragma unroll
-        for (int w = 0; w < WARPS - 1; w++)
-            if (w < warp) wpre = op.combine(wpre, s_warp[w]);
-    }
-    State texcl = shfl_up_state(winc, 1);
-    if (lane == 0) texcl = op.identity();
-    texcl = op.combine(wpre, texcl);
-    if (s_need) {   // rare: chained look-back for the straddling group
-        if (warp == 0) {
-            State prefix = chain_lookback(op, desc, tile, total, op.err);
-            if (lane == 0) s_prefix = prefix;
-        }
-        __syncthreads();
-    } else if (tid == 0) {
-        chain_publish<Op>(desc, tile, op.combine(s_prefix, total), PCB_DESC_INCL);
-    }
-    if (warp == 0) {   // winners before this tile: overlapped with the emission of the other warps
-        const u32 wbase = chain_sum_lookback(wstatus, tile, total.ntail, op.err);
-        if (lane == 0) s_wbase = wbase;
-    }
-    const State start = op.combine(s_prefix, texcl);
-    State run = start;
-#pragma unroll
-    for (int k = 0; k < ITEMS; k++) {
-        const u64 i = base + k;
-        if (i < n) {
-            op.emit((u32)i, run, v[k]);
-            run = op.combine(run, v[k]);
-        }
-    }
-    __syncthreads();
-    u32 wi = s_wbase + texcl.ntail;
-    run = start;
-#pragma unroll
-    for (int k = 0; k < ITEMS; k++) {
-        const u64 i = base + k;
-        if (i < n) {
-            run = op.combine(run, v[k]);
-            op.winner((u32)i, wi, run, v[k]);
-            wi += v[k].ntail;
-        }
-    }
-    if (tile == ntiles - 1 && tid == THREADS - 1) *op.nwin_out = wi;
-}
 
 // ---- record filter ---------------------------------------------------------------------------------------------------
 // On the upper levels a prism receives hundreds of arrivals and all but a handful of them lose to an incumbent
@@ -1204,12 +1028,9 @@ __device__ __forceinline__ OctPacked oct_combine(const OctPacked& a, const OctPa
     r.head = a.head | b.head;
     return r;
 }
-// MODE 0: single pass with a decoupled look-back (desc).  MODE 1 / 2 (experiment PCB_OCT_3PASS): reduce-then-scan without
-// any waiting - MODE 1 only writes the tile's aggregate to agg[tile], k_oct_tilescan turns the aggregates into exclusive
-// prefixes, MODE 2 is the pass proper with its prefix read from agg[tile] (the 8-byte emission words are read twice).
-template <int OCT_THREADS, int OCT_ITEMS, int MODE = 0>
+template <int OCT_THREADS, int OCT_ITEMS>
 __global__ void __launch_bounds__(OCT_THREADS, 5)   // 48 registers: 5 blocks per SM (4: 3.07 ms, 5: 3.00, 6: 3.05 per C2 step)
-k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc, Oct8* __restrict__ agg = nullptr) {
+k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     constexpr int WARPS = OCT_THREADS / 32;
     constexpr int OCT_TILE = OCT_THREADS * OCT_ITEMS;
     static_assert(OCT_TILE <= OCT_TILE_MAX && OCT_ITEMS % 8 == 0, "tile shape");
@@ -1282,16 +1103,9 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc, Oct8* __res
             tot8.c[4 + k] = (u32)(total.hi >> (16 * k)) & 0xFFFFu;
         }
         tot8.head = total.head;
-        if (MODE == 1) {
-            if (lane == 0) agg[tile] = tot8;
-        } else if (MODE == 2) {
-            if (lane == 0) s_prefix = agg[tile];
-        } else {
-            Oct8 prefix = chain_lookback(op, desc, tile, tot8, op.err);
-            if (lane == 0) s_prefix = prefix;
-        }
+        Oct8 prefix = chain_lookback(op, desc, tile, tot8, op.err);
+        if (lane == 0) s_prefix = prefix;
     }
-    if (MODE == 1) return;
     __syncthreads();
     // running 32-bit counters of this thread: prefix (+) texcl
     u32 run[8];
@@ -1351,40 +1165,6 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc, Oct8* __res
             if (base + k < n) op.rank[base + k] = rk[k];
     }
 }
-// exclusive segmented scan of the tile aggregates (one block): combine(a, b) = b.head ? b : a + b
-__global__ void __launch_bounds__(1024) k_oct_tilescan(Oct8* __restrict__ agg, u32 ntiles) {
-    __shared__ Oct8 sh[1024];
-    OctScanOp op{};
-    const u32 per = (ntiles + 1023u) / 1024u;
-    const u32 lo = min(ntiles, threadIdx.x * per), hi = min(ntiles, lo + per);
-    Oct8 acc = op.identity();
-    for (u32 i = lo; i < hi; i++) acc = op.combine(acc, agg[i]);
-    sh[threadIdx.x] = acc;
-    __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {
-        Oct8 v = sh[threadIdx.x];
-        if (threadIdx.x >= (u32)d) v = op.combine(sh[threadIdx.x - d], v);
-        __syncthreads();
-        sh[threadIdx.x] = v;
-        __syncthreads();
-    }
-    Oct8 run = threadIdx.x ? sh[threadIdx.x - 1] : op.identity();
-    for (u32 i = lo; i < hi; i++) {
-        const Oct8 v = agg[i];
-        agg[i] = run;
-        run = op.combine(run, v);
-    }
-}
-// temp must hold max(chain_temp_bytes(ntiles), 36 * ntiles) bytes
-static inline int octscan_3pass(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
-    const u32 ntiles = div_up(n, 256 * 16);
-    if (!ntiles) return 0;
-    Oct8* agg = (Oct8*)temp;
-    k_octscan<256, 16, 1><<<ntiles, 256, 0, st>>>(op, n, ntiles, nullptr, agg);
-    k_oct_tilescan<<<1, 1024, 0, st>>>(agg, ntiles);
-    k_octscan<256, 16, 2><<<ntiles, 256, 0, st>>>(op, n, ntiles, nullptr, agg);
-    return 3;
-}
 template <int T, int I>
 static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
     const u32 ntiles = div_up(n, T * I);
@@ -1395,8 +1175,6 @@ static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStr
 }
 static inline int octscan(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
     static const int variant = pcb_tuning_env("PCB_OCT_VARIANT") ? atoi(pcb_tuning_env("PCB_OCT_VARIANT")) : 0;   // tuning hook
-    static const bool three = pcb_tuning_env("PCB_OCT_3PASS") != nullptr;   // experiment: reduce / tile scan / apply
-    if (three) return octscan_3pass(op, n, temp, st);
     switch (variant) {
         case 1: return octscan_launch<256, 8>(op, n, temp, st);
         case 2: return octscan_launch<128, 16>(op, n, temp, st);
