@@ -639,7 +639,7 @@ class ShardedBuild:
     share.  Balanced clouds (C2, C5) never leave level 0 and pay nothing."""
 
     def __init__(self, pcb, device_index, batch_size=10_000, max_cell_size=1000.0, group=None, stream=None, flags=0,
-                 out_dir=None, rebalance="auto", max_level=8, profile=False):
+                 out_dir=None, rebalance="auto", max_level=12, profile=False):
         self.pcb, self.dev_index, self.bs, self.S0 = pcb, device_index, batch_size, max_cell_size
         self.group, self.stream, self.flags, self.out_dir = group, stream, flags, out_dir
         self.rebalance, self.max_level = rebalance, max_level
