@@ -342,7 +342,7 @@ def main():
         """N GPUs: one collective conversion step of this rank through shard.ShardedBuild (fused level-0 exchange, level-l
         re-balance by the automatic rule unless --rebalance says otherwise, build).  Returns (stats, kernel stats[, sb])."""
         rb = args.rebalance if args.rebalance in ("auto", "off") else int(args.rebalance)
-        sb = shard.ShardedBuild(pcb, local_rank, group=None, stream=stream, flags=flags, rebalance=rb)
+        sb = shard.ShardedBuild(pcb, local_rank, group=None, stream=stream, flags=flags, rebalance=rb, collect_nodes=keep_open)
         try:
             st, ks = sb.run(src, rank * n)
             exchange[0] = sb.info.get("exchange", "")

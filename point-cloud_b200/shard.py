@@ -600,7 +600,8 @@ def rebalance(pcb, arr, group=None):
     arr = dict(arr, level=int(lv.item()))
     split = _split_for_owners(arr, owners[offs[rank]:offs[rank + 1]], world)
     gather = torch.cat([s[0] for s in split])
-    send_pts = arr["pts"][gather].contiguous() if arr["n"] else arr["pts"]
+    # (16-byte records gathered as two 8-byte words: torch's row gather of 16 x u8 is an order of magnitude slower)
+    send_pts = arr["pts"].view(torch.int64).view(-1, 2)[gather].view(torch.uint8).view(-1, 16) if arr["n"] else arr["pts"]
     send_bat = arr["bat"][gather].contiguous() if arr["n"] else arr["bat"]
     ins = [int(s[1].sum()) for s in split]
     # what every source sends to me: from the global table (no second count exchange)
@@ -639,11 +640,14 @@ class ShardedBuild:
     share.  Balanced clouds (C2, C5) never leave level 0 and pay nothing."""
 
     def __init__(self, pcb, device_index, batch_size=10_000, max_cell_size=1000.0, group=None, stream=None, flags=0,
-                 out_dir=None, rebalance="auto", max_level=12, profile=False):
+                 out_dir=None, rebalance="auto", max_level=4, profile=False, collect_nodes=False):
         self.pcb, self.dev_index, self.bs, self.S0 = pcb, device_index, batch_size, max_cell_size
         self.group, self.stream, self.flags, self.out_dir = group, stream, flags, out_dir
         self.rebalance, self.max_level = rebalance, max_level
+        self.collect_nodes = collect_nodes   # keep every handle's node images (tests, bench check) when handles are retired
         self.handles = []
+        self._nodes = {}
+        self._kstats = {}
         self.info = {}
 
     def _open(self):
@@ -653,13 +657,24 @@ class ShardedBuild:
         self.handles.append(cv)
         return cv
 
+    def _retire(self, cv):
+        """A handle whose pending arrivals have been consumed: keep what is asked for, free its arenas."""
+        for k in cv.kernel_stats():
+            d = self._kstats.setdefault(k["name"], dict(name=k["name"], launches=0, units=0, bytes=0, ms=0.0))
+            for f in ("launches", "units", "bytes", "ms"):
+                d[f] += k[f]
+        if self.collect_nodes:
+            self._nodes.update(cv.nodes())
+        cv.close()
+        self.handles.remove(cv)
+
     def close(self):
-        for cv in self.handles:
+        for cv in list(self.handles):
             cv.close()
         self.handles = []
 
     def nodes(self):
-        out = {}
+        out = dict(self._nodes)
         for cv in self.handles:
             out.update(cv.nodes())
         return out
@@ -717,15 +732,20 @@ class ShardedBuild:
                     do_rebalance = not go_deeper and level > 0
                 if not go_deeper:
                     break
+                prev = self.handles[-1] if self.handles else None
                 cv = self._open()                       # the owners build exactly one more level
                 add_arrivals_to(cv, arr)
                 cv.set_stop_level(level + 1)
                 stats.append(cv.finish())
+                if prev is not None:
+                    self._retire(prev)                  # its pending arrivals (this level's input) are consumed
                 arr = pending_to_arrivals(cv, dev)
                 arr["level"] = level + 1
                 level += 1
             if do_rebalance:
                 arr = rebalance(pcb, arr, group=self.group)
+                if self.handles:
+                    self._retire(self.handles[-1])      # the re-balanced arrivals are copies
                 self._keep.append(arr)
                 self.info["rebalance_level"] = level
                 self.info["rebalance_moved_bytes"] = arr.get("moved_bytes", 0)
@@ -733,7 +753,7 @@ class ShardedBuild:
             add_arrivals_to(cv, arr)
             stats.append(cv.finish())
             self.info["build_arrivals_after_cut"] = int(stats[-1].arrivals)
-        ks = {}
+        ks = {k: dict(v) for k, v in self._kstats.items()}
         for cv in self.handles:
             for k in cv.kernel_stats():
                 d = ks.setdefault(k["name"], dict(name=k["name"], launches=0, units=0, bytes=0, ms=0.0))
