@@ -159,7 +159,10 @@ int pcb_add_arrivals(pcb_handle* h, uint32_t level, const pcb_point* d_pts, cons
    the device and are described by pcb_pending_arrivals (valid until pcb_close).  Call before pcb_finish. */
 int pcb_set_stop_level(pcb_handle* h, uint32_t stop_level);
 typedef struct pcb_arrivals {
-    uint32_t level, reserved;
+    uint32_t level;
+    float prism_load;               /* arrivals per occupied hex prism on the last level built: pass it to the handle that
+                                       resumes (pcb_set_prism_load) so that its first level takes the same record-filter
+                                       decision a single handle would have taken; a performance hint, never affects results */
     uint64_t n, ncell;
     const pcb_point* d_pts;
     const uint32_t* d_batch_plus1;
@@ -167,6 +170,7 @@ typedef struct pcb_arrivals {
     const int32_t* d_cell_idx;      /* [3 * ncell] */
 } pcb_arrivals;
 int pcb_pending_arrivals(const pcb_handle* h, pcb_arrivals* out);
+int pcb_set_prism_load(pcb_handle* h, float prism_load);
 int pcb_finish(pcb_handle* h, pcb_stats* stats);
 /* Metadata::write_to (metadata.rs:51-53) for a reduced result: used by rank 0 after the per-rank builds. */
 int pcb_write_metadata(const char* out_dir, uint64_t number_of_points, uint32_t hierarchies, const float bbox_min[3],

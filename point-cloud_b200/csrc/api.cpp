@@ -257,11 +257,16 @@ int pcb_set_stop_level(pcb_handle* h, uint32_t stop_level) {
     PCB_GUARD(h, h->builder->set_stop_level(stop_level))
 }
 
+int pcb_set_prism_load(pcb_handle* h, float prism_load) {
+    if (h && h->finished) return fail(h, PCB_ERR_ARG, "handle already finished");
+    PCB_GUARD(h, h->builder->set_prism_load(prism_load > 0.0f ? (double)prism_load : 0.0))
+}
+
 int pcb_pending_arrivals(const pcb_handle* h, pcb_arrivals* out) {
     if (!h || !out || !h->finished) return PCB_ERR_ARG;
     const PendingArrivals p = h->builder->pending();
     out->level = p.level;
-    out->reserved = 0;
+    out->prism_load = (float)p.prism_load;
     out->n = p.n;
     out->ncell = p.ncell;
     out->d_pts = p.d_pts;

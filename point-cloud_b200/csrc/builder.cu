@@ -272,6 +272,7 @@ class BuilderImpl {
         bool has_box = false;
         float lo[3], hi[3];
         u64 count_points = 0;              // added to metadata.number_of_points (0: counted by another handle)
+        double prism_load = 0;             // arrivals per occupied prism on the level that produced them (0: unknown)
     } ext;
     // partial build: levels >= stop_level are not built; their arrivals stay on the device (pend_*)
     u32 stop_level = 0xFFFFFFFFu;
@@ -683,6 +684,7 @@ void BuilderImpl::build(Metadata* meta, NodeSource* existing) {
             CUDA_TRY(cudaMemcpyAsync(d_scr, h_scr, sizeof init, cudaMemcpyHostToDevice, st));
             arena_prepare(2, 18ull * ext.n + (64ull << 20));
             cur_arena = 0;
+            last_mult = ext.prism_load;   // the record filter's prediction for level ext.level (build_level)
             run_levels(meta, existing, ext.level, (PcbPoint*)ext.pts, (u32*)ext.bat, (u32*)ext.cell_start, (int*)ext.cell_idx,
                        ext.n, ext.ncell);
         }
@@ -1371,6 +1373,7 @@ void Builder::add_arrivals(uint32_t level, const pcb_point* d_pts, const uint32_
     guarded([&] { impl_->add_arrivals(level, d_pts, d_bat, n, d_cell_start, d_cell_idx, ncell, bbox6, count_points); return 0; });
 }
 void Builder::set_stop_level(uint32_t level) { impl_->stop_level = level; }
+void Builder::set_prism_load(double v) { impl_->ext.prism_load = v; }
 PendingArrivals Builder::pending() const {
     PendingArrivals p;
     p.level = impl_->pend_level;
@@ -1380,6 +1383,7 @@ PendingArrivals Builder::pending() const {
     p.d_bat = impl_->pend_bat;
     p.d_cell_start = impl_->pend_cell_start;
     p.d_cell_idx = impl_->pend_cell_idx;
+    p.prism_load = impl_->last_mult;
     return p;
 }
 void Builder::add_points_one_batch(const pcb_point* pts, uint64_t n, bool device_ptr) {

@@ -77,6 +77,7 @@ struct PendingArrivals {
     const uint32_t* d_bat = nullptr;          // batch ordinal + 1
     const uint32_t* d_cell_start = nullptr;   // [ncell + 1]
     const int32_t* d_cell_idx = nullptr;      // [3 * ncell]
+    double prism_load = 0;                    // arrivals per occupied prism on the last level built (record-filter hint)
 };
 
 class BuilderImpl;
@@ -96,6 +97,7 @@ class Builder {
                       const uint32_t* d_cell_start, const int32_t* d_cell_idx, uint64_t ncell, const float* bbox6,
                       uint64_t count_points);
     void set_stop_level(uint32_t level);   // build() stops before this level; its arrivals stay on the device
+    void set_prism_load(double v);         // hint that travels with pending arrivals (see PendingArrivals)
     PendingArrivals pending() const;
     // uncompressed LAS point records (host bytes), decoded on the device (converter/las.rs:32-41)
     void add_las_records(const uint8_t* records, uint64_t n, uint32_t stride, int32_t colour_off, const double scale[3],

@@ -30,7 +30,7 @@ EXPORTS = [
     "pcb_open", "pcb_set_stream", "pcb_begin_file", "pcb_add_points", "pcb_add_points_batch", "pcb_reserve",
     "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
     "pcb_route_bbox", "pcb_route_bbox_static", "pcb_route_histogram", "pcb_route_pack", "pcb_route_scatter",
-    "pcb_add_las_records", "pcb_alloc_host", "pcb_free_host", "pcb_add_arrivals", "pcb_set_stop_level", "pcb_pending_arrivals",
+    "pcb_add_las_records", "pcb_alloc_host", "pcb_free_host", "pcb_add_arrivals", "pcb_set_stop_level", "pcb_pending_arrivals", "pcb_set_prism_load",
     "pcb_route_scatter_cells", "pcb_plan_owners", "pcb_cull_lod",
     "pcb_add_points_device_batched", "pcb_write_metadata", "pcb_get_config", "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
@@ -60,7 +60,7 @@ class PcbNodeInfo(C.Structure):
 
 
 class PcbArrivals(C.Structure):
-    _fields_ = [("level", C.c_uint32), ("reserved", C.c_uint32), ("n", C.c_uint64), ("ncell", C.c_uint64),
+    _fields_ = [("level", C.c_uint32), ("prism_load", C.c_float), ("n", C.c_uint64), ("ncell", C.c_uint64),
                 ("d_pts", C.c_void_p), ("d_batch_plus1", C.c_void_p), ("d_cell_start", C.c_void_p),
                 ("d_cell_idx", C.c_void_p)]
 
@@ -112,6 +112,7 @@ def load_library():
     L.pcb_add_arrivals.argtypes = [vp, C.c_uint32, vp, vp, C.c_uint64, vp, vp, C.c_uint64, C.POINTER(C.c_float), C.c_uint64]
     L.pcb_set_stop_level.argtypes = [vp, C.c_uint32]
     L.pcb_pending_arrivals.argtypes = [vp, C.POINTER(PcbArrivals)]
+    L.pcb_set_prism_load.argtypes = [vp, C.c_float]
     L.pcb_route_scatter_cells.argtypes = [C.c_int, vp, vp, C.c_uint64, C.c_uint64, C.c_uint32, C.c_float, C.POINTER(C.c_int32),
                                           C.POINTER(C.c_uint32), vp, vp, C.c_uint32, C.POINTER(C.c_uint64),
                                           C.POINTER(C.c_uint64), vp]
@@ -206,6 +207,10 @@ class Converter:
         box = (C.c_float * 6)(*[float(v) for v in bbox6]) if bbox6 is not None else None
         self._check(self._L.pcb_add_arrivals(self._h, level, C.c_void_p(pts_ptr), C.c_void_p(bat_ptr), n,
                                              C.c_void_p(cell_start_ptr), C.c_void_p(cell_idx_ptr), ncell, box, count_points))
+
+    def set_prism_load(self, v: float):
+        """Record-filter hint that travels with pending arrivals (PcbArrivals.prism_load)."""
+        self._check(self._L.pcb_set_prism_load(self._h, float(v)))
 
     def set_stop_level(self, level: int):
         """finish() builds the levels < level only; pending() then describes the arrivals of `level`."""

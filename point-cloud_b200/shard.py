@@ -444,6 +444,8 @@ def add_arrivals_to(cv, arr):
     cv.add_arrivals(arr["level"], arr["pts"].data_ptr() if arr["n"] else 0, arr["bat"].data_ptr() if arr["n"] else 0,
                     arr["n"], arr["cell_start"].data_ptr() if arr["n"] else 0, arr["cell_idx"].data_ptr() if arr["n"] else 0,
                     arr["ncell"], arr.get("bbox"), arr.get("count_points", 0))
+    if arr.get("prism_load"):
+        cv.set_prism_load(arr["prism_load"])
 
 
 def route_cells_emulated(pcb, slices: List[torch.Tensor], batch_size: int, max_cell_size: float):
@@ -513,7 +515,7 @@ def pending_to_arrivals(cv, dev):
     return {"level": int(p.level), "n": n, "ncell": ncell,
             "pts": view(p.d_pts, 16 * n, torch.uint8).view(n, 16) if n else torch.zeros((0, 16), dtype=torch.uint8, device=dev),
             "bat": view(p.d_batch_plus1, 4 * n, torch.int32), "cell_start": view(p.d_cell_start, 4 * (ncell + 1) if n else 0, torch.int32),
-            "cell_idx": view(p.d_cell_idx, 12 * ncell, torch.int32), "count_points": 0}
+            "cell_idx": view(p.d_cell_idx, 12 * ncell, torch.int32), "count_points": 0, "prism_load": float(p.prism_load)}
 
 
 def _from_ptr(ptr, nbytes, dev):
@@ -569,7 +571,7 @@ def rebalance_emulated(pcb, arrs):
         ci = torch.cat(idx)[torch.from_numpy(np.nonzero(keep)[0]).to(dev)].contiguous()
         out.append({"level": level, "pts": torch.cat(pts).contiguous(), "bat": torch.cat(bat).contiguous(), "n": int(cnt.sum()),
                     "cell_start": torch.from_numpy(cs).to(dev), "cell_idx": ci.view(-1), "ncell": int(keep.sum()),
-                    "count_points": 0})
+                    "count_points": 0, "prism_load": max(float(a.get("prism_load", 0.0)) for a in arrs)})
     return out
 
 
@@ -597,6 +599,8 @@ def rebalance(pcb, arr, group=None):
     offs = np.cumsum([0] + [len(c) for c in counts])
     lv = torch.tensor([arr["level"] if arr["n"] else 0], dtype=torch.int64, device=dev)   # ranks without arrivals do not know it
     dist.all_reduce(lv, op=dist.ReduceOp.MAX, group=group)
+    hint = torch.tensor([float(arr.get("prism_load", 0.0))], dtype=torch.float32, device=dev)   # record-filter hint
+    dist.all_reduce(hint, op=dist.ReduceOp.MAX, group=group)
     arr = dict(arr, level=int(lv.item()))
     split = _split_for_owners(arr, owners[offs[rank]:offs[rank + 1]], world)
     gather = torch.cat([s[0] for s in split])
@@ -627,7 +631,7 @@ def rebalance(pcb, arr, group=None):
     cs = np.concatenate([[0], np.cumsum(cnt[keep])]).astype(np.int32)
     return {"level": arr["level"], "pts": recv_pts, "bat": recv_bat, "n": m, "cell_start": torch.from_numpy(cs).to(dev),
             "cell_idx": recv_idx[torch.from_numpy(np.nonzero(keep)[0]).to(dev)].contiguous().view(-1), "ncell": int(keep.sum()),
-            "count_points": 0, "moved_bytes": 20 * (sum(ins) - ins[rank])}
+            "count_points": 0, "moved_bytes": 20 * (sum(ins) - ins[rank]), "prism_load": float(hint.item())}
 
 
 class ShardedBuild:
@@ -724,7 +728,7 @@ class ShardedBuild:
                     mx, mean, big, total = self._level_stats(arr, dev)
                     unbalanced = total > 0 and mx > 1.10 * mean
                     go_deeper = unbalanced and big > total / (4.0 * world) and level < self.max_level
-                    do_rebalance = unbalanced and not go_deeper and level > 0
+                    do_rebalance = unbalanced and not go_deeper and level > 0 and big <= total / world
                 elif want == "off":
                     do_rebalance = False
                 else:

@@ -131,3 +131,36 @@ def test_oracle_at_size():
         assert mj == o.meta_json, name
         compare_trees(o.nodes, nodes, f"oracle-{name}", f"gpu-{name}")
         del nodes, o, pts
+
+
+@pytest.mark.timeout(900)
+def test_partial_build_at_size_equals_single_build():
+    """pcb_set_stop_level / pcb_add_arrivals at a size where the record filter engages in the resumed handle (it gets the
+    arrivals-per-prism hint with the pending arrivals): 12 M-point unit cube, levels 0-2 on one handle, the rest on a
+    second one - the union of the node files equals the single-handle build byte for byte (which test_oracle_at_size pins
+    against the oracle at this shape)."""
+    import importlib.util
+    import torch
+    import synth
+    spec = importlib.util.spec_from_file_location("pcb_shard", ROOT / "point-cloud_b200" / "shard.py")
+    shard = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(shard)
+    pcb = load_pcb()
+    pts = synth.uniform_cube(12_000_000, 7, "cuda").cpu().numpy()
+    whole, mj, st, _ = pcb.convert([pts])
+    dev = torch.device("cuda", 0)
+    with pcb.Converter(None, device=0) as top:
+        top.begin_file()
+        top.add_points(pts)
+        top.set_stop_level(3)
+        st_top = top.finish()
+        nodes = dict(top.nodes())
+        pend = shard.pending_to_arrivals(top, dev)
+        assert pend["level"] == 3 and pend["prism_load"] > 64.0     # the chain levels are what the record filter is for
+        with pcb.Converter(None, device=0) as low:
+            shard.add_arrivals_to(low, pend)
+            st_low = low.finish()
+            nodes.update(low.nodes())
+    assert nodes.keys() == whole.keys()
+    assert all(nodes[k] == whole[k] for k in whole)
+    assert st_top.arrivals + st_low.arrivals == st.arrivals and max(st_top.hierarchies, st_low.hierarchies) == st.hierarchies
