@@ -702,11 +702,23 @@ class ShardedBuild:
         """src: this rank's slice of the undivided stream ((n, 16) uint8 on the device).  Returns a namespace with the
         summed statistics of this rank's handles."""
         from types import SimpleNamespace
+        import time as _time
         pcb = self.pcb
         dev = src.device
+        trace = os.environ.get("PCB_SHARD_TRACE") is not None   # debugging aid: synchronises between the phases
+        phases = {}
+        t_mark = [_time.perf_counter()]
+
+        def mark(name):
+            if trace:
+                torch.cuda.synchronize(dev)
+                now = _time.perf_counter()
+                phases[name] = phases.get(name, 0.0) + (now - t_mark[0]) * 1e3
+                t_mark[0] = now
         world = dist.get_world_size(self.group)
         launches = 0
         arr = route_cells(pcb, src, first_index, self.bs, self.S0, group=self.group, stream=self.stream)
+        mark("route")
         stats = []
         if arr is None:   # general path: stream-ordered points + batch ordinals, the owner splits by level-0 cell itself
             rp, rb, info = route_device(pcb, src, first_index, self.bs, self.S0, group=self.group, stream=self.stream)
@@ -741,13 +753,16 @@ class ShardedBuild:
                 add_arrivals_to(cv, arr)
                 cv.set_stop_level(level + 1)
                 stats.append(cv.finish())
+                mark("partial_levels")
                 if prev is not None:
                     self._retire(prev)                  # its pending arrivals (this level's input) are consumed
+                mark("retire")
                 arr = pending_to_arrivals(cv, dev)
                 arr["level"] = level + 1
                 level += 1
             if do_rebalance:
                 arr = rebalance(pcb, arr, group=self.group)
+                mark("rebalance")
                 if self.handles:
                     self._retire(self.handles[-1])      # the re-balanced arrivals are copies
                 self._keep.append(arr)
@@ -756,7 +771,10 @@ class ShardedBuild:
             cv = self._open()
             add_arrivals_to(cv, arr)
             stats.append(cv.finish())
+            mark("final_build")
             self.info["build_arrivals_after_cut"] = int(stats[-1].arrivals)
+            if trace:
+                self.info["phases_ms"] = {k: round(v, 2) for k, v in phases.items()}
         ks = {k: dict(v) for k, v in self._kstats.items()}
         for cv in self.handles:
             for k in cv.kernel_stats():
