@@ -22,6 +22,7 @@ caller initialised (NCCL over NVLink on the GPU box, gloo in the CPU tests of th
 from __future__ import annotations
 
 import os
+import sys
 
 from typing import List, Optional, Tuple
 
@@ -580,9 +581,19 @@ def rebalance(pcb, arr, group=None):
     greedy plan on every rank (pcb_plan_owners) -> ONE all-to-all-v of the point records and one of their batch ordinals.
     Returns this rank's new arrivals dict."""
     import numpy as np
+    import time as _time
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     dev = arr["pts"].device
+    trace = os.environ.get("PCB_SHARD_TRACE") is not None and dev.type == "cuda"
+    ph, t0 = {}, [_time.perf_counter()]
+
+    def mark(name):
+        if trace:
+            torch.cuda.synchronize(dev)
+            now = _time.perf_counter()
+            ph[name] = round((now - t0[0]) * 1e3, 2)
+            t0[0] = now
     mine = np.diff(arr["cell_start"].cpu().numpy().astype(np.int64)) if arr["n"] else np.zeros(0, dtype=np.int64)
     ncs = torch.zeros(world, dtype=torch.int64, device=dev)
     nc = torch.tensor([len(mine)], dtype=torch.int64, device=dev)
@@ -595,8 +606,10 @@ def rebalance(pcb, arr, group=None):
     dist.all_gather_into_tensor(allc, pad, group=group)
     allc = allc.view(world, cap).cpu().numpy()
     counts = [allc[r, :ncs[r]] for r in range(world)]
+    mark("tables")
     owners = pcb.plan_owners(np.concatenate(counts), world)
     offs = np.cumsum([0] + [len(c) for c in counts])
+    mark("plan")
     lv = torch.tensor([arr["level"] if arr["n"] else 0], dtype=torch.int64, device=dev)   # ranks without arrivals do not know it
     dist.all_reduce(lv, op=dist.ReduceOp.MAX, group=group)
     hint = torch.tensor([float(arr.get("prism_load", 0.0))], dtype=torch.float32, device=dev)   # record-filter hint
@@ -608,6 +621,7 @@ def rebalance(pcb, arr, group=None):
     send_pts = arr["pts"].view(torch.int64).view(-1, 2)[gather].view(torch.uint8).view(-1, 16) if arr["n"] else arr["pts"]
     send_bat = arr["bat"][gather].contiguous() if arr["n"] else arr["bat"]
     ins = [int(s[1].sum()) for s in split]
+    mark("gather")
     # what every source sends to me: from the global table (no second count exchange)
     outs, cnt_in, idx_send = [], [], []
     for r in range(world):
@@ -619,6 +633,7 @@ def rebalance(pcb, arr, group=None):
     recv_bat = torch.empty((m,), dtype=torch.int32, device=dev)
     dist.all_to_all_single(recv_pts, send_pts, outs, ins, group=group)
     dist.all_to_all_single(recv_bat, send_bat, outs, ins, group=group)
+    mark("all_to_all")
     # cell indices of the cells I receive: the senders' index triples, exchanged the same way
     ci = arr["cell_idx"].view(-1, 3)
     send_idx = torch.cat([ci[torch.from_numpy(s[2]).to(dev)] for s in split]).contiguous() if len(mine) else ci
@@ -629,6 +644,9 @@ def rebalance(pcb, arr, group=None):
     cnt = np.concatenate(cnt_in) if cnt_in else np.zeros(0, dtype=np.int64)
     keep = cnt > 0
     cs = np.concatenate([[0], np.cumsum(cnt[keep])]).astype(np.int32)
+    mark("csr")
+    if trace and rank == 0:
+        print(f"[rebalance] {ph}", file=sys.stderr, flush=True)
     return {"level": arr["level"], "pts": recv_pts, "bat": recv_bat, "n": m, "cell_start": torch.from_numpy(cs).to(dev),
             "cell_idx": recv_idx[torch.from_numpy(np.nonzero(keep)[0]).to(dev)].contiguous().view(-1), "ncell": int(keep.sum()),
             "count_points": 0, "moved_bytes": 20 * (sum(ins) - ins[rank]), "prism_load": float(hint.item())}
