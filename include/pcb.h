@@ -227,6 +227,12 @@ int pcb_route_scatter_cells(int device, void* stream, const pcb_point* d_pts, ui
                             uint32_t batch_size, float max_cell_size, const int32_t origin[3], const uint32_t dims[3],
                             const uint8_t* d_owner, const uint32_t* d_dst_base, uint32_t world,
                             const uint64_t* recv_pts_ptrs, const uint64_t* recv_batch_ptrs, uint32_t* d_err);
+/* Level-l re-balance: packs whole cells of one level's arrivals (pcb_pending_arrivals) into a send buffer.  d_sel[k] =
+   source cell of output cell k, d_out_start[nsel + 1] = CSR of the output; `total` = d_out_start[nsel].  16 + 4 bytes per
+   arrival, one coalesced pass.  No reference counterpart (the reference is single-process). */
+int pcb_gather_cells(int device, void* stream, const pcb_point* d_pts, const uint32_t* d_batch, const uint32_t* d_cell_start,
+                     const uint32_t* d_sel, const uint32_t* d_out_start, uint32_t nsel, uint64_t total, pcb_point* d_out_pts,
+                     uint32_t* d_out_batch);
 /* Deterministic greedy owner plan (largest cell first onto the least loaded rank; host arrays): owner[i] for every
    cell ordinal i of the histogram `counts`.  A pure function of the global histogram: every rank computes the same. */
 int pcb_plan_owners(const uint64_t* counts, uint64_t ncells, uint32_t world, uint8_t* owner);

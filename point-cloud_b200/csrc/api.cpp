@@ -36,6 +36,9 @@ int route_scatter_cells(int device, void* stream, const pcb_point* d_pts, uint64
                         float S0, const int32_t origin[3], const uint32_t dims[3], const uint8_t* d_owner,
                         const uint32_t* d_dst_base, uint32_t world, const uint64_t* recv_pts_ptrs,
                         const uint64_t* recv_batch_ptrs, uint32_t* d_err);
+int gather_cells(int device, void* stream, const pcb_point* d_pts, const uint32_t* d_bat, const uint32_t* d_cell_start,
+                 const uint32_t* d_sel, const uint32_t* d_out_start, uint32_t nsel, uint64_t total, pcb_point* d_out_pts,
+                 uint32_t* d_out_bat);
 void plan_owners(const uint64_t* counts, uint64_t ncells, uint32_t world, uint8_t* owner);
 int route_bbox_static(int device, void* stream, const pcb_point* d_pts, uint64_t n, float S0, float* d_out6, uint32_t* d_err);
 int route_scatter(int device, void* stream, const pcb_point* d_pts, uint64_t n, uint64_t first_index, uint32_t batch_size,
@@ -340,6 +343,14 @@ int pcb_route_scatter_cells(int device, void* stream, const pcb_point* d_pts, ui
     if (!origin || !dims || !d_owner || !d_dst_base || !recv_pts_ptrs || !recv_batch_ptrs || (n && !d_pts)) return PCB_ERR_ARG;
     PCB_ROUTE_GUARD(pcb::route_scatter_cells(device, stream, d_pts, n, first_index, batch_size, max_cell_size, origin, dims,
                                              d_owner, d_dst_base, world, recv_pts_ptrs, recv_batch_ptrs, d_err))
+}
+
+int pcb_gather_cells(int device, void* stream, const pcb_point* d_pts, const uint32_t* d_batch, const uint32_t* d_cell_start,
+                     const uint32_t* d_sel, const uint32_t* d_out_start, uint32_t nsel, uint64_t total, pcb_point* d_out_pts,
+                     uint32_t* d_out_batch) {
+    if (nsel && total && (!d_pts || !d_batch || !d_cell_start || !d_sel || !d_out_start || !d_out_pts || !d_out_batch)) return PCB_ERR_ARG;
+    PCB_ROUTE_GUARD(pcb::gather_cells(device, stream, d_pts, d_batch, d_cell_start, d_sel, d_out_start, nsel, total, d_out_pts,
+                                      d_out_batch))
 }
 
 int pcb_plan_owners(const uint64_t* counts, uint64_t ncells, uint32_t world, uint8_t* owner) {

@@ -1602,6 +1602,22 @@ int route_scatter_cells(int device, void* stream, const pcb_point* d_pts, uint64
     });
 }
 
+// Level-l re-balance: copy the selected cells of one level's arrivals back to back (the all-to-all send buffer).
+int gather_cells(int device, void* stream, const pcb_point* d_pts, const uint32_t* d_bat, const uint32_t* d_cell_start,
+                 const uint32_t* d_sel, const uint32_t* d_out_start, uint32_t nsel, uint64_t total, pcb_point* d_out_pts,
+                 uint32_t* d_out_bat) {
+    return guarded([&] {
+        CUDA_TRY(cudaSetDevice(device));
+        if (!nsel || !total) return 0;
+        if (total >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "more than 2^30-1 arrivals on one device"};
+        const u32 grid = (u32)std::min<u64>(148 * 8, (total + 255) / 256);
+        k_gather_cells<<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)d_pts, d_bat, d_cell_start, d_sel, d_out_start, nsel,
+                                                               (uint4*)d_out_pts, d_out_bat);
+        CUDA_TRY(cudaGetLastError());
+        return 1;
+    });
+}
+
 // Deterministic greedy bin packing of cells onto ranks: largest cell first (ties: lower cell ordinal), onto the least
 // loaded rank (ties: lower rank).  A pure function of the global histogram, so every rank computes the same plan.
 void plan_owners(const uint64_t* counts, uint64_t ncells, uint32_t world, uint8_t* owner) {

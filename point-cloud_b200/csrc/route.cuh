@@ -258,3 +258,24 @@ k_route_split(const PcbPoint* __restrict__ pts, u32 n, float S0, L0Box box, cons
         db[g] = s_bat[j];
     }
 }
+
+// ---- level-l re-balance: pack whole cells into the all-to-all send buffer ---------------------------------------------
+// Selected cells sel[0 .. nsel) of the source arrivals (CSR cs) are copied back to back: output element j belongs to
+// selected cell k = the segment of out_start containing j and comes from source element cs[sel[k]] + (j - out_start[k]).
+// One binary search per warp, then a walk (cells are thousands of elements long); 16 + 4 bytes per element, coalesced.
+__global__ void __launch_bounds__(256)
+k_gather_cells(const uint4* __restrict__ pts, const u32* __restrict__ bat, const u32* __restrict__ cs,
+               const u32* __restrict__ sel, const u32* __restrict__ out_start /* [nsel + 1] */, u32 nsel,
+               uint4* __restrict__ out_pts, u32* __restrict__ out_bat) {
+    const u32 total = __ldg(out_start + nsel);
+    for (u64 j0 = ((u64)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; j0 < total; j0 += (u64)gridDim.x * blockDim.x) {
+        const u64 j = j0 + (threadIdx.x & 31);
+        u32 k = find_segment(out_start, nsel, (u32)j0);
+        if (j < total) {
+            while (__ldg(out_start + k + 1) <= (u32)j) k++;
+            const u32 src = __ldg(cs + __ldg(sel + k)) + ((u32)j - __ldg(out_start + k));
+            out_pts[j] = __ldg(pts + src);
+            out_bat[j] = __ldg(bat + src);
+        }
+    }
+}

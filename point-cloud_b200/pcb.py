@@ -31,7 +31,7 @@ EXPORTS = [
     "pcb_add_points_device", "pcb_finish", "pcb_close", "pcb_trim_host_cache", "pcb_last_error", "pcb_node_count", "pcb_node_get",
     "pcb_route_bbox", "pcb_route_bbox_static", "pcb_route_histogram", "pcb_route_pack", "pcb_route_scatter",
     "pcb_add_las_records", "pcb_alloc_host", "pcb_free_host", "pcb_add_arrivals", "pcb_set_stop_level", "pcb_pending_arrivals", "pcb_set_prism_load",
-    "pcb_route_scatter_cells", "pcb_plan_owners", "pcb_cull_lod",
+    "pcb_route_scatter_cells", "pcb_plan_owners", "pcb_cull_lod", "pcb_gather_cells",
     "pcb_add_points_device_batched", "pcb_write_metadata", "pcb_get_config", "pcb_metadata_json", "pcb_kernel_stat_count", "pcb_kernel_stat_get", "pcb_version", "pcb_device_count",
 ]
 
@@ -117,6 +117,7 @@ def load_library():
                                           C.POINTER(C.c_uint32), vp, vp, C.c_uint32, C.POINTER(C.c_uint64),
                                           C.POINTER(C.c_uint64), vp]
     L.pcb_plan_owners.argtypes = [vp, C.c_uint64, C.c_uint32, vp]
+    L.pcb_gather_cells.argtypes = [C.c_int, vp, vp, vp, vp, vp, vp, C.c_uint32, C.c_uint64, vp, vp]
     L.pcb_cull_lod.argtypes = [C.c_int, vp, C.POINTER(PcbCullParams), vp, vp, C.c_uint32, vp, vp, vp, C.c_uint64, vp, vp]
     L.pcb_add_las_records.argtypes = [vp, vp, C.c_uint64, C.c_uint32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.pcb_alloc_host.argtypes = [C.c_uint64]
@@ -341,6 +342,13 @@ def route_scatter_cells(device, stream, pts_ptr, n, first_index, batch_size, max
                                                                batch_size, max_cell_size, o, d, C.c_void_p(owner_ptr),
                                                                C.c_void_p(dst_base_ptr), world, pp, pb,
                                                                C.c_void_p(err_ptr) if err_ptr else None))
+
+
+def gather_cells(device, stream, pts_ptr, bat_ptr, cell_start_ptr, sel_ptr, out_start_ptr, nsel, total, out_pts_ptr, out_bat_ptr):
+    """pcb_gather_cells: selected cells of one level's arrivals packed back to back (level-l re-balance)."""
+    return _route_check(load_library().pcb_gather_cells(device, C.c_void_p(stream), C.c_void_p(pts_ptr), C.c_void_p(bat_ptr),
+                                                        C.c_void_p(cell_start_ptr), C.c_void_p(sel_ptr), C.c_void_p(out_start_ptr),
+                                                        nsel, total, C.c_void_p(out_pts_ptr), C.c_void_p(out_bat_ptr)))
 
 
 def plan_owners(counts, world: int) -> np.ndarray:

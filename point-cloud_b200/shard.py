@@ -529,25 +529,42 @@ def _from_ptr(ptr, nbytes, dev):
 
 
 def _split_for_owners(arr, owners, world):
-    """arr: arrivals dict of this rank; owners: new owner per local cell (numpy).  Returns per destination the arrival
-    gather index (device int64) and the cell counts (numpy int64), cells in local order."""
+    """arr: arrivals dict of this rank; owners: new owner per local cell (numpy).  Returns per destination (cell counts,
+    local cell ordinals), cells in local order."""
     import numpy as np
-    dev = arr["pts"].device
     cs = arr["cell_start"].cpu().numpy().astype(np.int64) if arr["n"] else np.zeros(1, dtype=np.int64)
     lens = np.diff(cs)
     out = []
     for o in range(world):
         sel = np.nonzero(owners == o)[0]
-        cnt = lens[sel]
-        if cnt.sum() == 0:
-            out.append((torch.zeros(0, dtype=torch.int64, device=dev), cnt, sel))
-            continue
-        starts = torch.from_numpy(cs[sel]).to(dev)
-        ln = torch.from_numpy(cnt).to(dev)
-        off = torch.cumsum(ln, 0) - ln
-        idx = torch.arange(int(cnt.sum()), device=dev) + torch.repeat_interleave(starts - off, ln)
-        out.append((idx, cnt, sel))
+        out.append((lens[sel], sel))
     return out
+
+
+def _pack_cells(pcb, arr, split):
+    """The all-to-all send buffer of this rank: the cells for destination 0, then 1, ... back to back (points, batch
+    ordinals) and the element count per destination.  On the GPU one pass of pcb_gather_cells; torch indexing on the CPU
+    (gloo tests)."""
+    import numpy as np
+    dev = arr["pts"].device
+    sel = np.concatenate([s[1] for s in split]).astype(np.int64) if split else np.zeros(0, dtype=np.int64)
+    cnt = np.concatenate([s[0] for s in split]).astype(np.int64) if split else np.zeros(0, dtype=np.int64)
+    ins = [int(s[0].sum()) for s in split]
+    total = int(cnt.sum())
+    if total == 0:
+        return arr["pts"][:0], arr["bat"][:0], ins
+    out_start = np.concatenate([[0], np.cumsum(cnt)])
+    if dev.type == "cuda":
+        tab = torch.from_numpy(np.concatenate([sel, out_start]).astype(np.uint32).view(np.int32).copy()).to(dev)
+        out_p = torch.empty((total, 16), dtype=torch.uint8, device=dev)
+        out_b = torch.empty((total,), dtype=torch.int32, device=dev)
+        pcb.gather_cells(dev.index, torch.cuda.current_stream(dev).cuda_stream, arr["pts"].data_ptr(), arr["bat"].data_ptr(),
+                         arr["cell_start"].data_ptr(), tab.data_ptr(), tab[len(sel):].data_ptr(), len(sel), total,
+                         out_p.data_ptr(), out_b.data_ptr())
+        return out_p, out_b, ins
+    cs = arr["cell_start"].numpy().astype(np.int64)
+    idx = torch.from_numpy(np.concatenate([np.arange(cs[c], cs[c + 1]) for c in sel]) if len(sel) else np.zeros(0, dtype=np.int64))
+    return arr["pts"][idx].contiguous(), arr["bat"][idx].contiguous(), ins
 
 
 def rebalance_emulated(pcb, arrs):
@@ -561,12 +578,17 @@ def rebalance_emulated(pcb, arrs):
     owners = pcb.plan_owners(np.concatenate(counts) if counts else np.zeros(0), world)
     offs = np.cumsum([0] + [len(c) for c in counts])
     splits = [_split_for_owners(arrs[r], owners[offs[r]:offs[r + 1]], world) for r in range(world)]
+    packed = [_pack_cells(pcb, arrs[r], splits[r]) for r in range(world)]
     out = []
     for o in range(world):
-        pts = [arrs[r]["pts"][splits[r][o][0]] for r in range(world)]
-        bat = [arrs[r]["bat"][splits[r][o][0]] for r in range(world)]
-        cnt = np.concatenate([splits[r][o][1] for r in range(world)])
-        idx = [arrs[r]["cell_idx"].view(-1, 3)[torch.from_numpy(splits[r][o][2]).to(dev)] for r in range(world)]
+        pts, bat = [], []
+        for r in range(world):
+            sp, sb, ins = packed[r]
+            lo = sum(ins[:o])
+            pts.append(sp[lo:lo + ins[o]])
+            bat.append(sb[lo:lo + ins[o]])
+        cnt = np.concatenate([splits[r][o][0] for r in range(world)])
+        idx = [arrs[r]["cell_idx"].view(-1, 3)[torch.from_numpy(splits[r][o][1]).to(dev)] for r in range(world)]
         keep = cnt > 0
         cs = np.concatenate([[0], np.cumsum(cnt[keep])]).astype(np.int32)
         ci = torch.cat(idx)[torch.from_numpy(np.nonzero(keep)[0]).to(dev)].contiguous()
@@ -616,11 +638,7 @@ def rebalance(pcb, arr, group=None):
     dist.all_reduce(hint, op=dist.ReduceOp.MAX, group=group)
     arr = dict(arr, level=int(lv.item()))
     split = _split_for_owners(arr, owners[offs[rank]:offs[rank + 1]], world)
-    gather = torch.cat([s[0] for s in split])
-    # (16-byte records gathered as two 8-byte words: torch's row gather of 16 x u8 is an order of magnitude slower)
-    send_pts = arr["pts"].view(torch.int64).view(-1, 2)[gather].view(torch.uint8).view(-1, 16) if arr["n"] else arr["pts"]
-    send_bat = arr["bat"][gather].contiguous() if arr["n"] else arr["bat"]
-    ins = [int(s[1].sum()) for s in split]
+    send_pts, send_bat, ins = _pack_cells(pcb, arr, split)
     mark("gather")
     # what every source sends to me: from the global table (no second count exchange)
     outs, cnt_in, idx_send = [], [], []
@@ -636,8 +654,8 @@ def rebalance(pcb, arr, group=None):
     mark("all_to_all")
     # cell indices of the cells I receive: the senders' index triples, exchanged the same way
     ci = arr["cell_idx"].view(-1, 3)
-    send_idx = torch.cat([ci[torch.from_numpy(s[2]).to(dev)] for s in split]).contiguous() if len(mine) else ci
-    ins_c = [len(s[2]) for s in split]
+    send_idx = torch.cat([ci[torch.from_numpy(s[1]).to(dev)] for s in split]).contiguous() if len(mine) else ci
+    ins_c = [len(s[1]) for s in split]
     outs_c = [len(c) for c in cnt_in]
     recv_idx = torch.empty((int(sum(outs_c)), 3), dtype=torch.int32, device=dev)
     dist.all_to_all_single(recv_idx, send_idx, outs_c, ins_c, group=group)
