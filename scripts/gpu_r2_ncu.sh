@@ -15,3 +15,6 @@ for w in blobs cube; do
   rm -f gpurun_out/r02_${w}_scans.ncu-rep
 done
 ls -la gpurun_out | tail -12
+# compute-sanitizer logs of small conversions through every sort path (memcheck always; racecheck bounded by a timeout)
+timeout 600 compute-sanitizer --tool memcheck --log-file gpurun_out/r02_sanitizer_memcheck.txt python scripts/gpu_sanitize.py > gpurun_out/sanitize_mem.log 2>&1; echo "memcheck rc=$?"; tail -3 gpurun_out/r02_sanitizer_memcheck.txt
+timeout 900 compute-sanitizer --tool racecheck --log-file gpurun_out/r02_sanitizer_racecheck.txt python scripts/gpu_sanitize.py > gpurun_out/sanitize_race.log 2>&1; echo "racecheck rc=$?"; tail -3 gpurun_out/r02_sanitizer_racecheck.txt
