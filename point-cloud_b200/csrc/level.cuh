@@ -1165,6 +1165,201 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
             if (base + k < n) op.rank[base + k] = rk[k];
     }
 }
+// Same scan with the per-item work cut to 32-bit register arithmetic (the kernel above issues ~96 instructions per
+// arrival: ncu, profiles/r02_ncu_full_cube_octscan.txt).  A thread's sixteen arrivals are counted ONCE, before the scan,
+// in eight 8-bit counters (two registers); the rank of an arrival inside its thread (< 16) is kept in four bits, and
+// after the look-back an arrival's rank is   4-bit local rank + (thread's start value of its octant, unless a cell
+// started inside the thread before it)   - one read-only shared-memory load instead of a load / store chain.
+// Inside the warp and the block the counters travel as four registers of two 16-bit fields; bit 31 of the fourth
+// is the "a cell starts in the range" flag, which the segmented combine (b.head ? b : a + b) carries along for free.
+struct OctW4 {
+    u32 w[4];   // octants (0,1) (2,3) (4,5) (6,7), 16 bits each; bit 31 of w[3]: head
+};
+#define OCT_HEAD_BIT 0x80000000u
+__device__ __forceinline__ OctW4 octw_combine(const OctW4& a, const OctW4& b) {
+    const bool cut = (b.w[3] & OCT_HEAD_BIT) != 0u;
+    OctW4 r;
+#pragma unroll
+    for (int q = 0; q < 4; q++) r.w[q] = cut ? b.w[q] : a.w[q] + b.w[q];
+    return r;
+}
+__device__ __forceinline__ u32 octw_field(const OctW4& a, int oct) { return (a.w[oct >> 1] >> (16 * (oct & 1))) & 0x1FFFu; }
+// one arrival into the byte counters (lo: octants 0-3, hi: 4-7); returns the count of its octant before it
+__device__ __forceinline__ u32 oct_bytes_step(u32 code, u32& lo, u32& hi, u32& started) {
+    if (code & 0x200u) { lo = 0u; hi = 0u; started = 1u; }   // PCB_EM_CELL_FIRST >> 32
+    const u32 o = code & 0xFu, sel = o & 3u;
+    const u32 r = __byte_perm((o & 4u) ? hi : lo, 0u, 0x4440u | sel);
+    const u32 one = 1u << (8u * sel);
+    lo += (o < 4u) ? one : 0u;
+    hi += (o & 4u) ? one : 0u;
+    return r;   // meaningless for octant 8 (no emission)
+}
+// XPOSE: a thread owns sixteen CONSECUTIVE arrivals (the scan wants that), so loading them directly makes every warp
+// load touch 32 different 128-byte lines (and every rank store 16).  With XPOSE the warp loads its 512 records with
+// coalesced 16-byte loads, keeps the 16-bit codes in shared memory (padded: conflict-free both ways) and every thread
+// picks up its sixteen codes with two 16-byte shared loads; the ranks take the same way back.
+template <int OCT_THREADS, bool XPOSE, int MINB>
+__global__ void __launch_bounds__(OCT_THREADS, MINB)
+k_octscan2(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
+    constexpr int OCT_ITEMS = 16;
+    constexpr int WARPS = OCT_THREADS / 32;
+    constexpr int OCT_TILE = OCT_THREADS * OCT_ITEMS;
+    static_assert(OCT_TILE <= OCT_TILE_MAX, "16-bit fields hold a whole tile");
+    __shared__ uint4 s_warp[WARPS];
+    __shared__ Oct8 s_prefix;
+    __shared__ __align__(16) u32 s_run[9][OCT_THREADS];   // XPOSE: first the code transpose, 288 words per warp
+    __shared__ __align__(16) u32 s_out[XPOSE ? WARPS * 576 : 4];
+    static_assert(9 * OCT_THREADS >= WARPS * 288, "code transpose fits the counter columns");
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const u32 tile = blockIdx.x;   // see k_chain_scan
+    const u64 base = (u64)tile * OCT_TILE + (u64)tid * OCT_ITEMS;
+    const u64 wbase = (u64)tile * OCT_TILE + (u64)warp * (32 * OCT_ITEMS);
+    const bool whole = base + OCT_ITEMS <= n;
+
+    // per element: high word of the emission record = octant (8 = none) | last << 8 | first << 9
+    // (two 16-bit codes per register: the sixteen codes stay live across both barriers)
+    u32 cw[OCT_ITEMS / 2];
+#define OCT_CODE(k) (((k) & 1) ? cw[(k) >> 1] >> 16 : cw[(k) >> 1] & 0xFFFFu)
+    if (XPOSE) {
+        u32* wcode = &s_run[0][0] + warp * 288;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const u64 e0 = wbase + (u64)(j * 64 + 2 * lane);
+            u32 c0 = PCB_EM_NONE_OCT, c1 = PCB_EM_NONE_OCT;
+            if (e0 + 1 < n) {
+                const ulonglong2 e = *(const ulonglong2*)(op.em + e0);
+                c0 = (u32)(e.x >> 32);
+                c1 = (u32)(e.y >> 32);
+            } else if (e0 < n) {
+                c0 = (u32)(op.em[e0] >> 32);
+            }
+            wcode[j * 36 + lane] = (c0 & 0xFFFFu) | (c1 << 16);   // word i = records 2i, 2i+1; 4 words of padding per 32
+        }
+        __syncwarp();
+        const uint4 a = *(const uint4*)(wcode + lane * 8 + (lane >> 2) * 4), b = *(const uint4*)(wcode + lane * 8 + (lane >> 2) * 4 + 4);
+        cw[0] = a.x; cw[1] = a.y; cw[2] = a.z; cw[3] = a.w;
+        cw[4] = b.x; cw[5] = b.y; cw[6] = b.z; cw[7] = b.w;
+    } else if (whole) {
+        const ulonglong2* src = (const ulonglong2*)(op.em + base);
+#pragma unroll
+        for (int k = 0; k < OCT_ITEMS / 2; k++) {
+            const ulonglong2 e = src[k];
+            cw[k] = ((u32)(e.x >> 32) & 0xFFFFu) | ((u32)(e.y >> 32) << 16);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < OCT_ITEMS / 2; k++) {
+            const u32 c0 = (base + 2 * k < n) ? (u32)(op.em[base + 2 * k] >> 32) : PCB_EM_NONE_OCT;
+            const u32 c1 = (base + 2 * k + 1 < n) ? (u32)(op.em[base + 2 * k + 1] >> 32) : PCB_EM_NONE_OCT;
+            cw[k] = (c0 & 0xFFFFu) | (c1 << 16);
+        }
+    }
+    u32 lo = 0u, hi = 0u, started = 0u;
+#pragma unroll
+    for (int k = 0; k < OCT_ITEMS; k++) oct_bytes_step(OCT_CODE(k), lo, hi, started);
+    OctW4 winc;
+    winc.w[0] = __byte_perm(lo, 0u, 0x4140u);
+    winc.w[1] = __byte_perm(lo, 0u, 0x4342u);
+    winc.w[2] = __byte_perm(hi, 0u, 0x4140u);
+    winc.w[3] = __byte_perm(hi, 0u, 0x4342u) | (started ? OCT_HEAD_BIT : 0u);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        OctW4 up;
+#pragma unroll
+        for (int q = 0; q < 4; q++) up.w[q] = __shfl_up_sync(0xFFFFFFFFu, winc.w[q], d);
+        if (lane >= d) winc = octw_combine(up, winc);
+    }
+    if (lane == 31) s_warp[warp] = make_uint4(winc.w[0], winc.w[1], winc.w[2], winc.w[3]);
+    __syncthreads();
+    OctW4 wpre{{0u, 0u, 0u, 0u}}, total{{0u, 0u, 0u, 0u}};
+#pragma unroll
+    for (int w = 0; w < WARPS; w++) {
+        const uint4 v = s_warp[w];
+        const OctW4 sw{{v.x, v.y, v.z, v.w}};
+        if (w < warp) wpre = octw_combine(wpre, sw);
+        total = octw_combine(total, sw);
+    }
+    OctW4 texcl;
+#pragma unroll
+    for (int q = 0; q < 4; q++) texcl.w[q] = __shfl_up_sync(0xFFFFFFFFu, winc.w[q], 1);
+    if (lane == 0) texcl = OctW4{{0u, 0u, 0u, 0u}};
+    texcl = octw_combine(wpre, texcl);
+
+    if (warp == 0) {
+        Oct8 tot8;
+#pragma unroll
+        for (int q = 0; q < 8; q++) tot8.c[q] = octw_field(total, q);
+        tot8.head = total.w[3] >> 31;
+        Oct8 prefix = chain_lookback(op, desc, tile, tot8, op.err);
+        if (lane == 0) s_prefix = prefix;
+    }
+    __syncthreads();
+    // start values of this thread's eight counters: (tiles before) (+) (threads before inside the tile)
+    const bool tcut = (texcl.w[3] & OCT_HEAD_BIT) != 0u;
+#pragma unroll
+    for (int q = 0; q < 8; q++) s_run[q][tid] = (tcut ? 0u : s_prefix.c[q]) + octw_field(texcl, q);
+    s_run[8][tid] = 0u;
+    u32 rk[4];
+    lo = 0u; hi = 0u; started = 0u;   // the same count again, now with the start values known
+#pragma unroll
+    for (int k = 0; k < OCT_ITEMS; k++) {
+        const u32 code = OCT_CODE(k);
+        const u32 o = code & 0xFu;
+        const u32 start = s_run[o][tid];
+        const u32 local = oct_bytes_step(code, lo, hi, started);
+        u32 r = started ? local : start + local;
+        r = o < 8u ? r : 0u;
+        rk[k & 3] = r;
+        if ((k & 3) == 3) {
+            if (XPOSE) {   // word lane * 16 + k - 3 of the warp's 512, 4 words of padding per 32
+                *(uint4*)(s_out + warp * 576 + lane * 16 + (k - 3) + (lane >> 1) * 4) = make_uint4(rk[0], rk[1], rk[2], rk[3]);
+            } else if (whole) {
+                ((uint4*)(op.rank + base))[k >> 2] = make_uint4(rk[0], rk[1], rk[2], rk[3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if (base + (k - 3 + j) < n) op.rank[base + (k - 3 + j)] = rk[j];
+            }
+        }
+        u32 c = PCB_NONE;
+        if (o < 8u && (op.ex_state || r == 0u || r - (op.L - 1u) <= 1u)) {   // r == 0, L - 1 or L  (L >= 1)
+            const u32 i = (u32)(base + k);
+            c = find_segment(op.cell_start, op.ncell, i);
+            const u32 kk = 8 * c + o;
+            const u32 b = op.bat[i];
+            if (r == 0) op.special[4 * kk + 0] = b;
+            if (r + 1 == op.L) op.special[4 * kk + 1] = b;
+            if (r == op.L) op.special[4 * kk + 2] = b;
+            if (op.ex_state && op.ex_state[kk] == PCB_EX_SOME) {
+                u32 m0 = op.ex_m0[kk];
+                u32 want = (op.L >= 1 + m0) ? op.L - 1 - m0 : 0;
+                if (r == want) op.special[4 * kk + 3] = b;
+            }
+        }
+        if (code & 0x100u) {   // PCB_EM_CELL_LAST >> 32: bucket totals of the cell
+            if (c == PCB_NONE) c = find_segment(op.cell_start, op.ncell, (u32)(base + k));
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+                op.bcnt[8 * c + q] = (started ? 0u : s_run[q][tid]) + (((q < 4 ? lo : hi) >> (8 * (q & 3))) & 0xFFu);
+        }
+    }
+    if (XPOSE) {
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int i = j * 128 + lane * 4;
+            const uint4 v = *(const uint4*)(s_out + warp * 576 + i + (i >> 5) * 4);
+            const u64 e0 = wbase + (u64)i;
+            if (e0 + 4 <= n) {
+                *(uint4*)(op.rank + e0) = v;
+            } else {
+                if (e0 < n) op.rank[e0] = v.x;
+                if (e0 + 1 < n) op.rank[e0 + 1] = v.y;
+                if (e0 + 2 < n) op.rank[e0 + 2] = v.z;
+            }
+        }
+    }
+}
 template <int T, int I>
 static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
     const u32 ntiles = div_up(n, T * I);
@@ -1173,11 +1368,25 @@ static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStr
     k_octscan<T, I><<<ntiles, T, 0, st>>>(op, n, ntiles, (uint4*)temp);
     return 1;
 }
+#undef OCT_CODE
+template <int T, bool X, int MINB>
+static inline int octscan2_launch(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
+    const u32 ntiles = div_up(n, T * 16);
+    if (!ntiles) return 0;
+    cudaMemsetAsync(temp, 0, chain_temp_bytes(ntiles), st);
+    k_octscan2<T, X, MINB><<<ntiles, T, 0, st>>>(op, n, ntiles, (uint4*)temp);
+    return 1;
+}
 static inline int octscan(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
     static const int variant = pcb_tuning_env("PCB_OCT_VARIANT") ? atoi(pcb_tuning_env("PCB_OCT_VARIANT")) : 0;   // tuning hook
     switch (variant) {
         case 1: return octscan_launch<256, 8>(op, n, temp, st);
         case 2: return octscan_launch<128, 16>(op, n, temp, st);
+        case 3: return octscan2_launch<256, false, 5>(op, n, temp, st);
+        case 5: return octscan2_launch<256, true, 5>(op, n, temp, st);
+        case 6: return octscan2_launch<256, true, 6>(op, n, temp, st);
+        case 7: return octscan2_launch<256, true, 7>(op, n, temp, st);
+        case 8: return octscan2_launch<256, true, 4>(op, n, temp, st);
         default: return octscan_launch<256, 16>(op, n, temp, st);   // measured best of the three on C2
     }
 }
