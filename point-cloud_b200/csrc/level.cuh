@@ -1014,164 +1014,23 @@ struct OctScanOp {
     __device__ void finish(const State&) const {}
 };
 
-// Specialised single-pass kernel for the scan above: inside a tile the eight counters are packed 4 x 16 bit
-// into two 64-bit words (a tile has 2048 arrivals), only the cross-tile prefix uses the 9-word state.
-#define OCT_TILE_MAX 4096   // 16-bit packed counters hold a whole tile
-struct OctPacked {
-    u64 lo, hi;   // counters of octants 0-3 / 4-7, 16 bits each
-    u32 head;
-};
-__device__ __forceinline__ OctPacked oct_combine(const OctPacked& a, const OctPacked& b) {
-    OctPacked r;
-    r.lo = b.head ? b.lo : a.lo + b.lo;
-    r.hi = b.head ? b.hi : a.hi + b.hi;
-    r.head = a.head | b.head;
-    return r;
-}
-template <int OCT_THREADS, int OCT_ITEMS>
-__global__ void __launch_bounds__(OCT_THREADS, 5)   // 48 registers: 5 blocks per SM (4: 3.07 ms, 5: 3.00, 6: 3.05 per C2 step)
-k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
-    constexpr int WARPS = OCT_THREADS / 32;
-    constexpr int OCT_TILE = OCT_THREADS * OCT_ITEMS;
-    static_assert(OCT_TILE <= OCT_TILE_MAX && OCT_ITEMS % 8 == 0, "tile shape");
-    __shared__ OctPacked s_warp[WARPS];
-    __shared__ Oct8 s_prefix;
-    __shared__ u32 s_run[9][OCT_THREADS];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const u32 tile = blockIdx.x;   // see k_chain_scan
-    const u64 base = (u64)tile * OCT_TILE + (u64)tid * OCT_ITEMS;
-
-    // per element: octant (8 = none) | first << 4 | last << 5
-    u32 code[OCT_ITEMS];
-    if (base + OCT_ITEMS <= n) {
-        const ulonglong2* src = (const ulonglong2*)(op.em + base);
-#pragma unroll
-        for (int k = 0; k < OCT_ITEMS / 2; k++) {
-            ulonglong2 e = src[k];
-            code[2 * k] = ((u32)(e.x >> 32) & 0xFu) | ((e.x & PCB_EM_CELL_FIRST) ? 16u : 0u) | ((e.x & PCB_EM_CELL_LAST) ? 32u : 0u);
-            code[2 * k + 1] = ((u32)(e.y >> 32) & 0xFu) | ((e.y & PCB_EM_CELL_FIRST) ? 16u : 0u) | ((e.y & PCB_EM_CELL_LAST) ? 32u : 0u);
-        }
-    } else {
-#pragma unroll
-        for (int k = 0; k < OCT_ITEMS; k++) {
-            code[k] = 8u;
-            if (base + k < n) {
-                u64 e = op.em[base + k];
-                code[k] = ((u32)(e >> 32) & 0xFu) | ((e & PCB_EM_CELL_FIRST) ? 16u : 0u) | ((e & PCB_EM_CELL_LAST) ? 32u : 0u);
-            }
-        }
-    }
-    OctPacked acc{0ull, 0ull, 0u};
-#pragma unroll
-    for (int k = 0; k < OCT_ITEMS; k++) {
-        const u32 o = code[k] & 0xFu;
-        if (code[k] & 16u) { acc.lo = 0; acc.hi = 0; acc.head = 1u; }
-        const u64 one = 1ull << (16 * (o & 3u));
-        acc.lo += (o < 4u) ? one : 0ull;
-        acc.hi += (o >= 4u && o < 8u) ? one : 0ull;
-    }
-    OctPacked winc = acc;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        OctPacked up;
-        up.lo = __shfl_up_sync(0xFFFFFFFFu, winc.lo, d);
-        up.hi = __shfl_up_sync(0xFFFFFFFFu, winc.hi, d);
-        up.head = __shfl_up_sync(0xFFFFFFFFu, winc.head, d);
-        if (lane >= d) winc = oct_combine(up, winc);
-    }
-    if (lane == 31) s_warp[warp] = winc;
-    __syncthreads();
-    OctPacked wpre{0ull, 0ull, 0u}, total{0ull, 0ull, 0u};
-#pragma unroll
-    for (int w = 0; w < WARPS; w++) {
-        OctPacked sw = s_warp[w];
-        if (w < warp) wpre = oct_combine(wpre, sw);
-        total = oct_combine(total, sw);
-    }
-    OctPacked texcl;
-    texcl.lo = __shfl_up_sync(0xFFFFFFFFu, winc.lo, 1);
-    texcl.hi = __shfl_up_sync(0xFFFFFFFFu, winc.hi, 1);
-    texcl.head = __shfl_up_sync(0xFFFFFFFFu, winc.head, 1);
-    if (lane == 0) texcl = OctPacked{0ull, 0ull, 0u};
-    texcl = oct_combine(wpre, texcl);
-
-    if (warp == 0) {
-        Oct8 tot8;
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            tot8.c[k] = (u32)(total.lo >> (16 * k)) & 0xFFFFu;
-            tot8.c[4 + k] = (u32)(total.hi >> (16 * k)) & 0xFFFFu;
-        }
-        tot8.head = total.head;
-        Oct8 prefix = chain_lookback(op, desc, tile, tot8, op.err);
-        if (lane == 0) s_prefix = prefix;
-    }
-    __syncthreads();
-    // running 32-bit counters of this thread: prefix (+) texcl
-    u32 run[8];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        u32 a = (u32)(texcl.lo >> (16 * k)) & 0xFFFFu, b = (u32)(texcl.hi >> (16 * k)) & 0xFFFFu;
-        run[k] = texcl.head ? a : s_prefix.c[k] + a;
-        run[4 + k] = texcl.head ? b : s_prefix.c[4 + k] + b;
-    }
-    // The eight running counters live in shared memory, one column per thread (row = octant, so a warp's accesses
-    // never share a bank): rank = load, bump = store, instead of eight selects and eight predicated adds per item.
-    // Row 8 takes the arrivals that emit nothing.
-#pragma unroll
-    for (int q = 0; q < 8; q++) s_run[q][tid] = run[q];
-    u32 rk[OCT_ITEMS];
-#pragma unroll
-    for (int k = 0; k < OCT_ITEMS; k++) {
-        const u64 i = base + k;
-        const u32 o = code[k] & 0xFu;
-        if (code[k] & 16u) {
-#pragma unroll
-            for (int q = 0; q < 8; q++) s_run[q][tid] = 0;
-        }
-        const u32 got = s_run[o][tid];
-        s_run[o][tid] = got + 1u;
-        const u32 r = o < 8u ? got : 0u;
-        rk[k] = r;
-        if (i < n) {
-            u32 c = PCB_NONE;
-            if (o < 8u && (op.ex_state || r == 0 || r + 1 == op.L || r == op.L)) {
-                c = find_segment(op.cell_start, op.ncell, (u32)i);
-                const u32 kk = 8 * c + o;
-                const u32 b = op.bat[i];
-                if (r == 0) op.special[4 * kk + 0] = b;
-                if (r + 1 == op.L) op.special[4 * kk + 1] = b;
-                if (r == op.L) op.special[4 * kk + 2] = b;
-                if (op.ex_state && op.ex_state[kk] == PCB_EX_SOME) {
-                    u32 m0 = op.ex_m0[kk];
-                    u32 want = (op.L >= 1 + m0) ? op.L - 1 - m0 : 0;
-                    if (r == want) op.special[4 * kk + 3] = b;
-                }
-            }
-            if (code[k] & 32u) {   // last arrival of its cell: bucket totals
-                if (c == PCB_NONE) c = find_segment(op.cell_start, op.ncell, (u32)i);
-#pragma unroll
-                for (int q = 0; q < 8; q++) op.bcnt[8 * c + q] = s_run[q][tid];
-            }
-        }
-    }
-    if (base + OCT_ITEMS <= n) {
-        uint4* dst = (uint4*)(op.rank + base);
-#pragma unroll
-        for (int k = 0; k < OCT_ITEMS / 4; k++) dst[k] = make_uint4(rk[4 * k], rk[4 * k + 1], rk[4 * k + 2], rk[4 * k + 3]);
-    } else {
-#pragma unroll
-        for (int k = 0; k < OCT_ITEMS; k++)
-            if (base + k < n) op.rank[base + k] = rk[k];
-    }
-}
-// Same scan with the per-item work cut to 32-bit register arithmetic (the kernel above issues ~96 instructions per
-// arrival: ncu, profiles/r02_ncu_full_cube_octscan.txt).  A thread's sixteen arrivals are counted ONCE, before the scan,
-// in eight 8-bit counters (two registers); the rank of an arrival inside its thread (< 16) is kept in four bits, and
-// after the look-back an arrival's rank is   4-bit local rank + (thread's start value of its octant, unless a cell
-// started inside the thread before it)   - one read-only shared-memory load instead of a load / store chain.
-// Inside the warp and the block the counters travel as four registers of two 16-bit fields; bit 31 of the fourth
-// is the "a cell starts in the range" flag, which the segmented combine (b.head ? b : a + b) carries along for free.
+// Specialised single-pass kernel for the scan above (tile = 256 threads x 16 consecutive arrivals each):
+//  * a thread's sixteen arrivals are counted in eight 8-bit counters (two registers); the count of an arrival's octant
+//    before it is its rank inside the thread.  The count runs twice: before the scan for the thread's totals, and after
+//    the look-back, when an arrival's rank is  local rank + (the thread's start value of its octant, unless a cell
+//    started inside the thread before it)  - one read-only shared-memory load per arrival;
+//  * inside the warp and the block the counters travel as four registers of two 16-bit fields (a tile has 4096
+//    arrivals); bit 31 of the fourth is the "a cell starts in the range" flag, which the segmented combine
+//    (b.head ? b : a + b) carries along for free.  Only the cross-tile prefix uses the 9-word state of OctScanOp;
+//  * a thread owns CONSECUTIVE arrivals (the scan wants that), so loading them directly would make every warp load
+//    touch 32 different 128-byte lines, and every rank store 16: the warp loads its 512 records with coalesced 16-byte
+//    loads instead, parks the 16-bit codes in shared memory (padded: conflict-free both ways), every thread picks its
+//    sixteen codes up with two 16-byte shared loads, and the ranks take the same way back.
+// Round 2, measured on the B200 per C2 step: 3.00 ms (64-bit packed counters, a shared-memory load / store chain per
+// arrival, direct loads: 96 instructions per arrival, l1tex 68 %) -> 3.44 (32-bit counters, direct loads narrowed to
+// sixteen 4-byte loads per thread: L1-bound) -> 2.74 (transposed loads / stores) -> 2.61 ms (codes packed two per
+// register: 40 registers, six blocks per SM; seven: 2.63, five: 2.76, four: 3.08).
+#define OCT_TILE_MAX 4096   // 16-bit fields hold a whole tile
 struct OctW4 {
     u32 w[4];   // octants (0,1) (2,3) (4,5) (6,7), 16 bits each; bit 31 of w[3]: head
 };
@@ -1194,33 +1053,28 @@ __device__ __forceinline__ u32 oct_bytes_step(u32 code, u32& lo, u32& hi, u32& s
     hi += (o & 4u) ? one : 0u;
     return r;   // meaningless for octant 8 (no emission)
 }
-// XPOSE: a thread owns sixteen CONSECUTIVE arrivals (the scan wants that), so loading them directly makes every warp
-// load touch 32 different 128-byte lines (and every rank store 16).  With XPOSE the warp loads its 512 records with
-// coalesced 16-byte loads, keeps the 16-bit codes in shared memory (padded: conflict-free both ways) and every thread
-// picks up its sixteen codes with two 16-byte shared loads; the ranks take the same way back.
-template <int OCT_THREADS, bool XPOSE, int MINB>
+template <int OCT_THREADS, int MINB>
 __global__ void __launch_bounds__(OCT_THREADS, MINB)
-k_octscan2(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
+k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     constexpr int OCT_ITEMS = 16;
     constexpr int WARPS = OCT_THREADS / 32;
     constexpr int OCT_TILE = OCT_THREADS * OCT_ITEMS;
     static_assert(OCT_TILE <= OCT_TILE_MAX, "16-bit fields hold a whole tile");
     __shared__ uint4 s_warp[WARPS];
     __shared__ Oct8 s_prefix;
-    __shared__ __align__(16) u32 s_run[9][OCT_THREADS];   // XPOSE: first the code transpose, 288 words per warp
-    __shared__ __align__(16) u32 s_out[XPOSE ? WARPS * 576 : 4];
+    __shared__ __align__(16) u32 s_run[9][OCT_THREADS];   // first the code transpose (288 words per warp), then the counters
+    __shared__ __align__(16) u32 s_out[WARPS * 576];      // rank transpose
     static_assert(9 * OCT_THREADS >= WARPS * 288, "code transpose fits the counter columns");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const u32 tile = blockIdx.x;   // see k_chain_scan
     const u64 base = (u64)tile * OCT_TILE + (u64)tid * OCT_ITEMS;
     const u64 wbase = (u64)tile * OCT_TILE + (u64)warp * (32 * OCT_ITEMS);
-    const bool whole = base + OCT_ITEMS <= n;
 
-    // per element: high word of the emission record = octant (8 = none) | last << 8 | first << 9
-    // (two 16-bit codes per register: the sixteen codes stay live across both barriers)
+    // per arrival: high word of the emission record = octant (8 = none) | last << 8 | first << 9, as a 16-bit code;
+    // two codes per register: the sixteen codes stay live across both barriers
     u32 cw[OCT_ITEMS / 2];
 #define OCT_CODE(k) (((k) & 1) ? cw[(k) >> 1] >> 16 : cw[(k) >> 1] & 0xFFFFu)
-    if (XPOSE) {
+    {
         u32* wcode = &s_run[0][0] + warp * 288;
 #pragma unroll
         for (int j = 0; j < 8; j++) {
@@ -1239,20 +1093,6 @@ k_octscan2(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
         const uint4 a = *(const uint4*)(wcode + lane * 8 + (lane >> 2) * 4), b = *(const uint4*)(wcode + lane * 8 + (lane >> 2) * 4 + 4);
         cw[0] = a.x; cw[1] = a.y; cw[2] = a.z; cw[3] = a.w;
         cw[4] = b.x; cw[5] = b.y; cw[6] = b.z; cw[7] = b.w;
-    } else if (whole) {
-        const ulonglong2* src = (const ulonglong2*)(op.em + base);
-#pragma unroll
-        for (int k = 0; k < OCT_ITEMS / 2; k++) {
-            const ulonglong2 e = src[k];
-            cw[k] = ((u32)(e.x >> 32) & 0xFFFFu) | ((u32)(e.y >> 32) << 16);
-        }
-    } else {
-#pragma unroll
-        for (int k = 0; k < OCT_ITEMS / 2; k++) {
-            const u32 c0 = (base + 2 * k < n) ? (u32)(op.em[base + 2 * k] >> 32) : PCB_EM_NONE_OCT;
-            const u32 c1 = (base + 2 * k + 1 < n) ? (u32)(op.em[base + 2 * k + 1] >> 32) : PCB_EM_NONE_OCT;
-            cw[k] = (c0 & 0xFFFFu) | (c1 << 16);
-        }
     }
     u32 lo = 0u, hi = 0u, started = 0u;
 #pragma unroll
@@ -1311,15 +1151,8 @@ k_octscan2(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
         r = o < 8u ? r : 0u;
         rk[k & 3] = r;
         if ((k & 3) == 3) {
-            if (XPOSE) {   // word lane * 16 + k - 3 of the warp's 512, 4 words of padding per 32
-                *(uint4*)(s_out + warp * 576 + lane * 16 + (k - 3) + (lane >> 1) * 4) = make_uint4(rk[0], rk[1], rk[2], rk[3]);
-            } else if (whole) {
-                ((uint4*)(op.rank + base))[k >> 2] = make_uint4(rk[0], rk[1], rk[2], rk[3]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < 4; j++)
-                    if (base + (k - 3 + j) < n) op.rank[base + (k - 3 + j)] = rk[j];
-            }
+            // word lane * 16 + k - 3 of the warp's 512, 4 words of padding per 32
+            *(uint4*)(s_out + warp * 576 + lane * 16 + (k - 3) + (lane >> 1) * 4) = make_uint4(rk[0], rk[1], rk[2], rk[3]);
         }
         u32 c = PCB_NONE;
         if (o < 8u && (op.ex_state || r == 0u || r - (op.L - 1u) <= 1u)) {   // r == 0, L - 1 or L  (L >= 1)
@@ -1343,7 +1176,7 @@ k_octscan2(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
                 op.bcnt[8 * c + q] = (started ? 0u : s_run[q][tid]) + (((q < 4 ? lo : hi) >> (8 * (q & 3))) & 0xFFu);
         }
     }
-    if (XPOSE) {
+    {
         __syncwarp();
 #pragma unroll
         for (int j = 0; j < 4; j++) {
@@ -1360,34 +1193,21 @@ k_octscan2(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
         }
     }
 }
-template <int T, int I>
-static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
-    const u32 ntiles = div_up(n, T * I);
-    if (!ntiles) return 0;
-    cudaMemsetAsync(temp, 0, chain_temp_bytes(ntiles), st);
-    k_octscan<T, I><<<ntiles, T, 0, st>>>(op, n, ntiles, (uint4*)temp);
-    return 1;
-}
 #undef OCT_CODE
-template <int T, bool X, int MINB>
-static inline int octscan2_launch(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
+template <int T, int MINB>
+static inline int octscan_launch(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
     const u32 ntiles = div_up(n, T * 16);
     if (!ntiles) return 0;
     cudaMemsetAsync(temp, 0, chain_temp_bytes(ntiles), st);
-    k_octscan2<T, X, MINB><<<ntiles, T, 0, st>>>(op, n, ntiles, (uint4*)temp);
+    k_octscan<T, MINB><<<ntiles, T, 0, st>>>(op, n, ntiles, (uint4*)temp);
     return 1;
 }
 static inline int octscan(const OctScanOp& op, u32 n, void* temp, cudaStream_t st) {
     static const int variant = pcb_tuning_env("PCB_OCT_VARIANT") ? atoi(pcb_tuning_env("PCB_OCT_VARIANT")) : 0;   // tuning hook
     switch (variant) {
-        case 1: return octscan_launch<256, 8>(op, n, temp, st);
-        case 2: return octscan_launch<128, 16>(op, n, temp, st);
-        case 3: return octscan2_launch<256, false, 5>(op, n, temp, st);
-        case 5: return octscan2_launch<256, true, 5>(op, n, temp, st);
-        case 6: return octscan2_launch<256, true, 6>(op, n, temp, st);
-        case 7: return octscan2_launch<256, true, 7>(op, n, temp, st);
-        case 8: return octscan2_launch<256, true, 4>(op, n, temp, st);
-        default: return octscan_launch<256, 16>(op, n, temp, st);   // measured best of the three on C2
+        case 1: return octscan_launch<256, 5>(op, n, temp, st);
+        case 2: return octscan_launch<256, 7>(op, n, temp, st);
+        default: return octscan_launch<256, 6>(op, n, temp, st);   // 40 registers, six blocks per SM
     }
 }
 
