@@ -107,25 +107,17 @@ struct DirNodeSource : NodeSource {
     std::string dir;
     std::atomic<uint64_t> total_before{0};   // header totals of the nodes loaded (PCB_FLAG_COUNT_BY_DELTA)
     bool load(uint32_t hierarchy, const int32_t idx[3], ExistingNode* out) override {
+        std::vector<uint8_t> bytes;
+        bool nf = false;
         std::string p = dir + "/" + node_rel_path(hierarchy, idx);
-        FILE* f = std::fopen(p.c_str(), "rb");
-        if (!f) {
-            if (errno == ENOENT) return false;
+        if (!read_file(p, &bytes, &nf)) {
+            if (nf) return false;
             throw Error{PCB_ERR_IO, "cannot read node file " + p};
         }
-        std::fseek(f, 0, SEEK_END);
-        const long n = std::ftell(f);
-        std::fseek(f, 0, SEEK_SET);
-        const size_t len = n > 0 ? (size_t)n : 0;
-        out->raw.reset(new uint8_t[len + 16]);   // uninitialised: the file is read straight into it
-        out->raw_len = len;
-        const size_t got = len ? std::fread(out->raw.get(), 1, len, f) : 0;
-        std::fclose(f);
-        if (got != len) throw Error{PCB_ERR_IO, "cannot read node file " + p};
-        if (!parse_node(out->raw.get(), len, out)) throw Error{PCB_ERR_FORMAT, "corrupt node file " + p};
-        if (len >= 20) {   // Header.total_number_of_points (cell.rs:286)
+        if (!parse_node(bytes.data(), bytes.size(), out)) throw Error{PCB_ERR_FORMAT, "corrupt node file " + p};
+        if (bytes.size() >= 20) {   // Header.total_number_of_points (cell.rs:286)
             uint32_t t;
-            std::memcpy(&t, out->raw.get() + 16, 4);
+            std::memcpy(&t, bytes.data() + 16, 4);
             total_before += t;
         }
         return true;

@@ -991,7 +991,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
                         at += e.list.size();
                     }
                 }
-                ens[c].raw.reset();   // release as we go
+                ExistingNode().grid.swap(ens[c].grid);   // release as we go
                 ens[c].entries.clear();
             });
             trace_mark(st, "merge_pack", h, nex);

@@ -6,7 +6,6 @@
 #include <stdint.h>
 
 #include <map>
-#include <memory>
 #include <string>
 #include <vector>
 
@@ -30,28 +29,16 @@ bool metadata_from_json(const std::string& text, Metadata* m);   // metadata.rs:
 std::string format_f32(float v);                                 // ryu / serde_json float text
 
 // State of one node file read back for merge mode (cell.rs:183-229).
-// A zero-copy VIEW over the bytes of the file (`raw`, or caller-owned memory): the 16-byte records are copied exactly
-// once, by whoever consumes them (merge loader -> pinned staging; own-format reader -> its chunk).  The record pointers
-// are not 16-byte aligned in general (overflow lists sit at odd offsets): memcpy only.
-struct RecordSpan {
-    const uint8_t* ptr = nullptr;      // count x 16-byte records
-    size_t count = 0;
-    size_t size() const { return count; }
-    bool empty() const { return count == 0; }
-    const uint8_t* data() const { return ptr; }
-};
 struct ExistingNode {
-    std::unique_ptr<uint8_t[]> raw;    // the file's bytes when the node owns them (not zero-filled first)
-    size_t raw_len = 0;
-    RecordSpan grid;
+    std::vector<pcb_point> grid;
     struct Entry {
         int32_t child[3];
         bool none;                     // count == 0 marker: child already flushed
-        RecordSpan list;
+        std::vector<pcb_point> list;
     };
     std::vector<Entry> entries;
 };
-bool parse_node(const uint8_t* data, size_t len, ExistingNode* out);   // out->grid / lists point into `data`
+bool parse_node(const uint8_t* data, size_t len, ExistingNode* out);
 std::string node_rel_path(uint32_t hierarchy, const int32_t idx[3]);  // cell.rs:20-31
 
 // Supplies existing nodes in merge mode; returns false when the node does not exist (converter.rs:187-207).

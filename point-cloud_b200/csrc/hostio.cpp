@@ -260,8 +260,8 @@ bool parse_node(const uint8_t* data, size_t len, ExistingNode* out) {
     const uint32_t ng = rd_u32(data + 20);
     size_t off = 48;
     if ((len - off) / 16 < ng) return false;
-    out->grid.ptr = data + off;
-    out->grid.count = ng;
+    out->grid.resize(ng);
+    if (ng) std::memcpy(out->grid.data(), data + off, 16ull * ng);
     off += 16ull * ng;
     if (off >= len) return false;
     const unsigned nent = data[off++];
@@ -275,8 +275,8 @@ bool parse_node(const uint8_t* data, size_t len, ExistingNode* out) {
         en.none = (cnt == 0);  // cell.rs:210-211
         if (cnt) {
             if ((len - off) / 16 < cnt) return false;
-            en.list.ptr = data + off;
-            en.list.count = cnt;
+            en.list.resize(cnt);
+            std::memcpy(en.list.data(), data + off, 16ull * cnt);
             off += 16ull * cnt;
         }
         out->entries.push_back(std::move(en));

@@ -402,16 +402,8 @@ int PointStream::next(uint64_t max_points, pcb_point* out, uint64_t* n, std::str
             im->carry.clear();
             im->carry_at = 0;
             if (!slurp(im->files[im->next_file++], &cell) || !parse_node(cell.data(), cell.size(), &node)) continue;  // own.rs:42-48
-            size_t total = node.grid.count;
-            for (auto& en : node.entries) total += en.list.count;
-            im->carry.resize(total);
-            size_t at = 0;
-            if (node.grid.count) memcpy(im->carry.data(), node.grid.ptr, 16 * node.grid.count);
-            at += node.grid.count;
-            for (auto& en : node.entries) {
-                if (en.list.count) memcpy(im->carry.data() + at, en.list.ptr, 16 * en.list.count);
-                at += en.list.count;
-            }
+            im->carry = std::move(node.grid);
+            for (auto& en : node.entries) im->carry.insert(im->carry.end(), en.list.begin(), en.list.end());
         }
         *n = got;
         im->delivered += got;
