@@ -16,7 +16,7 @@ for w in new old; do grep "^{" gpurun_out/r02_bench_k_merge_$w.json | python -c 
 P="python bench.py --steps 1 --warmup 1 --e2e-steps 0 --no-cpu --no-files --no-clocks"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'^k_' -c 600 --csv --log-file gpurun_out/r02_launches_k.csv $P > gpurun_out/ncu_list.log 2>&1
 python scripts/ncu_launches.py gpurun_out/r02_launches_k.csv > gpurun_out/r02_ncu_launches_k.txt; head -12 gpurun_out/r02_ncu_launches_k.txt
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_octscan -s 12 -c 4 -o gpurun_out/r02_octscan_k $P > gpurun_out/ncu_full_oct.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_octscan -s 5 -c 5 -o gpurun_out/r02_octscan_k $P > gpurun_out/ncu_full_oct.log 2>&1
 python scripts/ncu_summary.py gpurun_out/r02_octscan_k.ncu-rep > gpurun_out/r02_ncu_full_octscan_k.txt 2>&1
 ncu -i gpurun_out/r02_octscan_k.ncu-rep --page raw --csv 2>/dev/null | python -c "
 import csv,sys
