@@ -1016,9 +1016,9 @@ struct OctScanOp {
 
 // Specialised single-pass kernel for the scan above (tile = 256 threads x 16 consecutive arrivals each):
 //  * a thread's sixteen arrivals are counted in eight 8-bit counters (two registers); the count of an arrival's octant
-//    before it is its rank inside the thread.  The count runs twice: before the scan for the thread's totals, and after
-//    the look-back, when an arrival's rank is  local rank + (the thread's start value of its octant, unless a cell
-//    started inside the thread before it)  - one read-only shared-memory load per arrival;
+//    before it is its rank inside the thread.  The count runs twice: before the scan for the thread's totals, and again
+//    for the ranks inside the tile:  local rank + (the thread's start value of its octant, unless a cell started inside
+//    the thread before it)  - one read-only shared-memory load per arrival;
 //  * inside the warp and the block the counters travel as four registers of two 16-bit fields (a tile has 4096
 //    arrivals); bit 31 of the fourth is the "a cell starts in the range" flag, which the segmented combine
 //    (b.head ? b : a + b) carries along for free.  Only the cross-tile prefix uses the 9-word state of OctScanOp;
@@ -1026,10 +1026,15 @@ struct OctScanOp {
 //    touch 32 different 128-byte lines, and every rank store 16: the warp loads its 512 records with coalesced 16-byte
 //    loads instead, parks the 16-bit codes in shared memory (padded: conflict-free both ways), every thread picks its
 //    sixteen codes up with two 16-byte shared loads, and the ranks take the same way back.
+//  * the ranks INSIDE the tile do not depend on the tiles before it, so they are computed while warp 0 waits in the
+//    look-back (warp 0: publish the aggregate, own ranks, then poll); they are parked in the rank-transpose buffer as
+//    tile-local rank | octant << 16 | "no prefix" << 20  and the tile prefix of the octant is added on the way out, in
+//    the coalesced layout: behind the look-back there is one shared load, one add and the trigger test per arrival.
 // Round 2, measured on the B200 per C2 step: 3.00 ms (64-bit packed counters, a shared-memory load / store chain per
 // arrival, direct loads: 96 instructions per arrival, l1tex 68 %) -> 3.44 (32-bit counters, direct loads narrowed to
 // sixteen 4-byte loads per thread: L1-bound) -> 2.74 (transposed loads / stores) -> 2.61 ms (codes packed two per
-// register: 40 registers, six blocks per SM; seven: 2.63, five: 2.76, four: 3.08).
+// register: 40 registers, six blocks per SM; seven: 2.63, five: 2.76, four: 3.08) -> 2.55 ms (in-tile ranks computed
+// during the look-back).
 #define OCT_TILE_MAX 4096   // 16-bit fields hold a whole tile
 struct OctW4 {
     u32 w[4];   // octants (0,1) (2,3) (4,5) (6,7), 16 bits each; bit 31 of w[3]: head
@@ -1053,6 +1058,24 @@ __device__ __forceinline__ u32 oct_bytes_step(u32 code, u32& lo, u32& hi, u32& s
     hi += (o & 4u) ? one : 0u;
     return r;   // meaningless for octant 8 (no emission)
 }
+#define OCT_CODE(k) (((k) & 1) ? cw[(k) >> 1] >> 16 : cw[(k) >> 1] & 0xFFFFu)   // two 16-bit codes per register
+struct OctCw8 {
+    u32 w[8];
+};
+// bucket totals of the cell whose last arrival is item kl of this thread (rare: once per cell)
+__device__ __noinline__ void oct_cell_totals(OctCw8 cw, int kl, u32 cell, bool tcut, const u32* __restrict__ col /* s_run column, stride */,
+                                             int stride, const Oct8* __restrict__ prefix, u32* __restrict__ bcnt) {
+    u32 lo = 0u, hi = 0u, started = 0u;
+    for (int j = 0; j <= kl; j++) {
+        const u32 c16 = (j & 1) ? cw.w[j >> 1] >> 16 : cw.w[j >> 1] & 0xFFFFu;
+        oct_bytes_step(c16, lo, hi, started);
+    }
+    for (int q = 0; q < 8; q++) {
+        u32 v = ((q < 4 ? lo : hi) >> (8 * (q & 3))) & 0xFFu;
+        if (!started) v += col[q * stride] + (tcut ? 0u : prefix->c[q]);
+        bcnt[8 * cell + q] = v;
+    }
+}
 template <int OCT_THREADS, int MINB>
 __global__ void __launch_bounds__(OCT_THREADS, MINB)
 k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
@@ -1062,18 +1085,14 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     static_assert(OCT_TILE <= OCT_TILE_MAX, "16-bit fields hold a whole tile");
     __shared__ uint4 s_warp[WARPS];
     __shared__ Oct8 s_prefix;
-    __shared__ __align__(16) u32 s_run[9][OCT_THREADS];   // first the code transpose (288 words per warp), then the counters
-    __shared__ __align__(16) u32 s_out[WARPS * 576];      // rank transpose
+    __shared__ __align__(16) u32 s_run[9][OCT_THREADS];
+    __shared__ __align__(16) u32 s_out[WARPS * 576];
     static_assert(9 * OCT_THREADS >= WARPS * 288, "code transpose fits the counter columns");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const u32 tile = blockIdx.x;   // see k_chain_scan
     const u64 base = (u64)tile * OCT_TILE + (u64)tid * OCT_ITEMS;
     const u64 wbase = (u64)tile * OCT_TILE + (u64)warp * (32 * OCT_ITEMS);
-
-    // per arrival: high word of the emission record = octant (8 = none) | last << 8 | first << 9, as a 16-bit code;
-    // two codes per register: the sixteen codes stay live across both barriers
     u32 cw[OCT_ITEMS / 2];
-#define OCT_CODE(k) (((k) & 1) ? cw[(k) >> 1] >> 16 : cw[(k) >> 1] & 0xFFFFu)
     {
         u32* wcode = &s_run[0][0] + warp * 288;
 #pragma unroll
@@ -1087,7 +1106,7 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
             } else if (e0 < n) {
                 c0 = (u32)(op.em[e0] >> 32);
             }
-            wcode[j * 36 + lane] = (c0 & 0xFFFFu) | (c1 << 16);   // word i = records 2i, 2i+1; 4 words of padding per 32
+            wcode[j * 36 + lane] = (c0 & 0xFFFFu) | (c1 << 16);
         }
         __syncwarp();
         const uint4 a = *(const uint4*)(wcode + lane * 8 + (lane >> 2) * 4), b = *(const uint4*)(wcode + lane * 8 + (lane >> 2) * 4 + 4);
@@ -1110,7 +1129,7 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
         if (lane >= d) winc = octw_combine(up, winc);
     }
     if (lane == 31) s_warp[warp] = make_uint4(winc.w[0], winc.w[1], winc.w[2], winc.w[3]);
-    __syncthreads();
+    __syncthreads();   // (also: every warp has picked its codes up, s_run may be reused)
     OctW4 wpre{{0u, 0u, 0u, 0u}}, total{{0u, 0u, 0u, 0u}};
 #pragma unroll
     for (int w = 0; w < WARPS; w++) {
@@ -1124,73 +1143,85 @@ k_octscan(OctScanOp op, u32 n, u32 ntiles, uint4* __restrict__ desc) {
     for (int q = 0; q < 4; q++) texcl.w[q] = __shfl_up_sync(0xFFFFFFFFu, winc.w[q], 1);
     if (lane == 0) texcl = OctW4{{0u, 0u, 0u, 0u}};
     texcl = octw_combine(wpre, texcl);
-
+    Oct8 tot8;
     if (warp == 0) {
-        Oct8 tot8;
 #pragma unroll
         for (int q = 0; q < 8; q++) tot8.c[q] = octw_field(total, q);
         tot8.head = total.w[3] >> 31;
-        Oct8 prefix = chain_lookback(op, desc, tile, tot8, op.err);
+        if (lane == 0) chain_publish<OctScanOp>(desc, tile, tot8, tile == 0 ? PCB_DESC_INCL : PCB_DESC_AGG);
+    }
+    // ranks inside the tile
+    const bool tcut = (texcl.w[3] & OCT_HEAD_BIT) != 0u;
+#pragma unroll
+    for (int q = 0; q < 8; q++) s_run[q][tid] = octw_field(texcl, q);
+    s_run[8][tid] = 0u;
+    u32 lastmask = 0u;
+    {
+        u32 pk[4];
+        lo = 0u; hi = 0u; started = 0u;
+#pragma unroll
+        for (int k = 0; k < OCT_ITEMS; k++) {
+            const u32 code = OCT_CODE(k);
+            const u32 o = code & 0xFu;
+            const u32 start = s_run[o][tid];
+            const u32 local = oct_bytes_step(code, lo, hi, started);
+            const u32 r = started ? local : start + local;
+            const u32 nofix = (started != 0u || tcut || o >= 8u) ? 1u : 0u;
+            pk[k & 3] = (o < 8u ? r : 0u) | (o << 16) | (nofix << 20);
+            lastmask |= ((code >> 8) & 1u) << k;
+            if ((k & 3) == 3)
+                *(uint4*)(s_out + warp * 576 + lane * 16 + (k - 3) + (lane >> 1) * 4) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        }
+    }
+    if (warp == 0) {
+        Oct8 prefix = chain_lookback(op, desc, tile, tot8, op.err, false);
         if (lane == 0) s_prefix = prefix;
     }
     __syncthreads();
-    // start values of this thread's eight counters: (tiles before) (+) (threads before inside the tile)
-    const bool tcut = (texcl.w[3] & OCT_HEAD_BIT) != 0u;
+    // on the way out (coalesced layout): + prefix of the octant, trigger batches, store
 #pragma unroll
-    for (int q = 0; q < 8; q++) s_run[q][tid] = (tcut ? 0u : s_prefix.c[q]) + octw_field(texcl, q);
-    s_run[8][tid] = 0u;
-    u32 rk[4];
-    lo = 0u; hi = 0u; started = 0u;   // the same count again, now with the start values known
+    for (int j = 0; j < 4; j++) {
+        const int i = j * 128 + lane * 4;
+        const uint4 v = *(const uint4*)(s_out + warp * 576 + i + (i >> 5) * 4);
+        const u32 w4[4] = {v.x, v.y, v.z, v.w};
+        const u64 e0 = wbase + (u64)i;
+        u32 rk[4];
 #pragma unroll
-    for (int k = 0; k < OCT_ITEMS; k++) {
-        const u32 code = OCT_CODE(k);
-        const u32 o = code & 0xFu;
-        const u32 start = s_run[o][tid];
-        const u32 local = oct_bytes_step(code, lo, hi, started);
-        u32 r = started ? local : start + local;
-        r = o < 8u ? r : 0u;
-        rk[k & 3] = r;
-        if ((k & 3) == 3) {
-            // word lane * 16 + k - 3 of the warp's 512, 4 words of padding per 32
-            *(uint4*)(s_out + warp * 576 + lane * 16 + (k - 3) + (lane >> 1) * 4) = make_uint4(rk[0], rk[1], rk[2], rk[3]);
-        }
-        u32 c = PCB_NONE;
-        if (o < 8u && (op.ex_state || r == 0u || r - (op.L - 1u) <= 1u)) {   // r == 0, L - 1 or L  (L >= 1)
-            const u32 i = (u32)(base + k);
-            c = find_segment(op.cell_start, op.ncell, i);
-            const u32 kk = 8 * c + o;
-            const u32 b = op.bat[i];
-            if (r == 0) op.special[4 * kk + 0] = b;
-            if (r + 1 == op.L) op.special[4 * kk + 1] = b;
-            if (r == op.L) op.special[4 * kk + 2] = b;
-            if (op.ex_state && op.ex_state[kk] == PCB_EX_SOME) {
-                u32 m0 = op.ex_m0[kk];
-                u32 want = (op.L >= 1 + m0) ? op.L - 1 - m0 : 0;
-                if (r == want) op.special[4 * kk + 3] = b;
+        for (int t = 0; t < 4; t++) {
+            const u32 o = (w4[t] >> 16) & 0xFu;
+            const u32 pre = s_prefix.c[o & 7u];
+            const u32 r = (w4[t] & 0xFFFFu) + (((w4[t] >> 20) & 1u) ? 0u : pre);
+            rk[t] = r;
+            if (o < 8u && (op.ex_state || r == 0u || r - (op.L - 1u) <= 1u)) {   // r == 0, L - 1 or L  (L >= 1)
+                const u32 ii = (u32)(e0 + t);
+                const u32 c = find_segment(op.cell_start, op.ncell, ii);
+                const u32 kk = 8 * c + o;
+                const u32 b = op.bat[ii];
+                if (r == 0) op.special[4 * kk + 0] = b;
+                if (r + 1 == op.L) op.special[4 * kk + 1] = b;
+                if (r == op.L) op.special[4 * kk + 2] = b;
+                if (op.ex_state && op.ex_state[kk] == PCB_EX_SOME) {
+                    u32 m0 = op.ex_m0[kk];
+                    u32 want = (op.L >= 1 + m0) ? op.L - 1 - m0 : 0;
+                    if (r == want) op.special[4 * kk + 3] = b;
+                }
             }
         }
-        if (code & 0x100u) {   // PCB_EM_CELL_LAST >> 32: bucket totals of the cell
-            if (c == PCB_NONE) c = find_segment(op.cell_start, op.ncell, (u32)(base + k));
-#pragma unroll
-            for (int q = 0; q < 8; q++)
-                op.bcnt[8 * c + q] = (started ? 0u : s_run[q][tid]) + (((q < 4 ? lo : hi) >> (8 * (q & 3))) & 0xFFu);
+        if (e0 + 4 <= n) {
+            *(uint4*)(op.rank + e0) = make_uint4(rk[0], rk[1], rk[2], rk[3]);
+        } else {
+            if (e0 < n) op.rank[e0] = rk[0];
+            if (e0 + 1 < n) op.rank[e0 + 1] = rk[1];
+            if (e0 + 2 < n) op.rank[e0 + 2] = rk[2];
         }
     }
-    {
-        __syncwarp();
+    while (lastmask) {   // last arrival of a cell (once per cell): bucket totals
+        const int kl = __ffs(lastmask) - 1;
+        lastmask &= lastmask - 1u;
+        OctCw8 c8;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int i = j * 128 + lane * 4;
-            const uint4 v = *(const uint4*)(s_out + warp * 576 + i + (i >> 5) * 4);
-            const u64 e0 = wbase + (u64)i;
-            if (e0 + 4 <= n) {
-                *(uint4*)(op.rank + e0) = v;
-            } else {
-                if (e0 < n) op.rank[e0] = v.x;
-                if (e0 + 1 < n) op.rank[e0 + 1] = v.y;
-                if (e0 + 2 < n) op.rank[e0 + 2] = v.z;
-            }
-        }
+        for (int m = 0; m < 8; m++) c8.w[m] = cw[m];
+        oct_cell_totals(c8, kl, find_segment(op.cell_start, op.ncell, (u32)(base + kl)), tcut, &s_run[0][tid], OCT_THREADS, &s_prefix, op.bcnt);
     }
 }
 #undef OCT_CODE

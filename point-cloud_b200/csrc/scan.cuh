@@ -120,12 +120,14 @@ __device__ __forceinline__ void chain_publish(uint4* __restrict__ desc, u32 tile
 
 // Warp-wide look-back of tile `tile` (call with all 32 lanes of ONE warp): publishes `total` as the tile's
 // aggregate, folds the predecessors, publishes the inclusive prefix and returns the exclusive one (all lanes).
+// publish = false: the caller has already published the aggregate (chain_publish by one lane) and did other work since.
 template <class Op>
 __device__ __forceinline__ typename Op::State chain_lookback(const Op& op, uint4* __restrict__ desc, u32 tile,
-                                                             const typename Op::State& total, u32* err = nullptr) {
+                                                             const typename Op::State& total, u32* err = nullptr,
+                                                             bool publish = true) {
     typedef typename Op::State State;
     const int lane = threadIdx.x & 31;
-    if (lane == 0) chain_publish<Op>(desc, tile, total, tile == 0 ? PCB_DESC_INCL : PCB_DESC_AGG);
+    if (publish && lane == 0) chain_publish<Op>(desc, tile, total, tile == 0 ? PCB_DESC_INCL : PCB_DESC_AGG);
     State prefix = op.identity();
     if (tile > 0) {
         int look = (int)tile - 1;
