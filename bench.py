@@ -386,9 +386,6 @@ def main():
     for _ in range(args.warmup):
         step()
     barrier()
-    import gc
-    gc.collect()
-    gc.disable()   # no collector pause inside the timed region
     route_launches[0] = 0
     sampler.mark_start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -407,7 +404,6 @@ def main():
                 d[f] += k[f]
     ev1.record(stream)
     barrier()
-    gc.enable()
     route_timed = route_launches[0]
     sampler.mark_end()
     clocks = sampler.stop()
