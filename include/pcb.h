@@ -256,6 +256,8 @@ int pcb_route_bbox_static(int device, void* stream, const pcb_point* d_pts, uint
    the point (binary search over the loaded cells, optionally overridden by distance to the camera), colour alpha :=
    that hierarchy, append to d_out through the atomic counter *d_count (the indirect draw buffer's instance_count:
    the caller zeroes it, or lets several cells accumulate).  Output order is the atomic's, as in the shader.
+   CAPACITY: d_out must hold (*d_count on entry) + n records - when several dispatches accumulate into one counter they
+   share ONE output buffer sized for all of them, as the renderer's indirect buffer is; nothing is bounds-checked.
    Matrices are column-major (glam / wgpu): m[4 * col + row].  d_hierarchies: number_of_hierarchies x (cell_size,
    spacing) floats; d_loaded_cells: n_loaded x (hierarchy, x, y, z) i32, sorted ascending, 16-byte aligned;
    d_far_distances: >= max_hierarchy + 1 floats (only read when size_by_distance); d_depth: depth_height rows of
