@@ -132,21 +132,24 @@ __device__ __forceinline__ void radix_hist_flush(const u32* __restrict__ hist, c
 // digits 20 % faster).  MODE 0 = match, 1 = votes, 2 = adaptive: the warp matches its first item, counts the
 // groups and picks the cheaper way for the other items.
 #define RADIX_ADAPT_GROUPS 8
+// CBITS > 0: the digit width is a compile-time constant (the production plans are all 8-bit passes): no per-bit
+// `b < bits` test.  Per bit: test (LOP3 -> predicate), VOTE, SEL, one 3-input LOP3.
+template <int CBITS = 0>
 __device__ __forceinline__ u32 radix_peers_vote(u32 d, bool valid, int bits) {
     u32 peers = __ballot_sync(0xFFFFFFFFu, valid);
 #pragma unroll
-    for (int b = 0; b < RADIX_MAX_BITS; b++) {
-        if (b < bits) {
-            const bool bit = (d >> b) & 1u;
-            const u32 m = __ballot_sync(0xFFFFFFFFu, bit);
-            peers &= bit ? m : ~m;
+    for (int b = 0; b < (CBITS ? CBITS : RADIX_MAX_BITS); b++) {
+        if (CBITS || b < bits) {
+            const u32 sel = d & (1u << b);
+            const u32 m = __ballot_sync(0xFFFFFFFFu, sel != 0u);
+            peers &= m ^ (sel ? 0u : 0xFFFFFFFFu);
         }
     }
     return peers;
 }
-template <int MODE>
+template <int MODE, int CBITS = 0>
 __device__ __forceinline__ u32 radix_peers(u32 d, bool valid, int bits, u32 bins, int k, bool& votes) {
-    if (MODE == 1 || (MODE == 2 && k > 0 && votes)) return radix_peers_vote(d, valid, bits);
+    if (MODE == 1 || (MODE == 2 && k > 0 && votes)) return radix_peers_vote<CBITS>(d, valid, bits);
     const u32 peers = __match_any_sync(0xFFFFFFFFu, valid ? d : bins);   // invalid lanes form their own group
     if (MODE == 2 && k == 0) {
         const u32 leaders = __ballot_sync(0xFFFFFFFFu, (peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u);
@@ -169,10 +172,10 @@ struct RadixShape {
                                     : (65536 / (64 * THREADS));
 };
 
-template <bool PAIRS, int THREADS, int MODE>
+template <bool PAIRS, int THREADS, int MODE, int CBITS>
 __global__ void __launch_bounds__(THREADS, RadixShape<PAIRS, THREADS>::minb)
 k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u32* __restrict__ vals_in,
-           u32* __restrict__ vals_out, u32 n, int shift, int bits, const u32* __restrict__ ghist /* [bins] */,
+           u32* __restrict__ vals_out, u32 n, int shift, int bits_arg, const u32* __restrict__ ghist /* [bins] */,
            u32* __restrict__ status /* [ntiles][bins] */, u32* __restrict__ counter,
            const uint4* __restrict__ tinfo /* segmented: per tile {first key, keys, segment, first key of the segment} */,
            u32 hist_stride /* words between the histograms of consecutive segments */, u32* __restrict__ err) {
@@ -185,6 +188,7 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
     __shared__ u32 s_tile;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bits = CBITS ? CBITS : bits_arg;   // CBITS > 0: compile-time digit width (bins, digits per thread, votes)
     const u32 bins = 1u << bits, mask = bins - 1u;
     u32* dig_excl = cnt + WARPS * bins;
     u32* gbase = dig_excl + bins;
@@ -222,19 +226,20 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
     // warp-striped ownership: item k of lane l in warp w is element w*32*ITEMS + k*32 + l (order: k, then lane)
     u64 key[RADIX_ITEMS];
     const u32 wbase = warp * 32 * RADIX_ITEMS + lane;
+    // item k is valid iff wbase + 32 k < tile_n iff k < kmax: one compare against a register per item (the compiler
+    // otherwise rebuilds j from the thread index for every item under the 64-register cap)
+    const int kmax = tile_n > wbase ? (int)min((u32)RADIX_ITEMS, (tile_n - wbase + 31u) / 32u) : 0;
 #pragma unroll
     for (int k = 0; k < RADIX_ITEMS; k++) {
         u32 j = wbase + k * 32;
-        key[k] = (j < tile_n) ? keys_in[tbase + j] : ~0ull;
+        key[k] = (k < kmax) ? keys_in[tbase + j] : ~0ull;
     }
     // early counts: per-warp digit histogram with shared-memory atomics, so that the tile's counts can be
     // published (and the tiles behind us unblocked) before the stable ranking
     u32* wcnt = cnt + warp * bins;
 #pragma unroll
-    for (int k = 0; k < RADIX_ITEMS; k++) {
-        u32 j = wbase + k * 32;
-        if (j < tile_n) atomicAdd(&wcnt[(u32)(key[k] >> shift) & mask], 1u);
-    }
+    for (int k = 0; k < RADIX_ITEMS; k++)
+        if (k < kmax) atomicAdd(&wcnt[(u32)(key[k] >> shift) & mask], 1u);
     __syncthreads();
     RADIX_TICK(1);   // key loads + early counts
 
@@ -304,9 +309,9 @@ k_onesweep(const u64* __restrict__ keys_in, u64* __restrict__ keys_out, const u3
 #pragma unroll
     for (int k = 0; k < RADIX_ITEMS; k++) {
         u32 j = wbase + k * 32;
-        bool valid = j < tile_n;
+        bool valid = k < kmax;
         u32 d = (u32)(key[k] >> shift) & mask;
-        u32 peers = radix_peers<MODE>(d, valid, bits, bins, k, votes);
+        u32 peers = radix_peers<MODE, CBITS>(d, valid, bits, bins, k, votes);
         u32 lower = __popc(peers & lt);
         u32 before = valid ? wcnt[d] : 0u;
         __syncwarp();
@@ -437,14 +442,18 @@ struct RadixTemp {
 template <bool PAIRS, int THREADS, int MODE, class Prof>
 static inline int radix_sort_shape(u64* k0, u32* v0, u64* k1, u32* v1, u32 n, const RadixPlan& plan, RadixTemp& tmp,
                                    cudaStream_t st, Prof& prof) {
-    auto kern = k_onesweep<PAIRS, THREADS, MODE>;
+    auto kern_any = k_onesweep<PAIRS, THREADS, MODE, 0>;                      // any digit width
+    auto kern_def = k_onesweep<PAIRS, THREADS, MODE, RADIX_DEFAULT_BITS>;     // the production width, compiled in
     constexpr int smem = RadixSmem<PAIRS, THREADS>::bytes, TILE = THREADS * RADIX_ITEMS;
     static bool attr_set = false;   // per instantiation
     if (!attr_set) {
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        for (auto kern : {kern_any, kern_def}) {
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        }
         attr_set = true;
     }
+    static const bool generic_only = pcb_tuning_env("PCB_RADIX_GENERIC") != nullptr;   // tuning hook: A/B of the two
     int cur = 0;
     if (n < 2) return 0;
     const u32 ntiles = tmp.tinfo ? tmp.ntiles_seg : div_up(n, TILE);
@@ -455,6 +464,7 @@ static inline int radix_sort_shape(u64* k0, u32* v0, u64* k1, u32* v1, u32 n, co
         u64 *ki = cur ? k1 : k0, *ko = cur ? k0 : k1;
         u32 *vi = cur ? v1 : v0, *vo = cur ? v0 : v1;
         prof.pb();
+        auto kern = (plan.bits[p] == RADIX_DEFAULT_BITS && !generic_only) ? kern_def : kern_any;
         kern<<<ntiles, THREADS, smem, st>>>(ki, ko, vi, vo, n, plan.shift[p], plan.bits[p],
                                             tmp.ghist + p * RADIX_MAX_BINS, status, status + words, tmp.tinfo,
                                             hist_stride, tmp.err);
