@@ -251,7 +251,7 @@ def write_ply(path, pts_np):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--points", type=int, default=100_000_000, help="points per GPU (C2 = 1e8)")
@@ -391,12 +391,16 @@ def main():
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches, kstats, last = 0, {}, None
     step_evs = []
+    import resource
+    step_host = []   # per step: involuntary context switches of this process (was the host thread preempted?)
     ev0.record(stream)
     for _ in range(args.steps):
+        nivcsw0 = resource.getrusage(resource.RUSAGE_SELF).ru_nivcsw
         last, ks = step()
         e = torch.cuda.Event(enable_timing=True)
         e.record(stream)
         step_evs.append(e)
+        step_host.append(resource.getrusage(resource.RUSAGE_SELF).ru_nivcsw - nivcsw0)
         launches += last.gpu_launches
         for k in ks:
             d = kstats.setdefault(k["name"], dict(launches=0, units=0, bytes=0, ms=0.0))
@@ -623,6 +627,10 @@ def main():
                           "levels": int(last.levels_built), "arrivals_per_point": round(last.arrivals / n, 3),
                           "nodes": int(last.nodes_written), "sharding": ("none (1 GPU)" if world == 1 else
                                        "level-0 cell owners; exchange inside the timed step = " + exchange[0]), "step_ms": step_ms,
+                                  "step_host": {"involuntary_ctx_switches": step_host, "open_finish_close_ms": [list(x) for x in host_log[-args.steps:]], "loadavg_1min": round(os.getloadavg()[0], 1),
+                                                "cpus": os.cpu_count(),
+                                                "note": "a step needs ~9 host round trips; a step far above the others is the "
+                                                        "host side of a shared box (preemption / PCIe latency), see kernels"},
                           **({"rebalance": {"mode": args.rebalance, **{k: v for k, v in shard_info[0].items() if k != "exchange"}}}
                              if world > 1 else {}),
                           **({"ranks": ranks_info} if ranks_info else {})},
