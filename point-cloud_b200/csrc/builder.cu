@@ -1112,6 +1112,16 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         }
     };
     const u32 hexgrid = std::min<u32>(148 * 8, div_up(n, 256));
+    static const int hexkey_minb = pcb_tuning_env("PCB_HEXKEY_MINB") ? atoi(pcb_tuning_env("PCB_HEXKEY_MINB")) : 8;   // tuning hook
+    auto launch_hexkey = [&](const RadixPlan& plan, u64* keys, u32* vals, u32* ghist, const u32* estart, u64* keys_e) {
+#define PCB_HEXKEY(M)                                                                                                     \
+    k_hexkey<PAIRS, M><<<std::min<u32>(148 * M, div_up(n, 256)), 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay, plan, keys, vals, \
+                                                                             d2oct, ghist, segk, nseg, estart, keys_e, &d_scr->err)
+        if (hexkey_minb == 6) PCB_HEXKEY(6);
+        else if (hexkey_minb == 5) PCB_HEXKEY(5);
+        else PCB_HEXKEY(8);
+#undef PCB_HEXKEY
+    };
     pb();
     k_cellgeo<<<div_up(ncell, 256), 256, 0, st>>>(cell_idx, cell_start, ncell, g, geo, &d_scr->err);
     pe("hexkey", 1, ncell, 60ull * ncell);
@@ -1135,8 +1145,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         RadixTemp rt;
         pb();
         radix_setup(rt, plan, nE_ub, estart, true);
-        k_hexkey<PAIRS><<<hexgrid, 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay, plan, kA, vA, d2oct, rt.ghist, segk, nseg,
-                                                 estart, eA, &d_scr->err);
+        launch_hexkey(plan, kA, vA, rt.ghist, estart, eA);
         pe("hexkey", 3, n, 32ull * n);
         trace_mark(st, "hexkey", h, n);
         int cur = radix_sort<PAIRS>(eA, nullptr, eB, nullptr, nE_ub, plan, rt, st, *this);
@@ -1209,8 +1218,7 @@ void BuilderImpl::build_level(u32 h, PcbPoint*& pts, u32*& bat, u32*& cell_start
         RadixTemp rt;
         pb();
         radix_setup(rt, plan, n, cell_start);
-        k_hexkey<PAIRS><<<hexgrid, 256, 0, st>>>(pts, n, cell_start, ncell, geo, g, lay, plan, kA, vA, d2oct, rt.ghist, segk, nseg,
-                                                 nullptr, nullptr, &d_scr->err);
+        launch_hexkey(plan, kA, vA, rt.ghist, nullptr, nullptr);
         pe("hexkey", nseg > 1 ? 3 : 1, n, (PAIRS ? 36ull : 32ull) * n);
         trace_mark(st, "hexkey", h, n);
 

@@ -521,8 +521,8 @@ __device__ __forceinline__ u32 cell_of_arrival(const u32* __restrict__ cell_star
 
 // Stage 2: hex-prism key (cell.rs:276-278 -> hex.rs:32-34) of every arrival, window-relative, plus the digit
 // histograms of all radix passes.
-template <bool PAIRS>
-__global__ void __launch_bounds__(256, 8)   // 32 registers: eight blocks per SM (37 registers ran 20 % slower)
+template <bool PAIRS, int MINB>
+__global__ void __launch_bounds__(256, MINB)   // MINB = 8: 32 registers, eight blocks per SM (37 registers ran 20 % slower)
 k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_start, u32 ncell,
          const CellGeo* __restrict__ geo, LevelGeom g, KeyLayout lay, RadixPlan plan, u64* __restrict__ keys,
          u32* __restrict__ vals, uint2* __restrict__ d2oct_out,
@@ -538,6 +538,7 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
     const u64 lo = (u64)blockIdx.x * chunk, hi = min((u64)n, lo + chunk);
     const u32 seg_lo = lo < hi ? find_segment(cell_start, ncell, (u32)lo) >> segk : 0u;   // first segment of the block
     const u32 seg_words = (u32)plan.npass * RADIX_MAX_BINS, slots = (u32)radix_hist_slots(plan);
+    const bool p3x8 = radix_plan_is_3x8(plan);
     u32 c = 0;
     CellGeo cg;
     cg.end = 0;
@@ -581,7 +582,10 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
             const u32 rel = (u32)i - cg.start;
             if (rel < elen) {   // every arrival without the record filter, else the early ones: these get sorted
                 if (estart) keys_e[ebase + rel] = key;
-                if (slot < slots) radix_hist_add(hist + slot * seg_words, plan, key, slot);
+                if (slot < slots) {
+                    if (p3x8) radix_hist_add_3x8(hist + slot * seg_words, plan.shift[0], key, slot);
+                    else radix_hist_add(hist + slot * seg_words, plan, key, slot);
+                }
                 else radix_hist_add_global(ghist + (u64)(seg_lo + slot) * seg_words, plan, key);
             }
         }

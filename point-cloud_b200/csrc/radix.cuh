@@ -96,6 +96,20 @@ __device__ __forceinline__ void radix_hist_add(u32* __restrict__ hist, const Rad
         if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u) atomicAdd(&hist[top * RADIX_MAX_BINS + d], (u32)__popc(peers));
     }
 }
+// The production plan - three 8-bit passes over 24 consecutive bits - without the plan lookups: one 64-bit shift, three
+// byte extractions (k_hexkey is issue-bound; the generic loop above costs ~45 of its ~210 instructions per arrival).
+__device__ __forceinline__ bool radix_plan_is_3x8(const RadixPlan& plan) {
+    return plan.npass == 3 && plan.bits[0] == 8 && plan.bits[1] == 8 && plan.bits[2] == 8 &&
+           plan.shift[1] == plan.shift[0] + 8 && plan.shift[2] == plan.shift[0] + 16;
+}
+__device__ __forceinline__ void radix_hist_add_3x8(u32* __restrict__ hist, int shift0, u64 key, u32 tag) {
+    const u32 kk = (u32)(key >> shift0);
+    atomicAdd(&hist[kk & 0xFFu], 1u);
+    atomicAdd(&hist[RADIX_MAX_BINS + ((kk >> 8) & 0xFFu)], 1u);
+    const u32 d = (kk >> 16) & 0xFFu;   // most significant digit: nearly uniform inside a warp, aggregated (see above)
+    const u32 peers = __match_any_sync(__activemask(), d | (tag << RADIX_MAX_BITS));
+    if ((peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0u) atomicAdd(&hist[2 * RADIX_MAX_BINS + d], (u32)__popc(peers));
+}
 // Segmented variant: a block accumulates the histograms of the first RADIX_MAX_PASSES / npass segments it meets
 // (slot = segment - first segment of the block) in shared memory; anything beyond goes to global memory directly.
 __device__ __forceinline__ int radix_hist_slots(const RadixPlan& plan) { return RADIX_MAX_PASSES / plan.npass; }
