@@ -215,6 +215,30 @@ class BuilderImpl {
     bool inputs_borrowed = false;   // build_level must not free its inputs (slices of the run's level-0 arrays)
     double h2d_s = 0, build_s = 0, d2h_s = 0;
 
+    // Process-wide cache of idle streams per device: cudaStreamCreate / cudaStreamDestroy take driver locks that an NVML
+    // query of another thread or of a monitoring agent can hold for ~13 ms (measured: pcb_open / pcb_close of a warm
+    // process took 13-27 ms instead of 0.2 ms in one step out of three on some boxes while pcb_finish kept its time);
+    // a handle takes its two streams from here and hands them back idle.  Never destroyed (process lifetime).
+    struct StreamCache {
+        std::mutex mu;
+        std::map<int, std::vector<cudaStream_t>> idle;
+        cudaStream_t get(int dev) {
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                auto& v = idle[dev];
+                if (!v.empty()) { cudaStream_t s = v.back(); v.pop_back(); return s; }
+            }
+            cudaStream_t s = nullptr;
+            CUDA_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+            return s;
+        }
+        void put(int dev, cudaStream_t s) {   // s must be idle
+            std::lock_guard<std::mutex> lk(mu);
+            idle[dev].push_back(s);
+        }
+    };
+    static StreamCache& stream_cache() { static StreamCache* c = new StreamCache(); return *c; }
+
     BuilderImpl(int dev, uint32_t fl) : device(dev), flags(fl), profile((fl & PCB_FLAG_PROFILE) != 0) {
         int count = 0;
         cudaError_t e = cudaGetDeviceCount(&count);
@@ -222,12 +246,20 @@ class BuilderImpl {
             throw Error{PCB_ERR_CUDA, "no CUDA device: this library has no CPU fallback"};
         if (dev < 0 || dev >= count) throw Error{PCB_ERR_ARG, "bad device ordinal"};
         CUDA_TRY(cudaSetDevice(dev));
-        CUDA_TRY(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
-        CUDA_TRY(cudaStreamCreateWithFlags(&copy_st, cudaStreamNonBlocking));
-        cudaMemPool_t pool;
-        CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, dev));
-        uint64_t thr = UINT64_MAX;
-        CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+        st = stream_cache().get(dev);
+        copy_st = stream_cache().get(dev);
+        static std::mutex pool_mu;
+        static std::map<int, bool> pool_set;   // once per device: keep freed pool memory (no trim at synchronisation)
+        {
+            std::lock_guard<std::mutex> lk(pool_mu);
+            if (!pool_set[dev]) {
+                cudaMemPool_t pool;
+                CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, dev));
+                uint64_t thr = UINT64_MAX;
+                CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+                pool_set[dev] = true;
+            }
+        }
         u64 got = 0;
         h_scr = (Scratch*)g_pinned.get(sizeof(Scratch), &got);   // recycled: cudaHostAlloc costs ~0.1 ms
         h_scr_cap = got;
@@ -242,7 +274,7 @@ class BuilderImpl {
         }
         if (slab_thread.joinable()) slab_thread.join();
         if (h_slab) g_pinned.put(h_slab, slab_cap);
-        if (d_in && !in_borrowed) cudaFree(d_in);
+        if (d_in && !in_borrowed) cudaFreeAsync(d_in, st);
         if (d_raw) cudaFree(d_raw);
         if (pend_owned) {
             void* pend[4] = {pend_pts, pend_bat, pend_cell_start, pend_cell_idx};
@@ -255,8 +287,8 @@ class BuilderImpl {
         cudaStreamSynchronize(st);
         for (auto& t : host_tmps) g_pinned.put(t.first, t.second);
         if (arenas) g_arenas.release(arenas);
-        if (st && own_stream) cudaStreamDestroy(st);
-        if (copy_st) cudaStreamDestroy(copy_st);
+        if (st && own_stream) stream_cache().put(device, st);   // idle: synchronised above
+        if (copy_st) { cudaStreamSynchronize(copy_st); stream_cache().put(device, copy_st); }
     }
 
     // Arrivals of level `ext.level` supplied by the caller in (cell, tau) order with their CSR (multi-GPU: the fused
@@ -368,7 +400,7 @@ class BuilderImpl {
     }
 
     void set_stream(cudaStream_t s) {
-        if (st && own_stream) cudaStreamDestroy(st);
+        if (st && own_stream) { cudaStreamSynchronize(st); stream_cache().put(device, st); }
         st = s;
         own_stream = false;
     }
@@ -440,11 +472,12 @@ class BuilderImpl {
         slab_prefetch(n);
         if (n <= cap_in) return;
         if (n >= (1ull << 30)) throw Error{PCB_ERR_RANGE, "more than 2^30-1 points on one device"};
+        // stream-ordered pool allocation: the pool keeps freed memory (release threshold = max, set at open), so a warm
+        // process gets the staging buffer of the previous conversion back without cudaMalloc / cudaFree (driver locks)
         PcbPoint* p = nullptr;
-        CUDA_TRY(cudaMalloc(&p, n * sizeof(PcbPoint)));
+        CUDA_TRY(cudaMallocAsync((void**)&p, n * sizeof(PcbPoint), st));
         if (n_in) CUDA_TRY(cudaMemcpyAsync(p, d_in, n_in * sizeof(PcbPoint), cudaMemcpyDeviceToDevice, st));
-        CUDA_TRY(cudaStreamSynchronize(st));
-        if (d_in && !in_borrowed) CUDA_TRY(cudaFree(d_in));
+        if (d_in && !in_borrowed) CUDA_TRY(cudaFreeAsync(d_in, st));
         d_in = p;
         cap_in = n;
         in_borrowed = false;

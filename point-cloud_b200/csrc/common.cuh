@@ -78,8 +78,10 @@ __device__ __forceinline__ HexKey hex_from_world(float px, float py, float pz, c
     float temp3 = __fadd_rn(__fmul_rn(2.0f, x), 1.0f);
     float qf = fdiv_inv(__fadd_rn(temp1, temp3), inv.third);   // (temp1 + temp3) / 3.0
     float rf = fdiv_inv(__fadd_rn(temp1, temp2), inv.third);
-    i32 q = sat_i32(floorf(qf));
-    i32 r = (i32)(0u - (u32)sat_i32(floorf(rf)));
+    // floor then saturating conversion == ONE conversion rounding towards minus infinity (cvt.rmi.s32.f32 saturates and
+    // maps NaN to 0 like cvt.rzi; beyond the i32 range floorf is the identity)
+    i32 q = __float2int_rd(qf);
+    i32 r = (i32)(0u - (u32)__float2int_rd(rf));
     i32 h = sat_i32(fdiv_inv(pz, inv.z));   // (pz / R) as i32: truncation
     i32 e = (i32)((u32)r - (u32)(r & 1));  // even => `/ 2` is exact
     HexKey k;

@@ -534,9 +534,10 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
     __syncthreads();
     u32 bad = 0;
     // every block owns one contiguous chunk of arrivals: the cell ordinal is searched once, then walked
-    const u64 chunk = (((u64)n + gridDim.x - 1) / gridDim.x + 255ull) & ~255ull;
-    const u64 lo = (u64)blockIdx.x * chunk, hi = min((u64)n, lo + chunk);
-    const u32 seg_lo = lo < hi ? find_segment(cell_start, ncell, (u32)lo) >> segk : 0u;   // first segment of the block
+    // (n < 2^30 per level, builder.cu: 32-bit indices cannot wrap, and addresses are one IMAD.WIDE each)
+    const u32 chunk = (u32)(((((u64)n + gridDim.x - 1) / gridDim.x) + 255ull) & ~255ull);
+    const u32 lo = (u32)min((u64)n, (u64)blockIdx.x * chunk), hi = (u32)min((u64)n, (u64)lo + chunk);
+    const u32 seg_lo = lo < hi ? find_segment(cell_start, ncell, lo) >> segk : 0u;   // first segment of the block
     const u32 seg_words = (u32)plan.npass * RADIX_MAX_BINS, slots = (u32)radix_hist_slots(plan);
     const bool p3x8 = radix_plan_is_3x8(plan);
     u32 c = 0;
@@ -544,19 +545,26 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
     cg.end = 0;
     u32 slot = 0;   // segment of cell c relative to the block's first segment (changes with the cell: rarely)
     u32 ebase = 0, elen = 0xFFFFFFFFu;   // record filter: the cell's early arrivals go to keys_e[ebase ...), elen of them
+    // key = cell | prism (| arrival position): the cell part only changes with the cell, the prism part fits 32 bits for
+    // every grid whose window has <= 32 bits - one 64-bit shift per arrival instead of four
+    const bool narrow = g.hexbits <= 32;
+    const int cshift = g.hexbits + (PAIRS ? 0 : lay.pb);
+    u64 cbase = 0;
     if (lo + threadIdx.x < hi) {
-        c = find_segment(cell_start, ncell, (u32)(lo + threadIdx.x));
+        c = find_segment(cell_start, ncell, lo + threadIdx.x);
         cg = load_geo(geo, c);
         slot = (c >> segk) - seg_lo;
+        cbase = (u64)c << cshift;
         if (estart) { ebase = __ldg(estart + c); elen = __ldg(estart + c + 1) - ebase; }
     }
-    for (u64 i0 = lo; i0 < hi; i0 += 256) {
-        u64 i = i0 + threadIdx.x;
+    for (u32 i0 = lo; i0 < hi; i0 += 256) {
+        const u32 i = i0 + threadIdx.x;
         if (i < hi) {
             PcbPoint p = pts[i];
-            if (cg.end <= (u32)i) {
-                do cg = load_geo(geo, ++c); while (cg.end <= (u32)i);
+            if (cg.end <= i) {
+                do cg = load_geo(geo, ++c); while (cg.end <= i);
                 slot = (c >> segk) - seg_lo;
+                cbase = (u64)c << cshift;
                 if (estart) { ebase = __ldg(estart + c); elen = __ldg(estart + c + 1) - ebase; }
             }
             HexKey k = hex_from_world(p.x, p.y, p.z, g.inv);
@@ -567,19 +575,22 @@ k_hexkey(const PcbPoint* __restrict__ pts, u32 n, const u32* __restrict__ cell_s
                 bad |= PCB_DERR_HEXRANGE;
                 rx &= (1u << g.bx) - 1u; ry &= (1u << g.by) - 1u; rz &= (1u << g.bz) - 1u;
             }
-            u64 key = ((u64)c << g.hexbits) | ((u64)rz << (g.bx + g.by)) | ((u64)ry << g.bx) | (u64)rx;
-            if (PAIRS) {
-                vals[i] = (u32)i;
+            u64 key;
+            if (narrow) {
+                const u32 prism = (rz << (g.bx + g.by)) | (ry << g.bx) | rx;
+                key = PAIRS ? (cbase | prism) : (cbase | ((u64)prism << lay.pb) | i);
             } else {
-                key = (key << lay.pb) | i;
+                key = ((u64)c << g.hexbits) | ((u64)rz << (g.bx + g.by)) | ((u64)ry << g.bx) | (u64)rx;
+                if (!PAIRS) key = (key << lay.pb) | i;
             }
+            if (PAIRS) vals[i] = i;
             keys[i] = key;
             // what the contest needs of this point, by arrival position: ONE 8-byte record (d2, child octant) that
             // stays L2-resident per cell, instead of a random 16-byte gather of the point itself (one DRAM sector per
             // arrival).  One record = one L2 sector per gather; d2 and octant in separate arrays cost two.
             d2oct_out[i] = make_uint2(__float_as_uint(hex_d2(k, p.x, p.y, p.z, g.R, g.half_sqrt3, g.row_pitch)),
                                       (p.x >= cg.tx ? 4u : 0u) | (p.y >= cg.ty ? 2u : 0u) | (p.z >= cg.tz ? 1u : 0u));
-            const u32 rel = (u32)i - cg.start;
+            const u32 rel = i - cg.start;
             if (rel < elen) {   // every arrival without the record filter, else the early ones: these get sorted
                 if (estart) keys_e[ebase + rel] = key;
                 if (slot < slots) {
