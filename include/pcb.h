@@ -180,7 +180,10 @@ int pcb_write_metadata(const char* out_dir, uint64_t number_of_points, uint32_t 
 int pcb_get_config(const pcb_handle* h, uint32_t* cell_point_overflow_limit, uint32_t* sub_grid_dimension,
                    float* max_cell_size);
 void pcb_close(pcb_handle* h);
-/* Node images are staged in pinned host buffers that are recycled across handles; this frees the idle ones. */
+/* A warm process keeps what a conversion needs between handles: pinned host buffers (node images, staging chunks),
+   the device arenas, the staging memory of the stream-ordered pool and two idle streams per device - pcb_open /
+   pcb_close then make no allocating or driver-lock calls.  This call frees the idle buffers, arenas and pool memory
+   (the streams stay: a few hundred bytes each). */
 void pcb_trim_host_cache(void);
 const char* pcb_last_error(const pcb_handle* h);
 

@@ -238,6 +238,24 @@ class BuilderImpl {
         }
     };
     static StreamCache& stream_cache() { static StreamCache* c = new StreamCache(); return *c; }
+    struct PoolDevices {
+        std::mutex mu;
+        std::map<int, bool> set;   // devices whose default pool this library configured (and may hold cached memory in)
+    };
+    static PoolDevices& pool_devices() { static PoolDevices* p = new PoolDevices(); return *p; }
+    static void trim_pools() {   // pcb_trim_host_cache: hand the pool's idle memory back to the driver
+        std::lock_guard<std::mutex> lk(pool_devices().mu);
+        int cur = 0;
+        cudaGetDevice(&cur);
+        for (auto& kv : pool_devices().set) {
+            cudaMemPool_t pool;
+            if (cudaSetDevice(kv.first) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, kv.first) == cudaSuccess) {
+                cudaDeviceSynchronize();
+                cudaMemPoolTrimTo(pool, 0);
+            }
+        }
+        cudaSetDevice(cur);
+    }
 
     BuilderImpl(int dev, uint32_t fl) : device(dev), flags(fl), profile((fl & PCB_FLAG_PROFILE) != 0) {
         int count = 0;
@@ -248,16 +266,14 @@ class BuilderImpl {
         CUDA_TRY(cudaSetDevice(dev));
         st = stream_cache().get(dev);
         copy_st = stream_cache().get(dev);
-        static std::mutex pool_mu;
-        static std::map<int, bool> pool_set;   // once per device: keep freed pool memory (no trim at synchronisation)
-        {
-            std::lock_guard<std::mutex> lk(pool_mu);
-            if (!pool_set[dev]) {
+        {   // once per device: the stream-ordered pool keeps freed memory (no trim at synchronisation)
+            std::lock_guard<std::mutex> lk(pool_devices().mu);
+            if (!pool_devices().set[dev]) {
                 cudaMemPool_t pool;
                 CUDA_TRY(cudaDeviceGetDefaultMemPool(&pool, dev));
                 uint64_t thr = UINT64_MAX;
                 CUDA_TRY(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
-                pool_set[dev] = true;
+                pool_devices().set[dev] = true;
             }
         }
         u64 got = 0;
@@ -1729,6 +1745,7 @@ int route_bbox_static(int device, void* stream, const pcb_point* d_pts, uint64_t
 void trim_host_cache() {
     g_pinned.trim();
     g_arenas.trim();
+    BuilderImpl::trim_pools();
 }
 
 int device_count() {

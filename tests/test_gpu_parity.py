@@ -311,3 +311,23 @@ def test_gui_converter_preset_batch_50000_count_by_delta(tmp_path):
         assert o2.points_by_delta == len(B) and st2.number_of_points == len(A) + o2.points_by_delta
         compare_trees(read_tree(d_o), read_tree(d_g), "oracle-50k-merge", "gpu-50k-merge")
         assert mj2 == o2.meta_json
+
+
+def test_trim_caches_between_conversions():
+    """pcb_trim_host_cache (pinned buffers, arenas, stream-ordered pool memory) between conversions of a warm process:
+    the next conversion re-creates what it needs and gives the same tree."""
+    import torch
+    pcb = load_pcb()
+    lib = pcb.load_library()
+    rng = np.random.default_rng(23)
+    pts = make_points(rng.random((120_000, 3)) * [300, 200, 40] - [150, 100, 5])
+    cfg = (300, 16, 64.0)
+    o = oracle_convert([pts], config=cfg, batch_size=4000)
+    for round_no in range(3):
+        nodes, mj, st, _ = _gpu([pts], config=cfg, bs=4000)
+        compare_trees(o.nodes, nodes, "oracle", f"gpu (conversion {round_no})")
+        assert mj == o.meta_json
+        free0, _ = torch.cuda.mem_get_info()
+        lib.pcb_trim_host_cache()
+        free1, _ = torch.cuda.mem_get_info()
+        assert free1 >= free0, "trimming must not take device memory"
