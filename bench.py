@@ -569,6 +569,11 @@ def main():
             write_ply(ply, hnp)
             cli = ROOT / "point-cloud_b200" / "point_converter"
             cold = None
+            # the child is a FRESH process: give back what this (warm) process holds first - pinned caches, arenas, pool
+            # memory - so that the child's own page-locking and allocations are not measured against a crowded box
+            host = hnp = None
+            pcb.load_library().pcb_trim_host_cache()
+            torch.cuda.empty_cache()
             if cli.exists():
                 d = os.path.join(scratch_dir, "cold")
                 t0 = time.perf_counter()
